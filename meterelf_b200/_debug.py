@@ -1,0 +1,22 @@
+"""``DEBUG`` environment switch (reference: ``_debug.py:1-14``).
+
+Only the text side of debug mode exists here: the CLI appends the meter_values dict and
+per-image errors are re-raised.  The reference's HighGUI windows (``cv2.imshow``) are
+unavailable on this box and are left out (out of scope).
+"""
+import os
+
+_OFF_WORDS = {'0', 'no', 'off', 'false'}
+
+DEBUG = set(
+    word for word in os.getenv('DEBUG', '').replace(',', ' ').split()
+    if word.lower() not in _OFF_WORDS)
+
+if 'all' in DEBUG:
+    DEBUG = {'masks'}
+
+
+def reraise_if_debug_on() -> None:
+    """Call inside an ``except`` block: re-raises the active exception in debug mode."""
+    if DEBUG:
+        raise
