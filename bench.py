@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""Throughput of the dial-reading hot path: meter readings/sec on 640x480 frames.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one pass of the whole path (locate dials + read 4 dials + value) over one
+HBM-resident synthetic batch (default 4096 frames of 640x480x3 u8 per GPU = 3.77 GB,
+larger than L2, so no flush between steps).  Frames are "S-planted" (SURVEY.md 8d):
+uniform noise canvases with decoded sample meter crops pasted at the meter_rect with a
+seeded +-6 px jitter, so every stage runs on every frame and the expected readings are
+known.  Prints ONE JSON line (rank 0).  Frames shard by index over the GPUs: no data-path
+collective; torch.distributed is used only for the barrier and the max-over-ranks time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
+
+METRIC = 'meter readings/sec (640x480 frames)'
+UNIT = 'frames/s'
+FRAME_H, FRAME_W = 640, 480        # the sample frames are portrait: 480 wide, 640 tall
+SMI_QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+
+def load_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as fp:
+            d = json.load(fp)
+        return dict(hbm_gbs=d['hbm_gbs'], bf16_tflops=d['bf16_tflops'], source='measured')
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source='fallback')
+
+
+def workload_config(frames):
+    return {
+        'workload': 'synthetic %dx%d BGR batch of %d frames per GPU, S-planted sample meter '
+                    'crops (sample-images1 params, meter_rect 250x250, template 188x119)'
+                    % (FRAME_H if False else 640, 480, frames),
+        'frames_per_gpu': frames, 'frame_h': FRAME_H, 'frame_w': FRAME_W,
+        'bytes_per_frame': FRAME_H * FRAME_W * 3,
+        'l2': 'batch (%.2f GB) is larger than L2; no flush between steps' % (
+            frames * FRAME_H * FRAME_W * 3 / 1e9),
+        'parallelism': 'frames sharded by index, one process per GPU, host-side gather',
+    }
+
+
+def planted_offsets(n, seed):
+    rng = np.random.default_rng(seed)
+    return rng.integers(-6, 7, size=(n, 2))
+
+
+def make_frames_host(gs, crops, n, seed):
+    """Host (numpy) version of the synthetic batch, used for the CPU arms and checks."""
+    rng = np.random.default_rng(seed + 1)
+    (x0, y0, x1, y1) = gs.meter_rect
+    frames = rng.integers(0, 256, size=(n, FRAME_H, FRAME_W, 3), dtype=np.uint8)
+    off = planted_offsets(n, seed)
+    for i in range(n):
+        (dx, dy) = off[i]
+        frames[i, y0 + dy:y1 + dy, x0 + dx:x1 + dx] = crops[i % len(crops)]
+    return frames
+
+
+def make_frames_device(torch, gs, crops, n, seed, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed + 1)
+    frames = torch.randint(0, 256, (n, FRAME_H, FRAME_W, 3), dtype=torch.uint8, device=device,
+                           generator=g)
+    d_crops = torch.from_numpy(np.ascontiguousarray(crops)).to(device)
+    (x0, y0, x1, y1) = gs.meter_rect
+    off = planted_offsets(n, seed)
+    for i in range(n):
+        (dx, dy) = (int(off[i][0]), int(off[i][1]))
+        frames[i, y0 + dy:y1 + dy, x0 + dx:x1 + dx] = d_crops[i % len(crops)]
+    return frames
+
+
+def valid_crops(gs):
+    sub = gs.subset()
+    names = [str(s) for s in sub['names']]
+    keep = [i for (i, fn) in enumerate(names) if gs.expected[fn]['status'] == 0]
+    return sub['crops'][keep]
+
+
+class ClockSampler:
+    def __init__(self, gpu_index):
+        self.tmp = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(gpu_index), '--query-gpu=' + SMI_QUERY,
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=self.tmp, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.tmp.flush()
+        self.tmp.seek(0)
+        sm, smax, power, reasons = [], [], [], set()
+        for line in self.tmp.read().splitlines():
+            cols = [c.strip() for c in line.split(',')]
+            if len(cols) < 9:
+                continue
+            try:
+                sm.append(float(cols[1])); smax.append(float(cols[2])); power.append(float(cols[3]))
+            except ValueError:
+                continue
+            for (name, val) in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown',
+                                    'sw_power_cap'), cols[5:9]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        os.unlink(self.tmp.name)
+        if sm:
+            busy = [s for (s, p) in zip(sm, power) if p >= 0.5 * max(power)] or sm
+            out.update(sm_mhz=float(np.median(busy)), sm_max_mhz=max(smax), samples=len(sm),
+                       power_w_max=max(power), reasons=sorted(reasons))
+        return out
+
+
+def cpu_arm(gs, frames_host, n_threads):
+    """The oracle port on host cores over full frames (meter_rect window by pointer math)."""
+    import oracle
+    (x0, y0, x1, y1) = gs.meter_rect
+    view = frames_host[:, y0:y1, x0:x1]
+    O = gs.oracle_params()
+    t0 = time.perf_counter()
+    res = oracle.read_batch(O, view, n_threads=n_threads)
+    dt = time.perf_counter() - t0
+    return (res, dt)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference itself is
+    Python + OpenCV and cannot travel to the GPU box) on all host cores, same workload."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    from helpers import golden_set
+    gs = golden_set(1)
+    cores = len(os.sched_getaffinity(0))
+    sample = max(cores * 4, 64)
+    frames = make_frames_host(gs, valid_crops(gs), sample, seed=1234)
+    times = []
+    for i in range(args.warmup + args.steps):
+        (_res, dt) = cpu_arm(gs, frames, cores)
+        if i >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = sample * len(times) / total
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * total / len(times), 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'u8/int32/f64', 'data': 'synthetic',
+        'config': workload_config(args.frames),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': '%d frames per step' % sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from helpers import golden_set
+    from meterelf_b200 import _engine
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise _engine.EngineUnavailableError('bench needs a CUDA device; there is no CPU fallback')
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=device)
+
+    gs = golden_set(1)
+    crops = valid_crops(gs)
+    n = args.frames
+    seed = 1234 + rank
+    eng = gs.engine(cropped_input=False, device=local)
+    d_frames = make_frames_device(torch, gs, crops, n, seed, device)
+    d_out = torch.zeros((n, _engine.RESULT_DTYPE.itemsize), dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream()
+    row_stride, frame_stride = FRAME_W * 3, FRAME_H * FRAME_W * 3
+
+    def step():
+        eng.read_device(d_frames.data_ptr(), n, FRAME_H, FRAME_W, row_stride, frame_stride,
+                        d_out.data_ptr(), stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    launches0 = _engine.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    launches = _engine.launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * n * args.steps / (ms_total / 1e3)
+
+    # ---- correctness spot check of the timed output (not timed) ------------------------
+    res = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n)
+    n_ok = int(np.sum(res['status'] == 0))
+
+    # ---- the dominant kernel alone: TM_CCOEFF locate (BGR in, lightness on the fly) -----
+    d_xy = torch.zeros((n, 2), dtype=torch.int32, device=device)
+    d_val = torch.zeros((n,), dtype=torch.float32, device=device)
+
+    def match_only():
+        eng.match_template_device(d_frames.data_ptr(), 3, n, FRAME_H, FRAME_W, row_stride,
+                                  frame_stride, True, d_xy.data_ptr(), d_val.data_ptr(), 0,
+                                  stream.cuda_stream)
+    match_only()
+    torch.cuda.synchronize()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record(stream)
+    for _ in range(args.steps):
+        match_only()
+    k1.record(stream)
+    torch.cuda.synchronize()
+    match_ms = k0.elapsed_time(k1) / args.steps
+
+    # ---- stage 1 as a standalone fused pass over the full frames (5 B/px) ---------------
+    nconv = min(n, 1024)
+    d_l = torch.empty((nconv, FRAME_H, FRAME_W), dtype=torch.uint8, device=device)
+    d_m = torch.empty((nconv, FRAME_H, FRAME_W), dtype=torch.uint8, device=device)
+
+    def convert_only():
+        _engine.convert_hls_device(local, d_frames.data_ptr(), nconv, FRAME_H, FRAME_W, row_stride,
+                                   frame_stride, gs.hue_shift, True, 0, d_l.data_ptr(),
+                                   (116, 35, 95), (134, 125, 165), d_m.data_ptr(), stream.cuda_stream)
+    for _ in range(3):
+        convert_only()
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record(stream)
+    for _ in range(args.steps):
+        convert_only()
+    c1.record(stream)
+    torch.cuda.synchronize()
+    conv_ms = c0.elapsed_time(c1) / args.steps
+    clocks = sampler.stop() if sampler else None
+
+    # ---- end to end through the public host API: pinned host frames in, results out -----
+    e2e = None
+    if rank == 0 or world > 1:
+        n_e2e = min(n, args.e2e_frames)
+        h_frames = torch.empty((n_e2e, FRAME_H, FRAME_W, 3), dtype=torch.uint8).pin_memory()
+        h_frames.copy_(d_frames[:n_e2e])
+        h_np = h_frames.numpy()
+        eng.read_frames(h_np[:64])
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            h_res = eng.read_frames(h_np)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        te = torch.tensor([dt], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        (x0, y0, x1, y1) = gs.meter_rect
+        e2e = {'value': world * n_e2e * args.steps / float(te.item()), 'unit': UNIT,
+               'h2d_bytes_per_step': int(n_e2e * (y1 - y0) * (x1 - x0) * 3),
+               'd2h_bytes_per_step': int(n_e2e * _engine.RESULT_DTYPE.itemsize),
+               'frames_per_step': n_e2e,
+               'note': 'melf_read_batch: pinned host frames, only meter_rect rows cross PCIe'}
+        assert np.array_equal(h_res['status'], res['status'][:n_e2e])
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- CPU baseline (oracle port) on a bounded sample, same frames -------------------
+    cores = len(os.sched_getaffinity(0))
+    sample = min(n, max(cores * 4, 64))
+    host_sample = d_frames[:sample].cpu().numpy()
+    (cpu_res, cpu_dt) = cpu_arm(gs, host_sample, cores)
+    mism = 0
+    for i in range(sample):
+        a, b = res[i], cpu_res[i]
+        same = (a['status'] == b['status'] and a['match_x'] == b['match_x'] and
+                a['match_y'] == b['match_y'] and
+                np.array_equal(a['dial_pos'][:4], b['dial_pos'][:4], equal_nan=True))
+        mism += 0 if same else 1
+
+    peaks = load_peaks()
+    rw, rh = 250 - 188 + 1, 250 - 119 + 1
+    macs = rw * rh * 188 * 119
+    tops = 2.0 * macs * n / (match_ms / 1e3) / 1e12
+    int8_peak = 2.0 * peaks['bf16_tflops']
+    conv_bytes = 5.0 * FRAME_H * FRAME_W * nconv
+    conv_gbs = conv_bytes / (conv_ms / 1e3) / 1e9
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+        'warmup': max(args.warmup, 3), 'ms_per_step': ms_total / args.steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'u8/int32 (correlation), f32 (HLS), f64 (angles)', 'data': 'synthetic',
+        'config': workload_config(n),
+        'e2e': e2e, 'gpu_launches': int(launches), 'clocks': clocks,
+        'roofline': {
+            'kernel': 'melf_match_kernel (TM_CCOEFF, exact integer correlation)',
+            'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
+            'frac': tops / int8_peak, 'traffic': None,
+            'note': 'algorithmic 2*%d MAC/frame; peak = 2 x %s bf16 dense (int8 tensor rate); '
+                    'kernel share of step %.2f' % (macs, peaks['source'], match_ms / (ms_total / args.steps)),
+        },
+        'stage_rooflines': [{
+            'kernel': 'melf_convert_vec_kernel (fused BGR->HLS + hue shift + L plane + mask, full frames)',
+            'bound': 'hbm', 'achieved': conv_gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
+            'frac': conv_gbs / peaks['hbm_gbs'], 'traffic': None,
+            'note': 'algorithmic 5 B/px x %d px; peak %s' % (FRAME_H * FRAME_W * nconv, peaks['source'])}],
+        'cpu_baseline': {'value': sample / cpu_dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': '%d frames of the same batch' % sample,
+                         'mismatches_vs_gpu': mism},
+        'check': {'frames_read_ok': n_ok, 'frames': n},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--frames', type=int, default=4096, help='frames per GPU')
+    ap.add_argument('--e2e-frames', type=int, default=4096)
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,86 @@
+"""Frame I/O and dial location (reference: ``_image.py:12-81``).
+
+JPEG decoding stays on the host with ``cv2.imread`` exactly as in the reference (so the
+decoded pixels are identical); everything after the decoded BGR frame runs on the GPU.
+"""
+from typing import Dict, Optional, Tuple
+
+import numpy
+
+from ._params import Params as _Params
+from ._types import Image, Rect, TemplateMatchResult
+from .exceptions import DialsNotFoundError, ImageLoadingError
+
+
+def _imread(filename: str, grayscale: bool = False) -> Optional[Image]:
+    import cv2
+    return cv2.imread(filename, cv2.IMREAD_GRAYSCALE if grayscale else cv2.IMREAD_COLOR)
+
+
+class ImageFile:
+    def __init__(self, filename: str, params: _Params,
+                 bgr_image: Optional[Image] = None) -> None:
+        self.filename = filename
+        self.params = params
+        self.bgr_image = bgr_image
+
+    # -- host side ----------------------------------------------------------------------
+    def load_frame(self) -> Tuple[Image, bool]:
+        """(frame, needs_crop): an injected ``bgr_image`` is used as is, un-cropped
+        (``_image.py:47-48``); a decoded file still has to be cut to ``meter_rect``."""
+        if self.bgr_image is not None:
+            return (self.bgr_image, False)
+        img = _imread(self.filename)
+        if img is None:
+            raise ImageLoadingError(self.filename)
+        return (img, True)
+
+    def get_bgr_image(self) -> Image:
+        (frame, needs_crop) = self.load_frame()
+        if not needs_crop:
+            return frame
+        ((x0, y0), (x1, y1)) = self.params.meter_rect
+        return frame[y0:y1, x0:x1]
+
+    # -- GPU side -----------------------------------------------------------------------
+    def get_hls_image(self) -> Image:
+        from ._utils import convert_to_hls
+        return convert_to_hls(self.get_bgr_image(), self.params.hue_shift)
+
+    def find_dials(self) -> TemplateMatchResult:
+        """``_find_dials`` (``_image.py:57-66``): TM_CCOEFF arg-max on the lightness plane."""
+        from ._utils import match_template_bgr
+        template = get_dials_template(self.params)
+        match = match_template_bgr(self.get_bgr_image(), template, self.params)
+        if match.max_val < self.params.dials_match_threshold:
+            raise DialsNotFoundError(
+                self.filename, extra_info={'match val': match.max_val})
+        return match
+
+    def get_dials_hls(self) -> Image:
+        match = self.find_dials()
+        ((x0, y0), (x1, y1)) = match.rect
+        return self.get_hls_image()[y0:y1, x0:x1]
+
+
+_template_cache: Dict[int, Tuple[_Params, Image]] = {}
+
+
+def get_dials_template(params: _Params) -> Image:
+    entry = _template_cache.get(id(params))
+    if entry is None or entry[0] is not params:
+        template = _imread(params.dials_file, grayscale=True)
+        if template is None:
+            raise IOError("Cannot read dials template: {}".format(params.dials_file))
+        entry = (params, template)
+        _template_cache[id(params)] = entry
+    assert entry[1].shape == params.dials_template_size
+    return entry[1]
+
+
+def as_rect(top_left: Tuple[int, int], size_wh: Tuple[int, int]) -> Rect:
+    return Rect(top_left, (top_left[0] + size_wh[0], top_left[1] + size_wh[1]))
+
+
+def stack_frames(frames) -> numpy.ndarray:
+    return numpy.stack([numpy.ascontiguousarray(f) for f in frames])

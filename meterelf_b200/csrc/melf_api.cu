@@ -1,0 +1,462 @@
+// C ABI of the dial-reading path (include/meterelf_b200.h): context, batching, launches.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "melf_common.cuh"
+
+// ---- kernel launchers implemented in the other translation units ---------------------
+#include "melf_args.h"
+
+cudaError_t melf_launch_dials(const MelfDialsArgs &args, int n_frames, cudaStream_t stream);
+dim3 melf_match_plan(MelfMatchArgs &a, int n_frames);
+cudaError_t melf_launch_match(const MelfMatchArgs &args, dim3 grid, cudaStream_t stream);
+cudaError_t melf_launch_match_unpack(const u64 *key, int n, int res_w, int32_t *xy, float *val,
+                                     cudaStream_t stream);
+cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStream_t stream);
+
+namespace {
+
+std::atomic<uint64_t> g_launches{0};
+std::mutex g_err_mutex;
+std::string g_create_error;
+
+constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
+
+}  // namespace
+
+struct melf_ctx {
+    int device = 0;
+    int num_sms = 148;
+    melf_params params{};              // pointers inside are NOT valid after create
+    std::string err;
+
+    // static device data
+    MelfDialDev *d_dials = nullptr;
+    uint16_t *d_ring_pos = nullptr;
+    double *d_ring_angle = nullptr;
+    double *d_ring_sqd = nullptr;
+    uint32_t *d_tmpl_words = nullptr;
+    uint32_t *d_ones_words = nullptr;
+    long long sum_t = 0, n_t = 0;
+    int tw4p = 0, steps = 0;
+    std::vector<int32_t> win_x0, win_y0;
+
+    // scratch for the async path
+    u64 *d_keys = nullptr;
+    int keys_cap = 0;
+
+    // pipeline resources of melf_read_batch
+    cudaStream_t streams[2] = {nullptr, nullptr};
+    uint8_t *d_chunk[2] = {nullptr, nullptr};
+    size_t chunk_bytes = 0;
+    melf_result *d_res[2] = {nullptr, nullptr};
+    melf_result *h_res = nullptr;       // pinned, 2 * kChunkFrames
+    u64 *d_chunk_keys[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+int fail(melf_ctx *ctx, int code, const std::string &msg)
+{
+    if (ctx) ctx->err = msg;
+    else {
+        std::lock_guard<std::mutex> lock(g_err_mutex);
+        g_create_error = msg;
+    }
+    return code;
+}
+
+int cuda_fail(melf_ctx *ctx, cudaError_t e, const char *what)
+{
+    return fail(ctx, MELF_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+#define MELF_CUDA(ctx, call)                                         \
+    do {                                                             \
+        cudaError_t e_ = (call);                                     \
+        if (e_ != cudaSuccess) return cuda_fail((ctx), e_, #call);   \
+    } while (0)
+
+// numpy-slice clipping of the meter_rect against the frame (_utils.py:52-54)
+int make_geom(melf_ctx *ctx, int h, int w, bool use_rect, MelfGeom *g)
+{
+    const melf_params &P = ctx->params;
+    int x0 = 0, y0 = 0, x1 = w, y1 = h;
+    if (use_rect) {
+        x0 = P.rect_x0 < w ? P.rect_x0 : w; x1 = P.rect_x1 < w ? P.rect_x1 : w;
+        y0 = P.rect_y0 < h ? P.rect_y0 : h; y1 = P.rect_y1 < h ? P.rect_y1 : h;
+    }
+    g->crop_x0 = x0; g->crop_y0 = y0;
+    g->crop_w = x1 - x0; g->crop_h = y1 - y0;
+    g->res_w = g->crop_w - P.tmpl_w + 1;
+    g->res_h = g->crop_h - P.tmpl_h + 1;
+    if (g->res_w < 1 || g->res_h < 1)
+        return fail(ctx, MELF_ERR_TOO_SMALL, "meter_rect crop is smaller than the dials template");
+    return MELF_OK;
+}
+
+void fill_match_args(const melf_ctx *ctx, MelfMatchArgs *a)
+{
+    a->tmpl_words = ctx->d_tmpl_words;
+    a->ones_words = ctx->d_ones_words;
+    a->tmpl_w = ctx->params.tmpl_w;
+    a->tmpl_h = ctx->params.tmpl_h;
+    a->sum_t = ctx->sum_t;
+    a->n_t = ctx->n_t;
+}
+
+int ensure_keys(melf_ctx *ctx, int n)
+{
+    if (n <= ctx->keys_cap) return MELF_OK;
+    if (ctx->d_keys) cudaFree(ctx->d_keys);
+    ctx->d_keys = nullptr; ctx->keys_cap = 0;
+    MELF_CUDA(ctx, cudaMalloc(&ctx->d_keys, (size_t)n * sizeof(u64)));
+    ctx->keys_cap = n;
+    return MELF_OK;
+}
+
+// locate + read on device-resident frames; keys = per-frame scratch (n entries)
+int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, size_t row_stride, size_t frame_stride,
+             const MelfGeom &geom, u64 *d_keys, melf_result *d_out, const melf_taps *taps,
+             cudaStream_t stream)
+{
+    MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
+    MelfMatchArgs m{};
+    fill_match_args(ctx, &m);
+    m.img = d_bgr; m.channels = 3;
+    m.row_stride = row_stride; m.frame_stride = frame_stride;
+    m.geom = geom;
+    m.match_key = d_keys;
+    m.result = nullptr;
+    // grid.z is limited to 65535 frames per launch
+    for (int f0 = 0; f0 < n; f0 += 65535) {
+        const int nf = n - f0 < 65535 ? n - f0 : 65535;
+        MelfMatchArgs mm = m;
+        mm.img = d_bgr + (size_t)f0 * frame_stride;
+        mm.match_key = d_keys + f0;
+        const dim3 grid = melf_match_plan(mm, nf);
+        MELF_CUDA(ctx, melf_launch_match(mm, grid, stream));
+        g_launches++;
+    }
+    MelfDialsArgs a{};
+    a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
+    a.geom = geom;
+    a.dials = ctx->d_dials;
+    a.ring_pos = ctx->d_ring_pos; a.ring_angle = ctx->d_ring_angle; a.ring_sqd = ctx->d_ring_sqd;
+    a.match_key = d_keys;
+    a.out = d_out;
+    if (taps) a.taps = *taps; else std::memset(&a.taps, 0, sizeof a.taps);
+    a.threshold = ctx->params.match_threshold;
+    a.n_dials = ctx->params.n_dials;
+    a.tmpl_w = ctx->params.tmpl_w; a.tmpl_h = ctx->params.tmpl_h;
+    a.hue_shift = ctx->params.hue_shift; a.s_tail = ctx->params.s_tail;
+    for (int k = 0; k < 4; k++) a.value_order[k] = ctx->params.value_order[k];
+    MELF_CUDA(ctx, melf_launch_dials(a, n, stream));
+    g_launches++;
+    return MELF_OK;
+}
+
+void free_ctx(melf_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_ring_angle);
+    cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
+    cudaFree(ctx->d_keys);
+    for (int i = 0; i < 2; i++) {
+        if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
+        cudaFree(ctx->d_chunk[i]); cudaFree(ctx->d_res[i]); cudaFree(ctx->d_chunk_keys[i]);
+    }
+    if (ctx->h_res) cudaFreeHost(ctx->h_res);
+    delete ctx;
+}
+
+}  // namespace
+
+extern "C" {
+
+int melf_abi_version(void) { return MELF_ABI_VERSION; }
+
+uint64_t melf_launch_count(void) { return g_launches.load(); }
+
+const char *melf_last_error(const melf_ctx *ctx)
+{
+    if (ctx) return ctx->err.c_str();
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> lock(g_err_mutex);
+    copy = g_create_error;
+    return copy.c_str();
+}
+
+int melf_create(melf_ctx **out, int device, const melf_params *P)
+{
+    if (!out) return fail(nullptr, MELF_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    std::string err;
+    int rc = melf_host_check_params(P, &err);
+    if (rc) return fail(nullptr, rc, err);
+
+    // host-side static tables first (no CUDA needed to fail on bad params)
+    std::vector<MelfDialDev> dials(P->n_dials);
+    MelfRingTables rings;
+    for (int d = 0; d < P->n_dials; d++) {
+        rc = melf_host_build_dial(P, d, &dials[d], &rings, &err);
+        if (rc) return fail(nullptr, rc, err);
+    }
+
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceCount");
+    if (device < 0 || device >= count)
+        return fail(nullptr, MELF_ERR_CUDA, "no such CUDA device");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
+
+    melf_ctx *ctx = new melf_ctx();
+    ctx->device = device;
+    ctx->params = *P;
+    ctx->params.tmpl = nullptr;
+    for (int d = 0; d < MELF_MAX_DIALS; d++) {
+        ctx->params.dials[d].mask = nullptr;
+        ctx->params.dials[d].circle_mask = nullptr;
+    }
+    cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
+    for (int d = 0; d < P->n_dials; d++) {
+        ctx->win_x0.push_back(dials[d].win_x0);
+        ctx->win_y0.push_back(dials[d].win_y0);
+    }
+
+    // template, packed 4 columns per word in the layout the match kernel streams:
+    // words[(jp*steps + s)*2 + q] = columns 4*(2jp+q)..+3 of template row s (0 beyond)
+    {
+        MelfMatchArgs plan{};
+        plan.tmpl_w = P->tmpl_w; plan.tmpl_h = P->tmpl_h;
+        plan.geom.res_w = 1; plan.geom.res_h = 1;
+        melf_match_plan(plan, 1);
+        ctx->tw4p = plan.tw4p; ctx->steps = plan.steps;
+        std::vector<uint32_t> words((size_t)plan.tw4p * plan.steps, 0), ones(plan.tw4p, 0);
+        for (int j4 = 0; j4 < plan.tw4p; j4++) {
+            for (int b = 0; b < 4; b++)
+                if (4 * j4 + b < P->tmpl_w) ones[j4] |= 1u << (8 * b);
+            for (int s = 0; s < plan.steps; s++) {
+                uint32_t w = 0;
+                if (s < P->tmpl_h)
+                    for (int b = 0; b < 4; b++)
+                        if (4 * j4 + b < P->tmpl_w)
+                            w |= (uint32_t)P->tmpl[(size_t)s * P->tmpl_w + 4 * j4 + b] << (8 * b);
+                words[((size_t)(j4 >> 1) * plan.steps + s) * 2 + (j4 & 1)] = w;
+            }
+        }
+        ctx->n_t = (long long)P->tmpl_w * P->tmpl_h;
+        ctx->sum_t = 0;
+        for (long long i = 0; i < ctx->n_t; i++) ctx->sum_t += P->tmpl[i];
+
+#define MELF_CREATE_CUDA(call)                                                  \
+    do {                                                                        \
+        cudaError_t e_ = (call);                                                \
+        if (e_ != cudaSuccess) {                                                \
+            int rc_ = cuda_fail(nullptr, e_, #call);                            \
+            free_ctx(ctx);                                                      \
+            return rc_;                                                         \
+        }                                                                       \
+    } while (0)
+
+        MELF_CREATE_CUDA(cudaMalloc(&ctx->d_tmpl_words, words.size() * 4));
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_tmpl_words, words.data(), words.size() * 4, cudaMemcpyHostToDevice));
+        MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ones_words, ones.size() * 4));
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ones_words, ones.data(), ones.size() * 4, cudaMemcpyHostToDevice));
+    }
+    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_dials, dials.size() * sizeof(MelfDialDev)));
+    MELF_CREATE_CUDA(cudaMemcpy(ctx->d_dials, dials.data(), dials.size() * sizeof(MelfDialDev), cudaMemcpyHostToDevice));
+    const size_t nr = rings.pos.size() ? rings.pos.size() : 1;
+    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ring_pos, nr * sizeof(uint16_t)));
+    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ring_angle, nr * sizeof(double)));
+    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ring_sqd, nr * sizeof(double)));
+    if (!rings.pos.empty()) {
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ring_pos, rings.pos.data(), nr * sizeof(uint16_t), cudaMemcpyHostToDevice));
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ring_angle, rings.angle.data(), nr * sizeof(double), cudaMemcpyHostToDevice));
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ring_sqd, rings.sqd.data(), nr * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    *out = ctx;
+    return MELF_OK;
+}
+
+void melf_destroy(melf_ctx *ctx) { free_ctx(ctx); }
+
+int melf_dial_window(const melf_ctx *ctx, int dial, int32_t *win_x0, int32_t *win_y0)
+{
+    if (!ctx || dial < 0 || dial >= ctx->params.n_dials || !win_x0 || !win_y0) return MELF_ERR_INVALID;
+    *win_x0 = ctx->win_x0[dial];
+    *win_y0 = ctx->win_y0[dial];
+    return MELF_OK;
+}
+
+int melf_read_batch_async(melf_ctx *ctx, const uint8_t *d_bgr, int n, int h, int w,
+                          size_t row_stride, size_t frame_stride,
+                          melf_result *d_out, const melf_taps *taps, void *stream)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if (n < 0 || h < 1 || w < 1 || !d_out || (n > 0 && !d_bgr))
+        return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
+    if (row_stride < (size_t)w * 3) return fail(ctx, MELF_ERR_INVALID, "row_stride < 3*w");
+    if (n == 0) return MELF_OK;
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    MelfGeom geom;
+    int rc = make_geom(ctx, h, w, true, &geom);
+    if (rc) return rc;
+    rc = ensure_keys(ctx, n);
+    if (rc) return rc;
+    return run_path(ctx, d_bgr, n, row_stride, frame_stride, geom, ctx->d_keys, d_out, taps,
+                    (cudaStream_t)stream);
+}
+
+int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
+                    size_t row_stride, size_t frame_stride, melf_result *out)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if (n < 0 || h < 1 || w < 1 || (n > 0 && (!bgr || !out)))
+        return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
+    if (row_stride < (size_t)w * 3) return fail(ctx, MELF_ERR_INVALID, "row_stride < 3*w");
+    if (n == 0) return MELF_OK;
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    MelfGeom geom;
+    int rc = make_geom(ctx, h, w, true, &geom);
+    if (rc) return rc;
+
+    // only the meter_rect rows travel: compact device layout [frame][crop_h][pitch]
+    const size_t crop_row_bytes = (size_t)geom.crop_w * 3;
+    const size_t pitch = (crop_row_bytes + 15) & ~(size_t)15;
+    const size_t frame_bytes = pitch * geom.crop_h;
+    const size_t need = frame_bytes * kChunkFrames;
+    if (!ctx->streams[0]) {
+        for (int i = 0; i < 2; i++) {
+            MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking));
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_res[i], sizeof(melf_result) * kChunkFrames));
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_chunk_keys[i], sizeof(u64) * kChunkFrames));
+        }
+        MELF_CUDA(ctx, cudaMallocHost(&ctx->h_res, sizeof(melf_result) * kChunkFrames * 2));
+    }
+    if (need > ctx->chunk_bytes) {
+        for (int i = 0; i < 2; i++) {
+            if (ctx->d_chunk[i]) cudaFree(ctx->d_chunk[i]);
+            ctx->d_chunk[i] = nullptr;
+        }
+        ctx->chunk_bytes = 0;
+        for (int i = 0; i < 2; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_chunk[i], need));
+        ctx->chunk_bytes = need;
+    }
+    MelfGeom cg = geom;
+    cg.crop_x0 = 0; cg.crop_y0 = 0;
+
+    const bool contiguous_frames = frame_stride == row_stride * (size_t)h;
+    int pending[2] = {0, 0}, pending_f0[2] = {0, 0};
+    int chunk = 0;
+    for (int f0 = 0; f0 < n; f0 += kChunkFrames, chunk++) {
+        const int b = chunk & 1;
+        const int nf = n - f0 < kChunkFrames ? n - f0 : kChunkFrames;
+        cudaStream_t st = ctx->streams[b];
+        if (pending[b]) {       // results of the chunk that used this buffer two rounds ago
+            MELF_CUDA(ctx, cudaStreamSynchronize(st));
+            std::memcpy(out + pending_f0[b], ctx->h_res + (size_t)b * kChunkFrames,
+                        sizeof(melf_result) * pending[b]);
+            pending[b] = 0;
+        }
+        if (contiguous_frames) {
+            cudaMemcpy3DParms p{};
+            p.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t *>(bgr) + (size_t)f0 * frame_stride,
+                                           row_stride, (size_t)w * 3, (size_t)h);
+            p.srcPos = make_cudaPos((size_t)geom.crop_x0 * 3, (size_t)geom.crop_y0, 0);
+            p.dstPtr = make_cudaPitchedPtr(ctx->d_chunk[b], pitch, crop_row_bytes, (size_t)geom.crop_h);
+            p.dstPos = make_cudaPos(0, 0, 0);
+            p.extent = make_cudaExtent(crop_row_bytes, (size_t)geom.crop_h, (size_t)nf);
+            p.kind = cudaMemcpyHostToDevice;
+            MELF_CUDA(ctx, cudaMemcpy3DAsync(&p, st));
+        } else {
+            for (int f = 0; f < nf; f++) {
+                const uint8_t *src = bgr + (size_t)(f0 + f) * frame_stride +
+                                     (size_t)geom.crop_y0 * row_stride + (size_t)geom.crop_x0 * 3;
+                MELF_CUDA(ctx, cudaMemcpy2DAsync(ctx->d_chunk[b] + (size_t)f * frame_bytes, pitch, src,
+                                                 row_stride, crop_row_bytes, (size_t)geom.crop_h,
+                                                 cudaMemcpyHostToDevice, st));
+            }
+        }
+        rc = run_path(ctx, ctx->d_chunk[b], nf, pitch, frame_bytes, cg, ctx->d_chunk_keys[b],
+                      ctx->d_res[b], nullptr, st);
+        if (rc) return rc;
+        MELF_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + (size_t)b * kChunkFrames, ctx->d_res[b],
+                                       sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
+        pending[b] = nf; pending_f0[b] = f0;
+    }
+    for (int b = 0; b < 2; b++)
+        if (pending[b]) {
+            MELF_CUDA(ctx, cudaStreamSynchronize(ctx->streams[b]));
+            std::memcpy(out + pending_f0[b], ctx->h_res + (size_t)b * kChunkFrames,
+                        sizeof(melf_result) * pending[b]);
+        }
+    return MELF_OK;
+}
+
+int melf_convert_hls(int device, const uint8_t *d_bgr, int n, int h, int w,
+                     size_t row_stride, size_t frame_stride, int hue_shift, int s_tail,
+                     uint8_t *d_hls, uint8_t *d_light,
+                     const uint8_t *lo, const uint8_t *hi, uint8_t *d_mask, void *stream)
+{
+    if (n < 0 || h < 1 || w < 1 || (n > 0 && !d_bgr) || row_stride < (size_t)w * 3 ||
+        hue_shift < 0 || hue_shift > 255 || (d_mask && (!lo || !hi)))
+        return fail(nullptr, MELF_ERR_INVALID, "bad melf_convert_hls arguments");
+    if (n == 0) return MELF_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    MelfConvertArgs a{};
+    a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
+    a.n = n; a.h = h; a.w = w;
+    a.hue_shift = hue_shift; a.s_tail = s_tail;
+    a.hls = d_hls; a.light = d_light; a.mask = d_mask;
+    a.lo = lo ? (lo[0] | (lo[1] << 8) | (lo[2] << 16)) : 0;
+    a.hi = hi ? (hi[0] | (hi[1] << 8) | (hi[2] << 16)) : 0xffffff;
+    e = melf_launch_convert(a, sms, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "melf_convert kernel launch");
+    g_launches++;
+    return MELF_OK;
+}
+
+int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
+                        size_t row_stride, size_t frame_stride, int use_rect,
+                        int32_t *d_max_xy, float *d_max_val, float *d_result, void *stream)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if ((channels != 1 && channels != 3) || n < 0 || h < 1 || w < 1 || (n > 0 && !d_img) ||
+        !d_max_xy || !d_max_val || row_stride < (size_t)w * channels)
+        return fail(ctx, MELF_ERR_INVALID, "bad melf_match_template arguments");
+    if (n == 0) return MELF_OK;
+    if (n > 65535) return fail(ctx, MELF_ERR_UNSUPPORTED, "more than 65535 frames per call");
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    MelfGeom geom;
+    int rc = make_geom(ctx, h, w, use_rect != 0, &geom);
+    if (rc) return rc;
+    rc = ensure_keys(ctx, n);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    MELF_CUDA(ctx, cudaMemsetAsync(ctx->d_keys, 0, (size_t)n * sizeof(u64), st));
+    MelfMatchArgs m{};
+    fill_match_args(ctx, &m);
+    m.img = d_img; m.channels = channels;
+    m.row_stride = row_stride; m.frame_stride = frame_stride;
+    m.geom = geom;
+    m.match_key = ctx->d_keys;
+    m.result = d_result;
+    const dim3 grid = melf_match_plan(m, n);
+    MELF_CUDA(ctx, melf_launch_match(m, grid, st));
+    g_launches++;
+    MELF_CUDA(ctx, melf_launch_match_unpack(ctx->d_keys, n, geom.res_w, d_max_xy, d_max_val, st));
+    g_launches++;
+    return MELF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,48 @@
+// Kernel argument blocks shared between melf_api.cu and the kernel translation units.
+#pragma once
+#include "melf_common.cuh"
+
+struct MelfDialsArgs {
+    const uint8_t *bgr;
+    size_t row_stride, frame_stride;
+    MelfGeom geom;
+    const MelfDialDev *dials;
+    const uint16_t *ring_pos;
+    const double *ring_angle;
+    const double *ring_sqd;
+    const u64 *match_key;
+    melf_result *out;
+    melf_taps taps;
+    double threshold;
+    int32_t n_dials, tmpl_w, tmpl_h, hue_shift, s_tail;
+    int32_t value_order[4];
+};
+
+struct MelfMatchArgs {
+    const uint8_t *img;          // BGR (channels = 3) or single channel frames
+    size_t row_stride, frame_stride;
+    int32_t channels;
+    MelfGeom geom;
+    const uint32_t *tmpl_words;  // [tw4p/2][steps][2]: template, 4 columns per word
+    const uint32_t *ones_words;  // [tw4p]: 1 per valid template column
+    int32_t tmpl_w, tmpl_h;
+    int32_t tw4p;                // template width in words, padded to even
+    int32_t steps;               // roundup(th + RY - 1, RY)
+    int32_t nyt;                 // y-threads per CTA
+    int32_t pitch_w;             // lightness tile row pitch in words
+    int32_t tile_rows;           // rows of the lightness tile = nyt*RY + steps - RY ... (+slack)
+    long long sum_t, n_t;
+    u64 *match_key;              // [n] atomicMax slot per frame (zeroed before launch)
+    float *result;               // optional [n][res_h][res_w]
+};
+
+struct MelfConvertArgs {
+    const uint8_t *bgr;
+    size_t row_stride, frame_stride;
+    int32_t n, h, w;
+    int32_t hue_shift, s_tail;
+    uint8_t *hls;      // [n][h][w][3] or NULL
+    uint8_t *light;    // [n][h][w]    or NULL
+    uint8_t *mask;     // [n][h][w]    or NULL
+    uint32_t lo, hi;   // packed H | L<<8 | S<<16 bounds (inclusive)
+};

@@ -1,0 +1,482 @@
+// Per-dial needle reading: one warp per (frame, dial), one block per frame.
+//
+// Replaces, for a whole batch, the per-dial loop of get_meter_value (_reading.py:28-96),
+// get_needle_points (_reading.py:118-151), get_dial_color (_reading.py:154-160),
+// get_mask_by_color (_utils.py:113-119) and determine_value_by_dial_positions
+// (_reading.py:163-182).
+//
+// Formulation (DESIGN.md "dial kernel"): everything the reference does on the 119x188
+// dials rect is ANDed with the dial's disc mask, so only the disc's bounding box plus a
+// 2-pixel halo matters.  That window (<= 64x64) is held as one 64-bit word per row, two
+// rows per lane, entirely in registers:
+//   inRange       -> ballots of the per-pixel HLS test (HLS recomputed from BGR on the fly)
+//   dilate/erode  -> shifts and ANDs/ORs of row words, neighbours by warp shuffle
+//   findContours + contourArea + drawContours(FILLED)
+//                 -> bit-parallel 8-connected flood per component, 4-connected exterior
+//                    flood for hole filling, bit-quad area (2*#quads4 + #quads3)
+//   momentum, ring angles, trimmed weighted mean
+//                 -> sequential float64 sums in the reference's order over host-built
+//                    static tables (per-pixel angle / squared distance / sort order depend
+//                    only on params), so dial positions are bit-identical to the oracle.
+#include "melf_common.cuh"
+#include "melf_args.h"
+
+namespace {
+
+constexpr u64 ALL1 = ~0ull;
+
+__device__ __forceinline__ u64 shfl_u64(u64 v, int src)
+{
+    return __shfl_sync(0xffffffffu, v, src);
+}
+__device__ __forceinline__ u64 shfl_up1(u64 v, u64 fill, int lane)
+{
+    u64 r = __shfl_up_sync(0xffffffffu, v, 1);
+    return lane == 0 ? fill : r;
+}
+__device__ __forceinline__ u64 shfl_down1(u64 v, u64 fill, int lane)
+{
+    u64 r = __shfl_down_sync(0xffffffffu, v, 1);
+    return lane == 31 ? fill : r;
+}
+__device__ __forceinline__ u64 warp_or64(u64 v)
+{
+    uint32_t lo = __reduce_or_sync(0xffffffffu, (uint32_t)v);
+    uint32_t hi = __reduce_or_sync(0xffffffffu, (uint32_t)(v >> 32));
+    return ((u64)hi << 32) | lo;
+}
+
+// fill every run of ones of m that contains a bit of s (carry propagation both ways)
+__device__ __forceinline__ u64 spread(u64 s, u64 m)
+{
+    s &= m;
+    const u64 up = (((m + s) ^ m) | s) & m;
+    const u64 mr = __brevll(m), sr = __brevll(s);
+    const u64 dn = __brevll((((mr + sr) ^ mr) | sr) & mr);
+    return up | dn;
+}
+__device__ __forceinline__ u64 h3(u64 x) { return x | (x << 1) | (x >> 1); }
+__device__ __forceinline__ u64 e3(u64 x) { return x & ((x << 1) | 1ull) & ((x >> 1) | (1ull << 63)); }
+
+// 8-connected flood of the seed inside `allowed` (rows 2*lane = a, 2*lane+1 = b)
+__device__ void flood8(u64 &ca, u64 &cb, const u64 al_a, const u64 al_b, const int lane)
+{
+    for (int it = 0; it < 8192; ++it) {
+        u64 na = spread(ca, al_a), nb = spread(cb, al_b);
+        const u64 up = shfl_up1(nb, 0, lane);      // row 2*lane-1
+        const u64 dn = shfl_down1(na, 0, lane);    // row 2*lane+2
+        na |= h3(up | nb) & al_a;
+        nb |= h3(na | dn) & al_b;
+        const bool changed = (na != ca) | (nb != cb);
+        ca = na; cb = nb;
+        if (!__any_sync(0xffffffffu, changed)) break;
+    }
+}
+
+// component -> component plus its holes (background not 4-connected to the outside)
+__device__ void fill_holes(const u64 ca, const u64 cb, u64 &fa, u64 &fb, const int lane)
+{
+    const uint32_t rows = __ballot_sync(0xffffffffu, (ca | cb) != 0);
+    const int lmin = __ffs(rows) - 1, lmax = 31 - __clz(rows);
+    const u64 uni = warp_or64(ca | cb);
+    const int cmin = __ffsll((long long)uni) - 1, cmax = 63 - __clzll((long long)uni);
+    const u64 colrange = (cmax == 63 ? ALL1 : ((1ull << (cmax + 1)) - 1)) & ~((1ull << cmin) - 1);
+    const bool inrows = lane >= lmin && lane <= lmax;
+    u64 ra = inrows ? ~colrange : ALL1, rb = ra;          // everything outside the bbox
+    const u64 al_a = ~ca, al_b = ~cb;
+    for (int it = 0; it < 8192; ++it) {
+        u64 na = ra | spread(ra & al_a, al_a), nb = rb | spread(rb & al_b, al_b);
+        const u64 up = shfl_up1(nb, ALL1, lane);
+        const u64 dn = shfl_down1(na, ALL1, lane);
+        na |= (up | nb) & al_a;
+        nb |= (na | dn) & al_b;
+        const bool changed = (na != ra) | (nb != rb);
+        ra = na; rb = nb;
+        if (!__any_sync(0xffffffffu, changed)) break;
+    }
+    fa = ~ra; fb = ~rb;
+}
+
+__device__ __forceinline__ int quad_area2(u64 x, u64 y)
+{
+    const u64 q1 = x >> 1, q3 = y >> 1;
+    const u64 t01 = x & q1, x01 = x ^ q1, t23 = y & q3, x23 = y ^ q3;
+    return 2 * __popcll(t01 & t23) + __popcll((t01 & x23) | (x01 & t23));
+}
+
+// twice the area of the polygon through the boundary pixel centres of the filled set
+__device__ int filled_area2(const u64 fa, const u64 fb, const int lane)
+{
+    const u64 up = shfl_up1(fb, 0, lane);
+    int a = quad_area2(up, fa) + quad_area2(fa, fb);
+    if (lane == 31) a += quad_area2(fb, 0);
+    return __reduce_add_sync(0xffffffffu, a);
+}
+
+// Python float % for a positive modulus
+__device__ __forceinline__ double py_mod_pos(double a, double m)
+{
+    double r = fmod(a, m);
+    if (r != 0.0) {
+        if (r < 0.0) r = __dadd_rn(r, m);
+    } else {
+        r = 0.0;
+    }
+    return r;
+}
+
+// get_angle_by_vector (_utils.py:18-42); NaN = None
+__device__ double angle_by_vector(double x, double y)
+{
+    if (y == 0.0) return x > 0.0 ? 0.25 : x < 0.0 ? 0.75 : __longlong_as_double(0x7ff8000000000000ll);
+    const double at = __ddiv_rn(atan(__ddiv_rn(x, y)), 2 * 3.141592653589793);
+    return py_mod_pos(__dadd_rn(-at, y > 0.0 ? 0.5 : 0.0), 1.0);
+}
+
+__device__ __forceinline__ bool near_momentum(double a, double mom)
+{
+    const double diff = fabs(__dsub_rn(a, mom));
+    const double alt = fabs(__dsub_rn(diff, 1.0));
+    const double dist = alt < diff ? alt : diff;        // Python min()
+    return dist < 0.25;                                 // false for NaN
+}
+
+__device__ __forceinline__ int carry_digit(double r, double lower)
+{
+    const double frac = py_mod_pos(r, 1.0);
+    int v = (int)r + ((frac > 0.55 && lower <= 2.0) ? 1 : 0) - ((frac < 0.45 && lower >= 8.0) ? 1 : 0);
+    v %= 10;
+    return v < 0 ? v + 10 : v;
+}
+
+struct DialOut {
+    double pos;
+    int flag;       // 0 read, 1 no contours, 2 unreadable
+};
+
+}  // namespace
+
+
+__global__ void __launch_bounds__(32 * MELF_MAX_DIALS)
+melf_dials_kernel(const MelfDialsArgs A)
+{
+    __shared__ u64 nm_s[MELF_MAX_DIALS][64];
+    __shared__ DialOut dial_out[MELF_MAX_DIALS];
+
+    const int f = blockIdx.x;
+    const int d = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const u64 key = A.match_key[f];
+    const float max_val = melf_key_score(key);
+    const uint32_t midx = melf_key_index(key);
+    const int mx = (int)(midx % (uint32_t)A.geom.res_w), my = (int)(midx / (uint32_t)A.geom.res_w);
+
+    if ((double)max_val < A.threshold) {                 // _image.py:62-64 (block-uniform)
+        if (threadIdx.x == 0) {
+            melf_result r;
+            r.status = MELF_ST_DIALS_NOT_FOUND;
+            r.match_x = mx; r.match_y = my; r.max_val = max_val;
+            r.failed_dial = -1; r.unreadable_mask = 0;
+            for (int i = 0; i < MELF_MAX_DIALS; i++) r.dial_pos[i] = __longlong_as_double(0x7ff8000000000000ll);
+            r.value = __longlong_as_double(0x7ff8000000000000ll);
+            A.out[f] = r;
+        }
+        return;
+    }
+
+    const MelfDialDev &D = A.dials[d];
+    // pixel (u, v) of the dials rect -> crop column/row -> frame address
+    const uint8_t *frame = A.bgr + (size_t)f * A.frame_stride;
+    const int crop_w = A.geom.crop_w;
+    auto hls_at = [&](int u, int v) -> uint32_t {
+        const int cx = mx + u, cy = my + v;
+        const uint8_t *p = frame + (size_t)(A.geom.crop_y0 + cy) * A.row_stride + 3 * (size_t)(A.geom.crop_x0 + cx);
+        const int B = p[0], G = p[1], R = p[2];
+        return melf_hls_pixel(B, G, R, A.s_tail && melf_is_tail_col(cx, crop_w), A.hue_shift);
+    };
+
+    // ---- get_dial_color: rounded mean of the 5x5 patch at int(centre) -----------------
+    int sh = 0, sl = 0, ss = 0;
+    if (lane < 25) {
+        const uint32_t c = hls_at(D.patch_x + lane % 5, D.patch_y + lane / 5);
+        sh = c & 255; sl = (c >> 8) & 255; ss = (c >> 16) & 255;
+    }
+    sh = __reduce_add_sync(0xffffffffu, sh);
+    sl = __reduce_add_sync(0xffffffffu, sl);
+    ss = __reduce_add_sync(0xffffffffu, ss);
+    // round(sum / 25.0): 25 is odd so there are no ties
+    const int col_h = (2 * sh + 25) / 50, col_l = (2 * sl + 25) / 50, col_s = (2 * ss + 25) / 50;
+    const int lo_h = max(col_h - D.range_h, 0), hi_h = min(col_h + D.range_h, 255);
+    const int lo_l = max(col_l - D.range_l, 0), hi_l = min(col_l + D.range_l, 255);
+    const int lo_s = max(col_s - D.range_s, 0), hi_s = min(col_s + D.range_s, 255);
+
+    // ---- inRange over the window -> row words ----------------------------------------
+    const u64 V = D.colvalid, RV = D.rowvalid;
+    u64 m0a = 0, m0b = 0;
+    for (int rr = 0; rr < D.win_h; ++rr) {
+        u64 word = 0;
+        if ((RV >> rr) & 1) {
+            const int v = D.win_y0 + rr;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int cc = lane + 32 * half;
+                bool bit = false;
+                if (cc < D.win_w && ((V >> cc) & 1)) {
+                    const uint32_t c = hls_at(D.win_x0 + cc, v);
+                    const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
+                    bit = H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+                word |= (u64)bal << (32 * half);
+            }
+        }
+        if ((rr >> 1) == lane) { if (rr & 1) m0b = word; else m0a = word; }
+    }
+
+    // ---- 3x3 dilate then erode (pixels outside the dials rect do not take part) -------
+    const bool rva = (RV >> (2 * lane)) & 1, rvb = (RV >> (2 * lane + 1)) & 1;
+    u64 era, erb;
+    {
+        const u64 ha = h3(m0a), hb = h3(m0b);
+        const u64 hup = shfl_up1(hb, 0, lane), hdn = shfl_down1(ha, 0, lane);
+        const u64 da = rva ? ((hup | ha | hb) & V) : 0;
+        const u64 db = rvb ? ((ha | hb | hdn) & V) : 0;
+        const u64 pa = rva ? e3(da | ~V) : ALL1;
+        const u64 pb = rvb ? e3(db | ~V) : ALL1;
+        const u64 pup = shfl_up1(pb, ALL1, lane), pdn = shfl_down1(pa, ALL1, lane);
+        era = rva ? ((pup & pa & pb) & V) : 0;
+        erb = rvb ? ((pa & pb & pdn) & V) : 0;
+    }
+
+    // ---- components: largest filled area wins, first discovered wins ties -------------
+    u64 rem_a = era & D.disc_nb[2 * lane], rem_b = erb & D.disc_nb[2 * lane + 1];
+    u64 best_a = 0, best_b = 0;
+    int best_area2 = -1, ncomp = 0;
+    for (int guard = 0; guard < 4096; ++guard) {
+        const uint32_t rows = __ballot_sync(0xffffffffu, (rem_a | rem_b) != 0);
+        if (!rows) break;
+        const int l0 = __ffs(rows) - 1;
+        u64 ca = 0, cb = 0;
+        if (lane == l0) {
+            if (rem_a) ca = rem_a & (0 - rem_a); else cb = rem_b & (0 - rem_b);
+        }
+        flood8(ca, cb, rem_a, rem_b, lane);
+        u64 fa, fb;
+        fill_holes(ca, cb, fa, fb, lane);
+        const int a2 = filled_area2(fa, fb, lane);
+        ++ncomp;
+        if (a2 > best_area2) { best_area2 = a2; best_a = fa; best_b = fb; }
+        rem_a &= ~fa; rem_b &= ~fb;
+    }
+
+    DialOut res;
+    res.pos = __longlong_as_double(0x7ff8000000000000ll);
+    res.flag = 0;
+    int n_needle = 0, n_kept = 0;
+    double mom_x = 0.0, mom_y = 0.0, mom_angle = res.pos;
+    u64 nm_a = 0, nm_b = 0;
+
+    if (best_area2 < 0) {
+        res.flag = 1;                                    // _reading.py:137-138
+    } else {
+        // _reading.py:140-148: filled contour if area > 100 else the closed mask itself
+        nm_a = best_area2 > 200 ? best_a : era;
+        nm_b = best_area2 > 200 ? best_b : erb;
+
+        // ---- momentum (_reading.py:32-41): sequential sums in raster order -----------
+        const u64 np_a = nm_a & D.disc[2 * lane], np_b = nm_b & D.disc[2 * lane + 1];
+        n_needle = __reduce_add_sync(0xffffffffu, __popcll(np_a) + __popcll(np_b));
+        uint32_t lanes = __ballot_sync(0xffffffffu, (np_a | np_b) != 0);
+        while (lanes) {
+            const int l = __ffs(lanes) - 1;
+            lanes &= lanes - 1;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                u64 w = shfl_u64(half ? np_b : np_a, l);
+                const double ty = D.termy[2 * l + half];
+                while (w) {
+                    const int c = __ffsll((long long)w) - 1;
+                    w &= w - 1;
+                    mom_x = __dadd_rn(mom_x, D.termx[c]);
+                    mom_y = __dadd_rn(mom_y, ty);
+                }
+            }
+        }
+        const double sgn = D.neg_mom ? -1.0 : 1.0;
+        mom_angle = angle_by_vector(sgn * mom_x, sgn * mom_y);
+
+        // ---- ring pixels (_reading.py:51-96) ------------------------------------------
+        nm_s[d][2 * lane] = nm_a;
+        nm_s[d][2 * lane + 1] = nm_b;
+        __syncwarp();
+        const uint16_t *rpos = A.ring_pos + D.ring_off;
+        const double *rang = A.ring_angle + D.ring_off;
+        const double *rsqd = A.ring_sqd + D.ring_off;
+        double min_angle = 0.0;
+        for (int base = 0; base < D.n_ring; base += 32) {
+            const int e = base + lane;
+            bool kept = false;
+            double a = 0.0;
+            if (e < D.n_ring) {
+                const int pos = rpos[e];
+                a = rang[e];
+                kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, kept);
+            if (n_kept == 0 && bal) min_angle = __shfl_sync(0xffffffffu, a, __ffs(bal) - 1);
+            n_kept += __popc(bal);
+        }
+        if (n_kept == 0) {
+            res.flag = 2;                                // _reading.py:79-81
+        } else {
+            double num = 0.0, den = 0.0;
+            if (n_kept >= 5) {
+                // sorted()[cut:-cut]: the table is already in sorted order; entries that
+                // get "a - 1" come first (their keys are negative), in table order
+                const int cut = min(2, (n_kept - 3) / 2);
+                const int k_lo = cut, k_hi = n_kept - cut;
+                int k = 0;
+                for (int pass = 1; pass >= 0; --pass) {
+                    for (int base = 0; base < D.n_ring; base += 32) {
+                        const int e = base + lane;
+                        bool sel = false;
+                        double a = 0.0, sq = 0.0;
+                        if (e < D.n_ring) {
+                            const int pos = rpos[e];
+                            a = rang[e];
+                            sq = rsqd[e];
+                            const bool kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
+                            const bool wrapped = !(fabs(__dsub_rn(a, min_angle)) < 0.75);
+                            sel = kept && (wrapped == (pass == 1));
+                            if (wrapped) a = __dsub_rn(a, 1.0);
+                        }
+                        uint32_t bal = __ballot_sync(0xffffffffu, sel);
+                        while (bal) {
+                            const int src = __ffs(bal) - 1;
+                            bal &= bal - 1;
+                            if (k >= k_lo && k < k_hi) {
+                                const double aa = __shfl_sync(0xffffffffu, a, src);
+                                const double dd = __shfl_sync(0xffffffffu, sq, src);
+                                num = __dadd_rn(num, __dmul_rn(aa, dd));
+                                den = __dadd_rn(den, dd);
+                            }
+                            ++k;
+                        }
+                    }
+                }
+            } else {
+                // fewer than 5: no sort, the reference sums in raster order of the points
+                double ea[4], ed[4];
+                int ep[4];
+                int k = 0;
+                for (int base = 0; base < D.n_ring; base += 32) {
+                    const int e = base + lane;
+                    bool kept = false;
+                    double a = 0.0, sq = 0.0;
+                    int pos = 0;
+                    if (e < D.n_ring) {
+                        pos = rpos[e];
+                        a = rang[e];
+                        sq = rsqd[e];
+                        kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
+                        if (!(fabs(__dsub_rn(a, min_angle)) < 0.75)) a = __dsub_rn(a, 1.0);
+                    }
+                    uint32_t bal = __ballot_sync(0xffffffffu, kept);
+                    while (bal) {
+                        const int src = __ffs(bal) - 1;
+                        bal &= bal - 1;
+                        const double aa = __shfl_sync(0xffffffffu, a, src);
+                        const double dd = __shfl_sync(0xffffffffu, sq, src);
+                        const int pp = __shfl_sync(0xffffffffu, pos, src);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            if (q == k) { ea[q] = aa; ed[q] = dd; ep[q] = pp; }
+                        ++k;
+                    }
+                }
+                // insertion sort of <= 4 entries by raster position
+#pragma unroll
+                for (int i = 1; i < 4; ++i)
+#pragma unroll
+                    for (int j = i; j > 0; --j)
+                        if (j < n_kept && ep[j] < ep[j - 1]) {
+                            const int tp = ep[j]; ep[j] = ep[j - 1]; ep[j - 1] = tp;
+                            const double ta = ea[j]; ea[j] = ea[j - 1]; ea[j - 1] = ta;
+                            const double td = ed[j]; ed[j] = ed[j - 1]; ed[j - 1] = td;
+                        }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < n_kept) {
+                        num = __dadd_rn(num, __dmul_rn(ea[q], ed[q]));
+                        den = __dadd_rn(den, ed[q]);
+                    }
+            }
+            const double angle = __ddiv_rn(num, den);
+            const double fixed = __dsub_rn(angle, D.aoz_turns);
+            res.pos = py_mod_pos(__dmul_rn(10.0, fixed), 10.0);
+        }
+    }
+
+    // ---- taps --------------------------------------------------------------------------
+    const size_t fd = (size_t)f * A.n_dials + d;
+    if (A.taps.d_mask_orig) { A.taps.d_mask_orig[fd * 64 + 2 * lane] = m0a; A.taps.d_mask_orig[fd * 64 + 2 * lane + 1] = m0b; }
+    if (A.taps.d_mask_de) { A.taps.d_mask_de[fd * 64 + 2 * lane] = era; A.taps.d_mask_de[fd * 64 + 2 * lane + 1] = erb; }
+    if (A.taps.d_needle_mask) { A.taps.d_needle_mask[fd * 64 + 2 * lane] = nm_a; A.taps.d_needle_mask[fd * 64 + 2 * lane + 1] = nm_b; }
+    if (lane == 0) {
+        if (A.taps.d_dial_color) {
+            A.taps.d_dial_color[fd * 3 + 0] = col_h; A.taps.d_dial_color[fd * 3 + 1] = col_l; A.taps.d_dial_color[fd * 3 + 2] = col_s;
+        }
+        if (A.taps.d_counts) {
+            A.taps.d_counts[fd * 4 + 0] = n_needle; A.taps.d_counts[fd * 4 + 1] = n_kept;
+            A.taps.d_counts[fd * 4 + 2] = best_area2; A.taps.d_counts[fd * 4 + 3] = ncomp;
+        }
+        if (A.taps.d_momentum) {
+            A.taps.d_momentum[fd * 3 + 0] = mom_x; A.taps.d_momentum[fd * 3 + 1] = mom_y; A.taps.d_momentum[fd * 3 + 2] = mom_angle;
+        }
+        dial_out[d] = res;
+    }
+    __syncthreads();
+
+    // ---- frame result (_reading.py:98-115, 163-182) -------------------------------------
+    if (threadIdx.x == 0) {
+        const double nan = __longlong_as_double(0x7ff8000000000000ll);
+        melf_result r;
+        r.match_x = mx; r.match_y = my; r.max_val = max_val;
+        r.failed_dial = -1; r.unreadable_mask = 0; r.value = nan;
+        for (int i = 0; i < MELF_MAX_DIALS; i++) r.dial_pos[i] = nan;
+        int first_fail = -1;
+        for (int i = 0; i < A.n_dials; i++)
+            if (dial_out[i].flag == 1) { first_fail = i; break; }
+        const int upto = first_fail >= 0 ? first_fail : A.n_dials;
+        for (int i = 0; i < upto; i++) {
+            if (dial_out[i].flag == 2) r.unreadable_mask |= 1u << i;
+            else r.dial_pos[i] = dial_out[i].pos;
+        }
+        if (first_fail >= 0) {
+            r.status = MELF_ST_NO_CONTOURS;              // raised at the first such dial
+            r.failed_dial = first_fail;
+            r.unreadable_mask = 0;
+        } else if (r.unreadable_mask) {
+            r.status = MELF_ST_ANGLE_UNDETERMINED;
+        } else {
+            r.status = MELF_ST_OK;
+            if (A.n_dials == 4) {
+                const double r4 = r.dial_pos[A.value_order[0]], r3 = r.dial_pos[A.value_order[1]];
+                const double r2 = r.dial_pos[A.value_order[2]], r1 = r.dial_pos[A.value_order[3]];
+                const int d3 = carry_digit(r3, r4);
+                const int d2 = carry_digit(r2, (double)d3);
+                const int d1 = carry_digit(r1, (double)d2);
+                r.value = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(d1, 100.0), __dmul_rn(d2, 10.0)),
+                                              __dmul_rn(d3, 1.0)), __ddiv_rn(r4, 10.0));
+            }
+        }
+        A.out[f] = r;
+    }
+}
+
+// host launcher (called from melf_api.cu)
+cudaError_t melf_launch_dials(const MelfDialsArgs &args, int n_frames, cudaStream_t stream)
+{
+    melf_dials_kernel<<<n_frames, 32 * args.n_dials, 0, stream>>>(args);
+    return cudaGetLastError();
+}

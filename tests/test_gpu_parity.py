@@ -1,0 +1,313 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle.
+
+Bit-exact for everything integer/byte/index: HLS planes, lightness, colour masks, match
+location, per-dial masks and point counts.  The TM_CCOEFF map and max_val are compared
+bit-exact as float32 too (both sides evaluate the same exact integer expression).  Dial
+positions and values are float64 and compared bit-exact as well: both sides add the same
+table values in the same order; the only non-shared operation is one atan per dial for
+the coarse momentum direction (CUDA libm vs glibc), which feeds a < 0.25 comparison and
+never the result itself.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle
+from helpers import (
+    assert_results_equal, format_result_line, golden_set, synthetic_blob_frames,
+    window_words)
+
+pytestmark = pytest.mark.gpu
+
+
+def _torch():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def _dev(arr):
+    return _torch().from_numpy(np.ascontiguousarray(arr)).cuda()
+
+
+# ---------------------------------------------------------------------------------------
+# whole path, sample frames
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize('set_no', [1, 2])
+def test_sample_frames_readings_identical(set_no):
+    """configs[1]: readings of sample-images1/2 on the GPU diffed against the goldens."""
+    gs = golden_set(set_no)
+    (names, crops) = gs.frames()
+    eng = gs.engine(cropped_input=True)
+    got = eng.read_frames(crops)
+    want = oracle.read_batch(gs.oracle_params(), crops, n_threads=8)
+    n_lines = 0
+    for (fn, g, w) in zip(names, got, want):
+        assert_results_equal(g, w, len(gs.names), fn)
+        exp = gs.expected[fn]
+        line = format_result_line(g, gs.names)
+        if exp['status'] == 0:
+            assert line == exp['line'], fn
+            n_lines += 1
+        else:
+            assert line.split(' (match val')[0] == exp['line'].split(' (match val')[0], fn
+            assert abs(float(g['max_val']) - exp['cv2_max_val']) <= 256.0
+    assert n_lines >= 19
+
+
+@pytest.mark.parametrize('set_no', [1, 2])
+def test_full_frames_with_meter_rect(set_no):
+    """Whole 480x640 frames + meter_rect clipping on the device = host-cropped input."""
+    gs = golden_set(set_no)
+    sub = gs.subset()
+    crops = sub['crops'][:12]
+    rng = np.random.default_rng(5)
+    (x0, y0, x1, y1) = gs.meter_rect
+    frames = rng.integers(0, 256, size=(len(crops), 640, 480, 3), dtype=np.uint8)
+    frames[:, y0:y1, x0:x1] = crops
+    got = gs.engine(cropped_input=False).read_frames(frames)
+    want = gs.engine(cropped_input=True).read_frames(crops)
+    for (g, w) in zip(got, want):
+        assert_results_equal(g, w, len(gs.names))
+
+
+def test_device_resident_async_and_taps():
+    torch = _torch()
+    gs = golden_set(1)
+    sub = gs.subset()
+    names = [str(s) for s in sub['names']]
+    tap_names = [str(s) for s in sub['tap_names']]
+    crops = np.stack([sub['crops'][names.index(fn)] for fn in tap_names])
+    (n, h, w) = crops.shape[:3]
+    nd = len(gs.names)
+    from meterelf_b200 import _engine
+    eng = gs.engine(cropped_input=True)
+    d_in = _dev(crops)
+    d_out = torch.zeros((n, _engine.RESULT_DTYPE.itemsize), dtype=torch.uint8, device='cuda')
+    t_m0 = torch.zeros((n, nd, 64), dtype=torch.int64, device='cuda')
+    t_de = torch.zeros_like(t_m0)
+    t_nm = torch.zeros_like(t_m0)
+    t_col = torch.zeros((n, nd, 3), dtype=torch.int32, device='cuda')
+    t_cnt = torch.zeros((n, nd, 4), dtype=torch.int32, device='cuda')
+    t_mom = torch.zeros((n, nd, 3), dtype=torch.float64, device='cuda')
+    taps = _engine.CTaps(t_m0.data_ptr(), t_de.data_ptr(), t_nm.data_ptr(), t_col.data_ptr(),
+                         t_cnt.data_ptr(), t_mom.data_ptr())
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        eng.read_device(d_in.data_ptr(), n, h, w, w * 3, h * w * 3, d_out.data_ptr(),
+                        stream.cuda_stream, taps)
+    stream.synchronize()
+    got = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n)
+    O = gs.oracle_params()
+    m0 = t_m0.cpu().numpy().view(np.uint64)
+    de = t_de.cpu().numpy().view(np.uint64)
+    nm = t_nm.cpu().numpy().view(np.uint64)
+    for i in range(n):
+        (res, ot) = oracle.read_frame(O, crops[i], want_taps=True)
+        assert_results_equal(got[i], res, nd, tap_names[i])
+        assert np.array_equal(t_col[i].cpu().numpy(), ot.dial_color)
+        for d in range(nd):
+            (wx, wy) = eng.dial_window(d)
+            disc = window_words(gs.dials[d]['mask'], wx, wy)
+            # inRange / closing are compared over the whole disc; the needle mask too
+            for (mine, theirs) in ((m0, ot.mask_orig), (de, ot.mask_de), (nm, ot.needle_mask)):
+                ref = window_words(theirs[d], wx, wy)
+                assert np.array_equal(mine[i, d] & disc, ref & disc), (tap_names[i], d)
+            cnt = t_cnt[i, d].cpu().numpy()
+            assert cnt[0] == ot.n_needle_points[d]
+            assert cnt[1] == ot.n_outer_kept[d]
+            assert cnt[2] == int(round(2 * ot.contour_area[d]))
+            mom = t_mom[i, d].cpu().numpy()
+            assert mom[0] == ot.momentum[d, 0] and mom[1] == ot.momentum[d, 1]
+            assert abs(mom[2] - ot.momentum[d, 2]) < 1e-15
+
+
+# ---------------------------------------------------------------------------------------
+# branches the sample images never reach: synthetic blob frames, permissive threshold
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize('set_no,seed', [(2, 0), (2, 1), (1, 2)])
+def test_synthetic_blob_frames_all_branches(set_no, seed):
+    gs = golden_set(set_no)
+    rng = np.random.default_rng(seed)
+    (x0, y0, x1, y1) = gs.meter_rect
+    (h, w) = (y1 - y0, x1 - x0)
+    n = 160 if set_no == 2 else 48
+    frames = synthetic_blob_frames(rng, n, h, w)
+    # a few degenerate ones: flat colour (every TM value 0 -> match at (0,0), all in range)
+    frames[0] = 128
+    frames[1, :, :] = (40, 60, 200)
+    thr = -1e30
+    got = gs.engine(cropped_input=True, threshold=thr).read_frames(frames)
+    want = oracle.read_batch(gs.oracle_params(threshold=thr), frames, n_threads=8)
+    seen = set()
+    for (i, (g, wnt)) in enumerate(zip(got, want)):
+        assert_results_equal(g, wnt, len(gs.names), 'frame %d' % i)
+        seen.add(int(wnt['status']))
+    assert {0, 2, 3} & seen, seen        # the generator must reach the error branches
+
+
+def test_threshold_is_strict_less_than():
+    gs = golden_set(2)
+    crop = gs.subset()['crops'][:1]
+    base = gs.engine(cropped_input=True).read_frames(crop)[0]
+    assert int(base['status']) == 0
+    v = float(base['max_val'])
+    at = gs.engine(cropped_input=True, threshold=v).read_frames(crop)[0]
+    above = gs.engine(cropped_input=True, threshold=float(np.nextafter(np.float32(v), np.float32(np.inf)))).read_frames(crop)[0]
+    assert int(at['status']) == 0              # max_val < threshold is false when equal
+    assert int(above['status']) == 1
+
+
+def test_empty_batch_and_too_small_frame():
+    from meterelf_b200 import _engine
+    gs = golden_set(2)
+    eng = gs.engine(cropped_input=True)
+    assert len(eng.read_frames(np.zeros((0, 135, 220, 3), np.uint8))) == 0
+    with pytest.raises(_engine.EngineError) as exc:
+        eng.read_frames(np.zeros((1, 100, 100, 3), np.uint8))
+    assert exc.value.code == _engine.ERR_TOO_SMALL
+
+
+# ---------------------------------------------------------------------------------------
+# stage operators
+# ---------------------------------------------------------------------------------------
+def test_convert_hls_full_colour_cube_bit_exact():
+    """All 2^24 BGR colours: HLS, lightness plane and a colour mask, vs the oracle."""
+    torch = _torch()
+    from meterelf_b200 import _engine
+    v = np.arange(1 << 24, dtype=np.uint32)
+    cube = np.stack([v & 255, (v >> 8) & 255, v >> 16], axis=-1).astype(np.uint8).reshape(4096, 4096, 3)
+    want = oracle.convert_to_hls(cube, hue_shift=128)
+    lo, hi = (116, 35, 95), (134, 125, 165)
+    d_in = _dev(cube)
+    d_hls = torch.empty((4096, 4096, 3), dtype=torch.uint8, device='cuda')
+    d_l = torch.empty((4096, 4096), dtype=torch.uint8, device='cuda')
+    d_m = torch.empty((4096, 4096), dtype=torch.uint8, device='cuda')
+    _engine.convert_hls_device(0, d_in.data_ptr(), 1, 4096, 4096, 4096 * 3, 4096 * 4096 * 3,
+                               128, True, d_hls.data_ptr(), d_l.data_ptr(), lo, hi, d_m.data_ptr(),
+                               torch.cuda.current_stream().cuda_stream)
+    got = d_hls.cpu().numpy()
+    assert np.array_equal(got, want)
+    assert np.array_equal(d_l.cpu().numpy(), want[..., 1])
+    wm = np.all((want >= np.array(lo, np.uint8)) & (want <= np.array(hi, np.uint8)), axis=-1)
+    assert np.array_equal(d_m.cpu().numpy(), wm.astype(np.uint8) * 255)
+
+
+@pytest.mark.parametrize('shape', [(3, 37, 250), (2, 16, 220), (1, 5, 300), (2, 8, 640), (1, 3, 7)])
+def test_convert_hls_widths_and_tail_columns(shape):
+    torch = _torch()
+    from meterelf_b200 import _engine
+    rng = np.random.default_rng(shape[2])
+    (n, h, w) = shape
+    frames = rng.integers(0, 256, size=(n, h, w, 3), dtype=np.uint8)
+    d_in = _dev(frames)
+    for s_tail in (True, False):
+        d_hls = torch.empty((n, h, w, 3), dtype=torch.uint8, device='cuda')
+        _engine.convert_hls_device(0, d_in.data_ptr(), n, h, w, w * 3, h * w * 3, 7, s_tail,
+                                   d_hls.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
+        got = d_hls.cpu().numpy()
+        for f in range(n):
+            assert np.array_equal(got[f], oracle.convert_to_hls(frames[f], 7, s_tail))
+
+
+@pytest.mark.parametrize('set_no', [1, 2])
+def test_match_template_map_bit_exact(set_no):
+    """TM_CCOEFF map + arg-max on sample crops (BGR input, lightness computed on the fly)."""
+    torch = _torch()
+    gs = golden_set(set_no)
+    crops = gs.subset()['crops'][:6]
+    (n, h, w) = crops.shape[:3]
+    (rh, rw) = (h - gs.tmpl_h + 1, w - gs.tmpl_w + 1)
+    eng = gs.engine(cropped_input=True)
+    d_in = _dev(crops)
+    d_xy = torch.zeros((n, 2), dtype=torch.int32, device='cuda')
+    d_val = torch.zeros((n,), dtype=torch.float32, device='cuda')
+    d_map = torch.zeros((n, rh, rw), dtype=torch.float32, device='cuda')
+    eng.match_template_device(d_in.data_ptr(), 3, n, h, w, w * 3, h * w * 3, False,
+                              d_xy.data_ptr(), d_val.data_ptr(), d_map.data_ptr(),
+                              torch.cuda.current_stream().cuda_stream)
+    got_map = d_map.cpu().numpy()
+    for f in range(n):
+        light = oracle.convert_to_hls(crops[f], gs.hue_shift)[..., 1]
+        (x, y, val, ref_map) = oracle.match_template(np.ascontiguousarray(light), gs.template)
+        assert np.array_equal(got_map[f].view(np.uint32), ref_map.view(np.uint32))
+        assert tuple(d_xy[f].cpu().numpy()) == (x, y)
+        assert np.float32(d_val[f].item()).tobytes() == np.float32(val).tobytes()
+
+
+@pytest.mark.parametrize('h,w', [(119, 188), (120, 189), (130, 260), (200, 330), (480, 640)])
+def test_match_template_gray_sizes_and_ties(h, w):
+    """1-channel input, window-size sweep (configs[4]), constant image -> (0, 0)."""
+    torch = _torch()
+    gs = golden_set(1)
+    rng = np.random.default_rng(h * 1000 + w)
+    imgs = rng.integers(0, 256, size=(3, h, w), dtype=np.uint8)
+    imgs[1] = 77                                      # every score 0 -> first in raster order
+    ty, tx = rng.integers(0, h - gs.tmpl_h + 1), rng.integers(0, w - gs.tmpl_w + 1)
+    imgs[2, ty:ty + gs.tmpl_h, tx:tx + gs.tmpl_w] = gs.template   # planted template
+    eng = gs.engine(cropped_input=True)
+    d_in = _dev(imgs)
+    (rh, rw) = (h - gs.tmpl_h + 1, w - gs.tmpl_w + 1)
+    d_xy = torch.zeros((3, 2), dtype=torch.int32, device='cuda')
+    d_val = torch.zeros((3,), dtype=torch.float32, device='cuda')
+    d_map = torch.zeros((3, rh, rw), dtype=torch.float32, device='cuda')
+    eng.match_template_device(d_in.data_ptr(), 1, 3, h, w, w, h * w, False, d_xy.data_ptr(),
+                              d_val.data_ptr(), d_map.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    got_map = d_map.cpu().numpy()
+    for f in range(3):
+        (x, y, val, ref_map) = oracle.match_template(imgs[f], gs.template)
+        assert np.array_equal(got_map[f].view(np.uint32), ref_map.view(np.uint32)), f
+        assert tuple(d_xy[f].cpu().numpy()) == (x, y), f
+    assert tuple(d_xy[1].cpu().numpy()) == (0, 0) and d_val[1].item() == 0.0
+    assert tuple(d_xy[2].cpu().numpy()) == (tx, ty)
+
+
+# ---------------------------------------------------------------------------------------
+# the Python drop-in layer on top of the C ABI
+# ---------------------------------------------------------------------------------------
+def test_python_api_image_file_and_errors(tmp_path):
+    import cv2
+    import yaml
+    from meterelf_b200 import _params, _reading
+    from meterelf_b200._image import ImageFile
+    from meterelf_b200.exceptions import DialsNotFoundError
+    gs = golden_set(1)
+    cv2.imwrite(str(tmp_path / 'dials.png'), gs.template)
+    needle_data = [dict(
+        name=gs.names[i], color_range=dict(zip('hls', gs.dials[i]['color_range'])),
+        dist_from_center=int(gs.dist_from_center[i]), circle_thickness=int(gs.circle_thickness[i]),
+        angle_of_zero=gs.dials[i]['angle_of_zero'], center=list(gs.dials[i]['center']),
+        diameter=int(gs.diameters[i]), negative_momentum=gs.dials[i]['negative_momentum'])
+        for i in range(4)]
+    (x0, y0, x1, y1) = gs.meter_rect
+    doc = dict(image_glob='*.png', meter_rect=dict(top_left=[x0, y0], bottom_right=[x1, y1]),
+               dials_template='dials.png', dials_template_match_threshold=int(gs.match_threshold),
+               dials_template_size=[gs.tmpl_w, gs.tmpl_h], hue_shift=gs.hue_shift,
+               needle_color=dict(h=125, l=80, s=130), needle_color_range=dict(h=9, l=45, s=35),
+               needle_data=needle_data)
+    (tmp_path / 'params.yml').write_text(yaml.safe_dump(doc))
+    params = _params.load(str(tmp_path / 'params.yml'))
+    sub = gs.subset()
+    names = [str(s) for s in sub['names']]
+    fn = '20180814215230-01-e136.jpg'
+    crop = sub['crops'][names.index(fn)]
+    values = _reading.get_meter_value(ImageFile(fn, params, crop))
+    assert list(values) == gs.names + ['value']
+    assert all(type(v) is float for v in values.values())
+    assert '{:07.3f}'.format(values['value']) == '253.623'       # tests/test_meterelf.py:170-188
+    assert abs(values['value'] - 253.62306) < 0.000005
+    bad = sub['crops'][names.index('20180814021309-01-e01.jpg')]
+    with pytest.raises(DialsNotFoundError) as exc:
+        _reading.get_meter_value(ImageFile('x.jpg', params, bad))
+    assert exc.value.get_message() == 'Dials not found (match val = 0.0)'
+
+    # the CLI on real files (PNG is lossless, so the decoded pixels equal the crops)
+    frame = np.zeros((640, 480, 3), np.uint8)
+    frame[y0:y1, x0:x1] = crop
+    cv2.imwrite(str(tmp_path / 'a.png'), frame)
+    from meterelf_b200 import get_meter_values
+    out = list(get_meter_values(str(tmp_path / 'params.yml'),
+                                [str(tmp_path / 'a.png'), str(tmp_path / 'missing.png')]))
+    assert '{:07.3f}'.format(out[0].value) == '253.623' and out[0].error is None
+    assert out[1].value is None and out[1].error.get_message() == 'Unable to load image'
