@@ -1,6 +1,7 @@
 // C ABI of the dial-reading path (include/meterelf_b200.h): context, batching, launches.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -17,6 +18,12 @@ cudaError_t melf_launch_match(const MelfMatchArgs &args, dim3 grid, cudaStream_t
 cudaError_t melf_launch_match_unpack(const u64 *key, int n, int res_w, int32_t *xy, float *val,
                                      cudaStream_t stream);
 cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStream_t stream);
+bool melf_match_tc_supported(int tmpl_w, int tmpl_h);
+size_t melf_match_tc_toeplitz_bytes(int tmpl_h);
+void melf_match_tc_build_toeplitz(const uint8_t *tmpl, int tmpl_w, int tmpl_h, uint8_t *out);
+long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames);
+cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, long long n_pass, int num_sms,
+                                 cudaStream_t stream);
 
 namespace {
 
@@ -41,6 +48,8 @@ struct melf_ctx {
     double *d_ring_sqd = nullptr;
     uint32_t *d_tmpl_words = nullptr;
     uint32_t *d_ones_words = nullptr;
+    uint8_t *d_toeplitz = nullptr;     // tensor-core path operands (NULL: template not supported there)
+    bool use_tc = false;
     long long sum_t = 0, n_t = 0;
     int tw4p = 0, steps = 0;
     std::vector<int32_t> win_x0, win_y0;
@@ -109,6 +118,51 @@ void fill_match_args(const melf_ctx *ctx, MelfMatchArgs *a)
     a->n_t = ctx->n_t;
 }
 
+// TM_CCOEFF arg-max keys for n frames: tensor-core kernel when the template fits it, else
+// the dp4a kernel (both CUDA, both exact; MELF_MATCH_IMPL=dp4a forces the latter)
+int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
+                  size_t row_stride, size_t frame_stride, const MelfGeom &geom, u64 *d_keys,
+                  float *d_result, cudaStream_t stream)
+{
+    MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
+    if (ctx->use_tc) {
+        MelfMatchTcArgs t{};
+        t.img = d_img;
+        const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride +
+                             (size_t)w * channels;
+        t.img_limit = reinterpret_cast<const uint8_t *>((reinterpret_cast<uintptr_t>(end) + 15) & ~(uintptr_t)15);
+        t.row_stride = row_stride; t.frame_stride = frame_stride;
+        t.channels = channels;
+        t.geom = geom;
+        t.toeplitz = ctx->d_toeplitz;
+        t.tmpl_w = ctx->params.tmpl_w; t.tmpl_h = ctx->params.tmpl_h;
+        t.sum_t = ctx->sum_t; t.n_t = ctx->n_t;
+        t.match_key = d_keys;
+        t.result = d_result;
+        const long long n_pass = melf_match_tc_plan(t, n);
+        MELF_CUDA(ctx, melf_launch_match_tc(t, n_pass, ctx->num_sms, stream));
+        g_launches++;
+        return MELF_OK;
+    }
+    MelfMatchArgs m{};
+    fill_match_args(ctx, &m);
+    m.channels = channels;
+    m.row_stride = row_stride; m.frame_stride = frame_stride;
+    m.geom = geom;
+    // grid.z is limited to 65535 frames per launch
+    for (int f0 = 0; f0 < n; f0 += 65535) {
+        const int nf = n - f0 < 65535 ? n - f0 : 65535;
+        MelfMatchArgs mm = m;
+        mm.img = d_img + (size_t)f0 * frame_stride;
+        mm.match_key = d_keys + f0;
+        mm.result = d_result ? d_result + (size_t)f0 * geom.res_w * geom.res_h : nullptr;
+        const dim3 grid = melf_match_plan(mm, nf);
+        MELF_CUDA(ctx, melf_launch_match(mm, grid, stream));
+        g_launches++;
+    }
+    return MELF_OK;
+}
+
 int ensure_keys(melf_ctx *ctx, int n)
 {
     if (n <= ctx->keys_cap) return MELF_OK;
@@ -120,28 +174,13 @@ int ensure_keys(melf_ctx *ctx, int n)
 }
 
 // locate + read on device-resident frames; keys = per-frame scratch (n entries)
-int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, size_t row_stride, size_t frame_stride,
-             const MelfGeom &geom, u64 *d_keys, melf_result *d_out, const melf_taps *taps,
+int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_w,
+             size_t row_stride, size_t frame_stride, const MelfGeom &geom, u64 *d_keys, melf_result *d_out, const melf_taps *taps,
              cudaStream_t stream)
 {
-    MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
-    MelfMatchArgs m{};
-    fill_match_args(ctx, &m);
-    m.img = d_bgr; m.channels = 3;
-    m.row_stride = row_stride; m.frame_stride = frame_stride;
-    m.geom = geom;
-    m.match_key = d_keys;
-    m.result = nullptr;
-    // grid.z is limited to 65535 frames per launch
-    for (int f0 = 0; f0 < n; f0 += 65535) {
-        const int nf = n - f0 < 65535 ? n - f0 : 65535;
-        MelfMatchArgs mm = m;
-        mm.img = d_bgr + (size_t)f0 * frame_stride;
-        mm.match_key = d_keys + f0;
-        const dim3 grid = melf_match_plan(mm, nf);
-        MELF_CUDA(ctx, melf_launch_match(mm, grid, stream));
-        g_launches++;
-    }
+    int rc = launch_locate(ctx, d_bgr, 3, n, frame_h, frame_w, row_stride, frame_stride, geom, d_keys,
+                           nullptr, stream);
+    if (rc) return rc;
     MelfDialsArgs a{};
     a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
     a.geom = geom;
@@ -166,6 +205,7 @@ void free_ctx(melf_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_ring_angle);
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
+    cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_keys);
     for (int i = 0; i < 2; i++) {
         if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
@@ -270,6 +310,14 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
         MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ones_words, ones.size() * 4));
         MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ones_words, ones.data(), ones.size() * 4, cudaMemcpyHostToDevice));
     }
+    if (melf_match_tc_supported(P->tmpl_w, P->tmpl_h)) {
+        std::vector<uint8_t> toep(melf_match_tc_toeplitz_bytes(P->tmpl_h));
+        melf_match_tc_build_toeplitz(P->tmpl, P->tmpl_w, P->tmpl_h, toep.data());
+        MELF_CREATE_CUDA(cudaMalloc(&ctx->d_toeplitz, toep.size()));
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_toeplitz, toep.data(), toep.size(), cudaMemcpyHostToDevice));
+        const char *impl = std::getenv("MELF_MATCH_IMPL");
+        ctx->use_tc = !(impl && std::strcmp(impl, "dp4a") == 0);
+    }
     MELF_CREATE_CUDA(cudaMalloc(&ctx->d_dials, dials.size() * sizeof(MelfDialDev)));
     MELF_CREATE_CUDA(cudaMemcpy(ctx->d_dials, dials.data(), dials.size() * sizeof(MelfDialDev), cudaMemcpyHostToDevice));
     const size_t nr = rings.pos.size() ? rings.pos.size() : 1;
@@ -310,7 +358,7 @@ int melf_read_batch_async(melf_ctx *ctx, const uint8_t *d_bgr, int n, int h, int
     if (rc) return rc;
     rc = ensure_keys(ctx, n);
     if (rc) return rc;
-    return run_path(ctx, d_bgr, n, row_stride, frame_stride, geom, ctx->d_keys, d_out, taps,
+    return run_path(ctx, d_bgr, n, h, w, row_stride, frame_stride, geom, ctx->d_keys, d_out, taps,
                     (cudaStream_t)stream);
 }
 
@@ -384,8 +432,8 @@ int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
                                                  cudaMemcpyHostToDevice, st));
             }
         }
-        rc = run_path(ctx, ctx->d_chunk[b], nf, pitch, frame_bytes, cg, ctx->d_chunk_keys[b],
-                      ctx->d_res[b], nullptr, st);
+        rc = run_path(ctx, ctx->d_chunk[b], nf, geom.crop_h, geom.crop_w, pitch, frame_bytes, cg,
+                      ctx->d_chunk_keys[b], ctx->d_res[b], nullptr, st);
         if (rc) return rc;
         MELF_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + (size_t)b * kChunkFrames, ctx->d_res[b],
                                        sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
@@ -435,7 +483,6 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
         !d_max_xy || !d_max_val || row_stride < (size_t)w * channels)
         return fail(ctx, MELF_ERR_INVALID, "bad melf_match_template arguments");
     if (n == 0) return MELF_OK;
-    if (n > 65535) return fail(ctx, MELF_ERR_UNSUPPORTED, "more than 65535 frames per call");
     MELF_CUDA(ctx, cudaSetDevice(ctx->device));
     MelfGeom geom;
     int rc = make_geom(ctx, h, w, use_rect != 0, &geom);
@@ -443,17 +490,9 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
     rc = ensure_keys(ctx, n);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    MELF_CUDA(ctx, cudaMemsetAsync(ctx->d_keys, 0, (size_t)n * sizeof(u64), st));
-    MelfMatchArgs m{};
-    fill_match_args(ctx, &m);
-    m.img = d_img; m.channels = channels;
-    m.row_stride = row_stride; m.frame_stride = frame_stride;
-    m.geom = geom;
-    m.match_key = ctx->d_keys;
-    m.result = d_result;
-    const dim3 grid = melf_match_plan(m, n);
-    MELF_CUDA(ctx, melf_launch_match(m, grid, st));
-    g_launches++;
+    rc = launch_locate(ctx, d_img, channels, n, h, w, row_stride, frame_stride, geom, ctx->d_keys,
+                       d_result, st);
+    if (rc) return rc;
     MELF_CUDA(ctx, melf_launch_match_unpack(ctx->d_keys, n, geom.res_w, d_max_xy, d_max_val, st));
     g_launches++;
     return MELF_OK;

@@ -36,6 +36,23 @@ struct MelfMatchArgs {
     float *result;               // optional [n][res_h][res_w]
 };
 
+// tensor-core TM_CCOEFF (melf_match_tc.cu)
+struct MelfMatchTcArgs {
+    const uint8_t *img;          // BGR (channels = 3) or single channel frames
+    const uint8_t *img_limit;    // 16-byte aligned end of the readable image memory
+    size_t row_stride, frame_stride;
+    int32_t channels;
+    MelfGeom geom;
+    const uint8_t *toeplitz;     // [n_pairs][16 strips][128][16 B] Toeplitz operands of the template
+    int32_t tmpl_w, tmpl_h, n_pairs;
+    int32_t n_tx, n_ty, chunk_h; // work items per frame: 64-column tiles x row chunks
+    long long n_items;
+    long long sum_t, n_t;
+    u64 *match_key;              // [n] atomicMax slot per frame (zeroed before launch)
+    float *result;               // optional [n][res_h][res_w]
+    uint32_t ones_words[64];     // byte j = 1 for j < tmpl_w
+};
+
 struct MelfConvertArgs {
     const uint8_t *bgr;
     size_t row_stride, frame_stride;

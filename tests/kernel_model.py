@@ -190,3 +190,52 @@ def read_dial(T, m0, neg_mom, aoz_turns):
     out['pos'] = py_mod(10.0 * (angle - aoz_turns), 10.0)
     out['status'] = 'ok'
     return out
+
+
+# ---------------------------------------------------------------------------------------
+# Model of the tensor-core TM_CCOEFF kernel (csrc/melf_match_tc.cu): the same shared-memory
+# byte layouts (16-byte column strips), the same per-step operand addressing (a row shift
+# of the lightness slab = a 16-byte step of the descriptor start address), the same
+# Toeplitz operand image (built by the product library's host code), the same M-tile
+# offsets and D_0[y] + D_1[y+1] epilogue.  numpy int64 stands in for tcgen05.mma.
+# ---------------------------------------------------------------------------------------
+def match_tc_model(light, toeplitz, tmpl_w, tmpl_h, plan):
+    """light: (crop_h, crop_w) u8; toeplitz: bytes from melf_host_match_tc_toeplitz;
+    plan = (n_tx, n_ty, chunk_h, n_pairs).  Returns sum T*L for every result position."""
+    import numpy as np
+    (n_tx, n_ty, chunk_h, n_pairs) = plan
+    (crop_h, crop_w) = light.shape
+    (res_h, res_w) = (crop_h - tmpl_h + 1, crop_w - tmpl_w + 1)
+    toep = np.frombuffer(toeplitz, np.uint8).reshape(n_pairs, 16, 128, 16).astype(np.int64)
+    out = np.full((res_h, res_w), -1, np.int64)
+    for ty in range(n_ty):
+        for tx in range(n_tx):
+            (x0, y0) = (tx * 64, ty * chunk_h)
+            (w_c, h_c) = (min(64, res_w - x0), min(chunk_h, res_h - y0))
+            assert 1 <= h_c <= 137 and h_c + tmpl_h - 1 <= 255
+            # slab[strip][row][16]: zero outside the crop
+            slab = np.zeros((16, 256, 16), np.int64)
+            for s in range(16):
+                for b in range(16):
+                    cx = x0 + 16 * s + b
+                    if cx < crop_w:
+                        rows = min(256, crop_h - y0)
+                        slab[s, :rows, b] = light[y0:y0 + rows, cx]
+            tiles = [(0, 0)] + ([(1, h_c - 127)] if h_c > 127 else [])
+            for (mt, off) in tiles:
+                acc = np.zeros((128, 128), np.int64)
+                for p in range(n_pairs):
+                    row0 = off + 2 * p
+                    assert row0 + 127 <= 255
+                    for ks in range(8):
+                        # A[m][k] = slab[2ks + k // 16][row0 + m][k % 16], k < 32
+                        a = np.concatenate([slab[2 * ks, row0:row0 + 128], slab[2 * ks + 1, row0:row0 + 128]], axis=1)
+                        b = np.concatenate([toep[p, 2 * ks], toep[p, 2 * ks + 1]], axis=1)    # [n][k]
+                        acc += a @ b.T
+                for t in range(127):
+                    yl = off + t
+                    if yl >= h_c or (mt == 1 and yl < 127):
+                        continue
+                    out[y0 + yl, x0:x0 + w_c] = acc[t, :w_c] + acc[t + 1, 64:64 + w_c]
+    assert (out >= 0).all()
+    return out
