@@ -13,7 +13,7 @@ from typing import List
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
-OUT_DIR = os.path.join(HERE, '_lib')
+OUT_DIR = os.environ.get('MELF_OUT_DIR') or os.path.join(HERE, '_lib')
 LIB = os.path.join(OUT_DIR, 'libmeterelf_b200.so')
 
 SOURCES = ['melf_api.cu', 'melf_match.cu', 'melf_match_tc.cu', 'melf_dials.cu', 'melf_convert.cu', 'melf_host.cpp']
@@ -49,7 +49,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         obj = os.path.join(OUT_DIR, os.path.splitext(src)[0] + '.o')
         objs.append(obj)
         if force or _stale(obj, [path] + headers):
-            jobs.append([nvcc] + NVCC_FLAGS + ['-c', path, '-o', obj])
+            jobs.append([nvcc] + NVCC_FLAGS + os.environ.get('MELF_EXTRA_NVCC_FLAGS', '').split() +
+                        ['-c', path, '-o', obj])
 
     def run(cmd):
         res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

@@ -62,4 +62,17 @@ struct MelfConvertArgs {
     uint8_t *light;    // [n][h][w]    or NULL
     uint8_t *mask;     // [n][h][w]    or NULL
     uint32_t lo, hi;   // packed H | L<<8 | S<<16 bounds (inclusive)
+    // exact 32-bit division by multiplication (Granlund-Montgomery) for the flat index
+    uint32_t gdiv[3];  // by w / 16: multiplier, shift 1, shift 2
+    uint32_t hdiv[3];  // by h
 };
+
+__host__ __device__ __forceinline__ uint32_t melf_fastdiv(uint32_t n, const uint32_t (&d)[3])
+{
+#ifdef __CUDA_ARCH__
+    const uint32_t t = __umulhi(d[0], n);
+#else
+    const uint32_t t = (uint32_t)(((unsigned long long)d[0] * n) >> 32);
+#endif
+    return (t + ((n - t) >> d[1])) >> d[2];
+}

@@ -14,6 +14,10 @@
 #include "melf_args.h"
 
 
+#ifndef MELF_CONVERT_MIN_BLOCKS
+#define MELF_CONVERT_MIN_BLOCKS 4      // occupancy 4..6 measured within 1 % of each other (issue-bound)
+#endif
+
 namespace {
 
 __device__ __forceinline__ uint32_t in_range255(uint32_t c, uint32_t lo, uint32_t hi)
@@ -37,19 +41,55 @@ __device__ __forceinline__ void stg_stream(uint4 *p, const uint4 v)
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// bytes 0 / 1 = the sign bit of a / b replicated over the byte (PRMT sign mode: selector
+// nibble 8 + k); written as PTX because __byte_perm documents only 3 selector bits
+__device__ __forceinline__ uint32_t prmt_sign(uint32_t a, uint32_t b)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, 0x00FB;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+
 }  // namespace
 
-__global__ void __launch_bounds__(256)
+// Vector kernel: 16 pixels (three 128-bit loads) per thread per iteration, grid-stride.
+// Width is a multiple of 16 here, so no OpenCV scalar-tail column exists (tails are the
+// last w mod 8 columns of a 256-pixel block) and melf_hls_fast applies.
+// Mask test in the float pipe: the channel values are integer-valued floats M + v
+// (M = 1.5 * 2^23), so a = v - lo and b = v - hi are exact packed subtractions and
+// e = a * b - 0.5 is exact, never zero, and negative exactly for lo <= v <= hi.  The three
+// sign bits are ANDed by one LOP3 and turned into the mask byte by PRMT's sign-replicate
+// mode.  The hue shift is folded into the H bounds (a <= H <= b modulo 256); when that
+// interval wraps, the complementary interval is tested with the sign reversed
+// (e = -a * b + 0.5).
+template <bool HLS, bool LIGHT, bool MASK>
+__global__ void __launch_bounds__(256, MELF_CONVERT_MIN_BLOCKS)
 melf_convert_vec_kernel(const MelfConvertArgs A)
 {
-    const int groups_per_row = A.w >> 4;
-    const long long total = (long long)A.n * A.h * groups_per_row;
-    for (long long gidx = (long long)blockIdx.x * blockDim.x + threadIdx.x; gidx < total;
-         gidx += (long long)gridDim.x * blockDim.x) {
-        const int g = (int)(gidx % groups_per_row);
-        const long long rowi = gidx / groups_per_row;
-        const int y = (int)(rowi % A.h);
-        const int f = (int)(rowi / A.h);
+    const uint32_t groups_per_row = (uint32_t)A.w >> 4;
+    const uint32_t total = (uint32_t)A.n * (uint32_t)A.h * groups_per_row;     // < 2^32 (launcher)
+    const float M = MELF_MAGIC_RINT;
+    const int l0 = (A.lo >> 8) & 255, l1 = (A.hi >> 8) & 255, s0 = (A.lo >> 16) & 255, s1 = (A.hi >> 16) & 255;
+    // H' = (H + shift) mod 256 in [lo, hi]  <=>  H in [a, b] mod 256
+    const int ha = (int)((A.lo & 255) - (uint32_t)A.hue_shift) & 255;
+    const int hb = (int)((A.hi & 255) - (uint32_t)A.hue_shift) & 255;
+    const bool wrap = ha > hb;
+    const bool full = wrap && ha == hb + 1;                           // complement empty: every H passes
+    const int h0 = wrap ? hb + 1 : ha, h1 = wrap ? ha - 1 : hb;
+    const float2 neg1 = melf_f2(-1.f);
+    const float2 la_c = melf_f2(M + (float)l0), lb_c = melf_f2(M + (float)l1);
+    const float2 sa_c = melf_f2(M + (float)s0), sb_c = melf_f2(M + (float)s1);
+    // a_h = +-(V - (M + h0)) as one fma: V * hs - hs * (M + h0)
+    const float hs = (wrap && !full) ? -1.f : 1.f;
+    const float2 hs2 = melf_f2(hs), ha_c = melf_f2(-hs * (M + (float)h0)), hb_c = melf_f2(M + (float)h1);
+    const float2 half_neg = melf_f2(-0.5f);
+    const float2 eh_c = melf_f2(full ? -1e9f : (wrap ? 0.5f : -0.5f));
+    for (uint32_t gidx = blockIdx.x * blockDim.x + threadIdx.x; gidx < total;
+         gidx += gridDim.x * blockDim.x) {
+        const uint32_t rowi = melf_fastdiv(gidx, A.gdiv);
+        const uint32_t g = gidx - rowi * groups_per_row;
+        const uint32_t f = melf_fastdiv(rowi, A.hdiv);
+        const uint32_t y = rowi - f * (uint32_t)A.h;
         const uint4 *src = reinterpret_cast<const uint4 *>(
             A.bgr + (size_t)f * A.frame_stride + (size_t)y * A.row_stride) + 3 * g;
         uint32_t in[12];
@@ -61,34 +101,54 @@ melf_convert_vec_kernel(const MelfConvertArgs A)
         }
         uint32_t out[12], lw[4], mw[4];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) out[i] = 0;
+        for (int q = 0; q < 4; ++q) {
+            uint32_t c[4];                       // per pixel: H | L << 8 | S << 16
+            uint32_t lb[4], ob[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) { lw[q] = 0; mw[q] = 0; }
-        const int x0 = g << 4;
-#pragma unroll
-        for (int p = 0; p < 16; ++p) {
-            // bytes 3p, 3p+1, 3p+2 of the 48-byte group
-            const int b0 = 3 * p, b1 = 3 * p + 1, b2 = 3 * p + 2;
-            const int B = (in[b0 >> 2] >> (8 * (b0 & 3))) & 255;
-            const int G = (in[b1 >> 2] >> (8 * (b1 & 3))) & 255;
-            const int R = (in[b2 >> 2] >> (8 * (b2 & 3))) & 255;
-            const bool tail = A.s_tail && melf_is_tail_col(x0 + p, A.w);
-            const uint32_t c = melf_hls_pixel(B, G, R, tail, A.hue_shift);
-            out[b0 >> 2] |= (c & 255) << (8 * (b0 & 3));
-            out[b1 >> 2] |= ((c >> 8) & 255) << (8 * (b1 & 3));
-            out[b2 >> 2] |= ((c >> 16) & 255) << (8 * (b2 & 3));
-            lw[p >> 2] |= ((c >> 8) & 255) << (8 * (p & 3));
-            mw[p >> 2] |= in_range255(c, A.lo, A.hi) << (8 * (p & 3));
+            for (int pr = 0; pr < 2; ++pr) {     // two pixels per pass through the packed pipe
+                const int b0 = 3 * (4 * q + 2 * pr), b1 = b0 + 3;
+                float2 Hf, Lf, Sf;
+                melf_hls_fast2(
+                    make_float2(melf_byte_biased(in[b0 >> 2], b0 & 3), melf_byte_biased(in[b1 >> 2], b1 & 3)),
+                    make_float2(melf_byte_biased(in[(b0 + 1) >> 2], (b0 + 1) & 3),
+                                melf_byte_biased(in[(b1 + 1) >> 2], (b1 + 1) & 3)),
+                    make_float2(melf_byte_biased(in[(b0 + 2) >> 2], (b0 + 2) & 3),
+                                melf_byte_biased(in[(b1 + 2) >> 2], (b1 + 2) & 3)), Hf, Lf, Sf);
+                const int i = 2 * pr;
+                lb[i] = __float_as_uint(Lf.x); lb[i + 1] = __float_as_uint(Lf.y);
+                if (HLS) {
+                    const uint32_t h0 = __float_as_uint(Hf.x) + (uint32_t)A.hue_shift,
+                                   h1 = __float_as_uint(Hf.y) + (uint32_t)A.hue_shift;
+                    c[i] = __byte_perm(__byte_perm(h0, lb[i], 0x0040), __float_as_uint(Sf.x), 0x0410);
+                    c[i + 1] = __byte_perm(__byte_perm(h1, lb[i + 1], 0x0040), __float_as_uint(Sf.y), 0x0410);
+                }
+                if (MASK) {
+                    const float2 eh = melf_fma2(melf_fma2(Hf, hs2, ha_c), melf_fma2(hb_c, neg1, Hf), eh_c);
+                    const float2 el = melf_fma2(melf_fma2(la_c, neg1, Lf), melf_fma2(lb_c, neg1, Lf), half_neg);
+                    const float2 es = melf_fma2(melf_fma2(sa_c, neg1, Sf), melf_fma2(sb_c, neg1, Sf), half_neg);
+                    ob[i] = __float_as_uint(eh.x) & __float_as_uint(el.x) & __float_as_uint(es.x);
+                    ob[i + 1] = __float_as_uint(eh.y) & __float_as_uint(el.y) & __float_as_uint(es.y);
+                }
+            }
+            if (MASK)       // byte i = 0xFF where the sign of ob[i] is set
+                mw[q] = __byte_perm(prmt_sign(ob[0], ob[1]), prmt_sign(ob[2], ob[3]), 0x5410);
+            if (HLS) {
+                out[3 * q] = __byte_perm(c[0], c[1], 0x4210);
+                out[3 * q + 1] = __byte_perm(c[1], c[2], 0x5421);
+                out[3 * q + 2] = __byte_perm(c[2], c[3], 0x6542);
+            }
+            if (LIGHT)
+                lw[q] = __byte_perm(__byte_perm(lb[0], lb[1], 0x0040), __byte_perm(lb[2], lb[3], 0x0040), 0x5410);
         }
-        const size_t px = ((size_t)f * A.h + y) * A.w + x0;
-        if (A.hls) {
+        const size_t px = (size_t)gidx << 4;        // == ((f * h + y) * w + 16 g): outputs are dense
+        if (HLS) {
             uint4 *dst = reinterpret_cast<uint4 *>(A.hls + px * 3);
             stg_stream(dst, make_uint4(out[0], out[1], out[2], out[3]));
             stg_stream(dst + 1, make_uint4(out[4], out[5], out[6], out[7]));
             stg_stream(dst + 2, make_uint4(out[8], out[9], out[10], out[11]));
         }
-        if (A.light) stg_stream(reinterpret_cast<uint4 *>(A.light + px), make_uint4(lw[0], lw[1], lw[2], lw[3]));
-        if (A.mask) stg_stream(reinterpret_cast<uint4 *>(A.mask + px), make_uint4(mw[0], mw[1], mw[2], mw[3]));
+        if (LIGHT) stg_stream(reinterpret_cast<uint4 *>(A.light + px), make_uint4(lw[0], lw[1], lw[2], lw[3]));
+        if (MASK) stg_stream(reinterpret_cast<uint4 *>(A.mask + px), make_uint4(mw[0], mw[1], mw[2], mw[3]));
     }
 }
 
@@ -113,8 +173,37 @@ melf_convert_scalar_kernel(const MelfConvertArgs A)
     }
 }
 
-cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStream_t stream)
+static void make_fastdiv(uint32_t d, uint32_t (&out)[3])
 {
+    uint32_t l = 0;
+    while ((1ull << l) < d) ++l;
+    out[0] = (uint32_t)(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+    out[1] = l < 1 ? l : 1;
+    out[2] = l > 0 ? l - 1 : 0;
+}
+
+cudaError_t melf_launch_convert(const MelfConvertArgs &a_in, int num_sms, cudaStream_t stream)
+{
+    MelfConvertArgs a = a_in;
+    make_fastdiv((uint32_t)(a.w / 16 > 0 ? a.w / 16 : 1), a.gdiv);
+    make_fastdiv((uint32_t)a.h, a.hdiv);
+    // the vector kernel indexes 16-pixel groups with 32 bits: split very large batches
+    const long long per_frame = (long long)a.h * (a.w / 16 > 0 ? a.w / 16 : 1);
+    const long long max_frames = ((1ll << 31) / per_frame) > 0 ? ((1ll << 31) / per_frame) : 1;
+    if (a.n > max_frames) {
+        for (long long f0 = 0; f0 < a.n; f0 += max_frames) {
+            MelfConvertArgs part = a_in;
+            part.n = (int32_t)((a.n - f0) < max_frames ? (a.n - f0) : max_frames);
+            part.bgr = a.bgr + (size_t)f0 * a.frame_stride;
+            const size_t px0 = (size_t)f0 * a.h * a.w;
+            if (part.hls) part.hls += px0 * 3;
+            if (part.light) part.light += px0;
+            if (part.mask) part.mask += px0;
+            cudaError_t e = melf_launch_convert(part, num_sms, stream);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
     auto aligned16 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool vec = (a.w % 16 == 0) && aligned16(a.bgr) && (a.row_stride % 16 == 0) &&
                      (a.frame_stride % 16 == 0) && aligned16(a.hls) && aligned16(a.light) &&
@@ -122,10 +211,33 @@ cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStrea
     if (vec) {
         const long long total = (long long)a.n * a.h * (a.w / 16);
         long long blocks = (total + 255) / 256;
-        const long long cap = (long long)num_sms * 8;         // 8 resident CTAs of 256 per SM
+        const long long cap = (long long)num_sms * 8;         // measured best: ~2 waves of resident CTAs, grid-stride
         if (blocks > cap) blocks = cap;
         if (blocks < 1) blocks = 1;
-        melf_convert_vec_kernel<<<(unsigned)blocks, 256, 0, stream>>>(a);
+        MelfConvertArgs b = a;
+        // an empty range on any channel (lo > hi) selects nothing, like cv2.inRange
+        const bool empty = (b.lo & 255) > (b.hi & 255) || ((b.lo >> 8) & 255) > ((b.hi >> 8) & 255) ||
+                           ((b.lo >> 16) & 255) > ((b.hi >> 16) & 255);
+        if (empty) { b.lo = 0x000001; b.hi = 0x000000; }
+        const unsigned gb = (unsigned)blocks;
+        const int sel = (b.hls ? 4 : 0) | (b.light ? 2 : 0) | (b.mask ? 1 : 0);
+        if (empty && b.mask) {
+            // handled by the kernel's unsigned compare only for non-empty ranges
+            cudaError_t e = cudaMemsetAsync(b.mask, 0, (size_t)b.n * b.h * b.w, stream);
+            if (e != cudaSuccess) return e;
+            b.mask = nullptr;
+        }
+        switch ((b.hls ? 4 : 0) | (b.light ? 2 : 0) | (b.mask ? 1 : 0)) {
+        case 7: melf_convert_vec_kernel<true, true, true><<<gb, 256, 0, stream>>>(b); break;
+        case 6: melf_convert_vec_kernel<true, true, false><<<gb, 256, 0, stream>>>(b); break;
+        case 5: melf_convert_vec_kernel<true, false, true><<<gb, 256, 0, stream>>>(b); break;
+        case 4: melf_convert_vec_kernel<true, false, false><<<gb, 256, 0, stream>>>(b); break;
+        case 3: melf_convert_vec_kernel<false, true, true><<<gb, 256, 0, stream>>>(b); break;
+        case 2: melf_convert_vec_kernel<false, true, false><<<gb, 256, 0, stream>>>(b); break;
+        case 1: melf_convert_vec_kernel<false, false, true><<<gb, 256, 0, stream>>>(b); break;
+        default: break;
+        }
+        (void)sel;
     } else {
         const long long total = (long long)a.n * a.h * a.w;
         long long blocks = (total + 255) / 256;

@@ -311,3 +311,31 @@ def test_python_api_image_file_and_errors(tmp_path):
                                 [str(tmp_path / 'a.png'), str(tmp_path / 'missing.png')]))
     assert '{:07.3f}'.format(out[0].value) == '253.623' and out[0].error is None
     assert out[1].value is None and out[1].error.get_message() == 'Unable to load image'
+
+
+@pytest.mark.parametrize('hue_shift,lo,hi', [
+    (0, (10, 20, 30), (200, 220, 250)),        # plain interval on every channel
+    (128, (116, 35, 95), (134, 125, 165)),     # H interval wraps after removing the shift
+    (77, (0, 0, 0), (255, 255, 255)),          # everything
+    (200, (30, 0, 0), (29, 255, 255)),         # lo > hi on H: cv2.inRange selects nothing
+    (5, (100, 50, 60), (100, 50, 255)),        # single values
+    (250, (3, 0, 17), (9, 255, 17)),
+])
+def test_convert_mask_ranges_bit_exact(hue_shift, lo, hi):
+    """Fused inRange of the vector kernel (sign-bit formulation) against numpy on the oracle's HLS."""
+    torch = _torch()
+    from meterelf_b200 import _engine
+    rng = np.random.default_rng(hue_shift)
+    frames = rng.integers(0, 256, size=(2, 24, 64, 3), dtype=np.uint8)
+    frames[0, :8] = rng.integers(0, 256, size=(8, 64, 1), dtype=np.uint8)        # greys: diff == 0
+    d_in = _dev(frames)
+    d_m = torch.full((2, 24, 64), 7, dtype=torch.uint8, device='cuda')
+    d_l = torch.empty((2, 24, 64), dtype=torch.uint8, device='cuda')
+    _engine.convert_hls_device(0, d_in.data_ptr(), 2, 24, 64, 64 * 3, 24 * 64 * 3, hue_shift, True,
+                               0, d_l.data_ptr(), lo, hi, d_m.data_ptr(),
+                               torch.cuda.current_stream().cuda_stream)
+    for f in range(2):
+        want = oracle.convert_to_hls(frames[f], hue_shift)
+        wm = np.all((want >= np.array(lo, np.uint8)) & (want <= np.array(hi, np.uint8)), axis=-1)
+        assert np.array_equal(d_m[f].cpu().numpy(), wm.astype(np.uint8) * 255)
+        assert np.array_equal(d_l[f].cpu().numpy(), want[..., 1])
