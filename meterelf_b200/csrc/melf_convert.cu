@@ -10,6 +10,10 @@
 // 128-bit lightness store and one 128-bit mask store; consecutive threads own
 // consecutive 48-byte groups so every warp request is fully coalesced.  The scalar path
 // (one pixel per thread) covers unaligned rows / widths that are not a multiple of 16.
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
 #include "melf_common.cuh"
 #include "melf_args.h"
 
@@ -152,6 +156,163 @@ melf_convert_vec_kernel(const MelfConvertArgs A)
     }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Table kernel (the large-batch path).  ncu on the arithmetic kernel above
+// (profiles/r01_v3_ncu_convert_fma.txt) shows it bound by instruction issue, the half-rate ALU
+// pipe and the packed-FMA pipe both ~58 % busy, DRAM at 35 %.  Two observations cut the
+// arithmetic by more than half without changing a single output byte:
+//  * L and S depend only on (max, min) of the three channel bytes: 2^16 pairs.  A static
+//    table built once per device with the exact cv2-order scalar code (melf_hls_pixel) holds
+//    them; each CTA stages it in shared memory as int16 entries L | inrange(L, S) << 15, so
+//    one sign-extending 16-bit shared load yields the lightness byte AND the L/S part of the
+//    colour-range test (the sign bit, ANDed with the hue test's sign bit).
+//  * H = rint(256/360 * hue) is the round-to-nearest of the exact rational
+//    256 * N / (3 * D), D = max - min <= 255.  Its fractional part is a multiple of 1/(3 D)
+//    and can never be 1/2 (that would need 2^9 | 3 D (2m + 1)), so it stays at least
+//    1/(6 D) >= 6.5e-4 away from a rounding tie, while cv2's float32 evaluation is within
+//    ~1.3e-3 / D of the exact value and the float32 evaluation of
+//    t * (1 / D) * (128 / 3) + sector offset used here within ~1e-4.  Hence the short form below gives cv2's byte for every colour; this is
+//    CHECKED, not assumed: test_convert_hls_full_colour_cube_bit_exact runs all 2^24 colours
+//    through this kernel against the oracle.
+// One CTA of 1024 threads per SM (128 KB table, + 64 KB S table when HLS is written).
+// ---------------------------------------------------------------------------------------
+constexpr int TAB_THREADS = 1024;
+constexpr int TAB_SMEM_LS = 65536 * 2;
+constexpr int TAB_SMEM_S = 65536;
+
+__global__ void melf_convert_build_table_kernel(uint16_t *ls)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;      // imax << 8 | imin
+    const int imax = idx >> 8, imin = idx & 255;
+    uint32_t v = 0;
+    if (imin <= imax) {
+        const uint32_t c = melf_hls_pixel(imin, imin, imax, false, 0);
+        v = ((c >> 8) & 255u) | (((c >> 16) & 255u) << 8);
+    }
+    ls[idx] = (uint16_t)v;
+}
+
+extern __shared__ __align__(16) uint8_t melf_conv_smem[];
+
+template <bool HLS, bool LIGHT, bool MASK>
+__global__ void __launch_bounds__(TAB_THREADS, 1)
+melf_convert_tab_kernel(const MelfConvertArgs A, const uint16_t *__restrict__ ls_table)
+{
+    int16_t *tab = reinterpret_cast<int16_t *>(melf_conv_smem);
+    uint8_t *tab_s = melf_conv_smem + TAB_SMEM_LS;
+    const int l0 = (A.lo >> 8) & 255, l1 = (A.hi >> 8) & 255, s0 = (A.lo >> 16) & 255, s1 = (A.hi >> 16) & 255;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(ls_table);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
+        for (int i = threadIdx.x; i < 32768; i += TAB_THREADS) {
+            const uint32_t two = __ldg(src + i);
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int L = (two >> (16 * k)) & 255, S = (two >> (16 * k + 8)) & 255;
+                const bool in = L >= l0 && L <= l1 && S >= s0 && S <= s1;
+                out |= ((uint32_t)L | (in ? 0x8000u : 0u)) << (16 * k);
+                if (HLS) tab_s[2 * i + k] = (uint8_t)S;
+            }
+            dst[i] = out;
+        }
+    }
+    __syncthreads();
+
+    const uint32_t groups_per_row = (uint32_t)A.w >> 4;
+    const uint32_t total = (uint32_t)A.n * (uint32_t)A.h * groups_per_row;     // < 2^32 (launcher)
+    const float M = MELF_MAGIC_RINT;
+    // H' = (H + shift) mod 256 in [lo, hi]  <=>  H in [a, b] mod 256 (see the kernel above)
+    const int ha = (int)((A.lo & 255) - (uint32_t)A.hue_shift) & 255;
+    const int hb = (int)((A.hi & 255) - (uint32_t)A.hue_shift) & 255;
+    const bool wrap = ha > hb;
+    const bool full = wrap && ha == hb + 1;
+    const int h0 = wrap ? hb + 1 : ha, h1 = wrap ? ha - 1 : hb;
+    const float2 neg1 = melf_f2(-1.f);
+    const float hs = (wrap && !full) ? -1.f : 1.f;
+    const float2 hs2 = melf_f2(hs), ha_c = melf_f2(-hs * (M + (float)h0)), hb_c = melf_f2(M + (float)h1);
+    const float2 eh_c = melf_f2(full ? -1e9f : (wrap ? 0.5f : -0.5f));
+    const float2 tiny = melf_f2(1e-30f), c43 = melf_f2(128.f / 3.f), M2 = melf_f2(M);
+    for (uint32_t gidx = blockIdx.x * blockDim.x + threadIdx.x; gidx < total;
+         gidx += gridDim.x * blockDim.x) {
+        const uint32_t rowi = melf_fastdiv(gidx, A.gdiv);
+        const uint32_t g = gidx - rowi * groups_per_row;
+        const uint32_t f = melf_fastdiv(rowi, A.hdiv);
+        const uint32_t y = rowi - f * (uint32_t)A.h;
+        const uint4 *src = reinterpret_cast<const uint4 *>(
+            A.bgr + (size_t)f * A.frame_stride + (size_t)y * A.row_stride) + 3 * g;
+        uint32_t in[12];
+        {
+            const uint4 v0 = ldg_stream(src), v1 = ldg_stream(src + 1), v2 = ldg_stream(src + 2);
+            in[0] = v0.x; in[1] = v0.y; in[2] = v0.z; in[3] = v0.w;
+            in[4] = v1.x; in[5] = v1.y; in[6] = v1.z; in[7] = v1.w;
+            in[8] = v2.x; in[9] = v2.y; in[10] = v2.z; in[11] = v2.w;
+        }
+        uint32_t out[12], lw[4], mw[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t c[4], lb[4], ob[4];
+#pragma unroll
+            for (int pr = 0; pr < 2; ++pr) {
+                const int b0 = 3 * (4 * q + 2 * pr), b1 = b0 + 3;
+                const float2 fb = make_float2(melf_byte_biased(in[b0 >> 2], b0 & 3), melf_byte_biased(in[b1 >> 2], b1 & 3));
+                const float2 fg = make_float2(melf_byte_biased(in[(b0 + 1) >> 2], (b0 + 1) & 3),
+                                              melf_byte_biased(in[(b1 + 1) >> 2], (b1 + 1) & 3));
+                const float2 fr = make_float2(melf_byte_biased(in[(b0 + 2) >> 2], (b0 + 2) & 3),
+                                              melf_byte_biased(in[(b1 + 2) >> 2], (b1 + 2) & 3));
+                const float2 vmax = make_float2(fmaxf(fmaxf(fb.x, fg.x), fr.x), fmaxf(fmaxf(fb.y, fg.y), fr.y));
+                const float2 vmin = make_float2(fminf(fminf(fb.x, fg.x), fr.x), fminf(fminf(fb.y, fg.y), fr.y));
+                // imax << 8 | imin from the low mantissa bytes (bytes 1, 2 of the biased float are 0)
+                const uint32_t i0 = __byte_perm(__float_as_uint(vmin.x), __float_as_uint(vmax.x), 0x1140);
+                const uint32_t i1 = __byte_perm(__float_as_uint(vmin.y), __float_as_uint(vmax.y), 0x1140);
+                const int e0 = tab[i0], e1 = tab[i1];                 // sign-extending 16-bit loads
+                const float2 dl = melf_add2(melf_sub2(vmax, vmin), tiny);
+                float2 inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv.x) : "f"(dl.x));
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv.y) : "f"(dl.y));
+                const float2 u_r = melf_sub2(fg, fb), u_g = melf_sub2(fb, fr), u_b = melf_sub2(fr, fg);
+                const bool rx = vmax.x == fr.x, gx = vmax.x == fg.x, ry = vmax.y == fr.y, gy = vmax.y == fg.y;
+                const float2 t = make_float2(rx ? u_r.x : gx ? u_g.x : u_b.x, ry ? u_r.y : gy ? u_g.y : u_b.y);
+                const float2 off = make_float2(rx ? (u_r.x < 0.f ? 256.f : 0.f) : gx ? 256.f / 3.f : 512.f / 3.f,
+                                               ry ? (u_r.y < 0.f ? 256.f : 0.f) : gy ? 256.f / 3.f : 512.f / 3.f);
+                const float2 v = melf_fma2(melf_mul2(t, inv), c43, off);
+                const float2 Hf = melf_add2(make_float2(fminf(v.x, 255.f), fminf(v.y, 255.f)), M2);
+                const int i = 2 * pr;
+                lb[i] = (uint32_t)e0; lb[i + 1] = (uint32_t)e1;
+                if (HLS) {
+                    const uint32_t hh0 = __float_as_uint(Hf.x) + (uint32_t)A.hue_shift,
+                                   hh1 = __float_as_uint(Hf.y) + (uint32_t)A.hue_shift;
+                    c[i] = __byte_perm(__byte_perm(hh0, lb[i], 0x0040), (uint32_t)tab_s[i0], 0x0410);
+                    c[i + 1] = __byte_perm(__byte_perm(hh1, lb[i + 1], 0x0040), (uint32_t)tab_s[i1], 0x0410);
+                }
+                if (MASK) {
+                    const float2 eh = melf_fma2(melf_fma2(Hf, hs2, ha_c), melf_fma2(hb_c, neg1, Hf), eh_c);
+                    ob[i] = __float_as_uint(eh.x) & (uint32_t)e0;
+                    ob[i + 1] = __float_as_uint(eh.y) & (uint32_t)e1;
+                }
+            }
+            if (MASK) mw[q] = __byte_perm(prmt_sign(ob[0], ob[1]), prmt_sign(ob[2], ob[3]), 0x5410);
+            if (HLS) {
+                out[3 * q] = __byte_perm(c[0], c[1], 0x4210);
+                out[3 * q + 1] = __byte_perm(c[1], c[2], 0x5421);
+                out[3 * q + 2] = __byte_perm(c[2], c[3], 0x6542);
+            }
+            if (LIGHT)
+                lw[q] = __byte_perm(__byte_perm(lb[0], lb[1], 0x0040), __byte_perm(lb[2], lb[3], 0x0040), 0x5410);
+        }
+        const size_t px = (size_t)gidx << 4;
+        if (HLS) {
+            uint4 *dst = reinterpret_cast<uint4 *>(A.hls + px * 3);
+            stg_stream(dst, make_uint4(out[0], out[1], out[2], out[3]));
+            stg_stream(dst + 1, make_uint4(out[4], out[5], out[6], out[7]));
+            stg_stream(dst + 2, make_uint4(out[8], out[9], out[10], out[11]));
+        }
+        if (LIGHT) stg_stream(reinterpret_cast<uint4 *>(A.light + px), make_uint4(lw[0], lw[1], lw[2], lw[3]));
+        if (MASK) stg_stream(reinterpret_cast<uint4 *>(A.mask + px), make_uint4(mw[0], mw[1], mw[2], mw[3]));
+    }
+}
+
 __global__ void __launch_bounds__(256)
 melf_convert_scalar_kernel(const MelfConvertArgs A)
 {
@@ -170,6 +331,62 @@ melf_convert_scalar_kernel(const MelfConvertArgs A)
         }
         if (A.light) A.light[i] = (c >> 8) & 255;
         if (A.mask) A.mask[i] = (uint8_t)in_range255(c, A.lo, A.hi);
+    }
+}
+
+// the static (L, S) table of the current device, built on first use
+static cudaError_t convert_table(const uint16_t **out, cudaStream_t stream)
+{
+    static std::mutex mutex;
+    static uint16_t *tables[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!tables[dev]) {
+        uint16_t *t = nullptr;
+        e = cudaMalloc(&t, 65536 * sizeof(uint16_t));
+        if (e != cudaSuccess) return e;
+        melf_convert_build_table_kernel<<<256, 256, 0, stream>>>(t);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);    // once: other streams may use it next
+        if (e != cudaSuccess) { cudaFree(t); return e; }
+        tables[dev] = t;
+    }
+    *out = tables[dev];
+    return cudaSuccess;
+}
+
+template <bool HLS, bool LIGHT, bool MASK>
+static cudaError_t launch_tab_one(const MelfConvertArgs &b, const uint16_t *table, unsigned grid,
+                                  cudaStream_t stream)
+{
+    const int smem = TAB_SMEM_LS + (HLS ? TAB_SMEM_S : 0);
+    // per device and cheap: set on every launch rather than caching per process
+    cudaError_t e = cudaFuncSetAttribute(melf_convert_tab_kernel<HLS, LIGHT, MASK>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    melf_convert_tab_kernel<HLS, LIGHT, MASK><<<grid, TAB_THREADS, smem, stream>>>(b, table);
+    return cudaGetLastError();
+}
+
+static cudaError_t launch_tab(const MelfConvertArgs &b, const uint16_t *table, int num_sms,
+                              long long total_groups, cudaStream_t stream)
+{
+    long long blocks = (total_groups + TAB_THREADS - 1) / TAB_THREADS;
+    if (blocks > num_sms) blocks = num_sms;
+    if (blocks < 1) blocks = 1;
+    const unsigned grid = (unsigned)blocks;
+    switch ((b.hls ? 4 : 0) | (b.light ? 2 : 0) | (b.mask ? 1 : 0)) {
+    case 7: return launch_tab_one<true, true, true>(b, table, grid, stream);
+    case 6: return launch_tab_one<true, true, false>(b, table, grid, stream);
+    case 5: return launch_tab_one<true, false, true>(b, table, grid, stream);
+    case 4: return launch_tab_one<true, false, false>(b, table, grid, stream);
+    case 3: return launch_tab_one<false, true, true>(b, table, grid, stream);
+    case 2: return launch_tab_one<false, true, false>(b, table, grid, stream);
+    case 1: return launch_tab_one<false, false, true>(b, table, grid, stream);
+    default: return cudaSuccess;
     }
 }
 
@@ -226,6 +443,17 @@ cudaError_t melf_launch_convert(const MelfConvertArgs &a_in, int num_sms, cudaSt
             cudaError_t e = cudaMemsetAsync(b.mask, 0, (size_t)b.n * b.h * b.w, stream);
             if (e != cudaSuccess) return e;
             b.mask = nullptr;
+        }
+        // large batches: the table kernel (one persistent CTA per SM); small ones are not worth
+        // staging 128 KB per CTA.  MELF_CONVERT_IMPL=fma|tab forces one of them.
+        const char *impl = std::getenv("MELF_CONVERT_IMPL");
+        const bool want_tab = impl ? std::strcmp(impl, "tab") == 0
+                                   : (long long)b.n * b.h * b.w >= (long long)num_sms * TAB_THREADS * 64;
+        if (want_tab && !(impl && std::strcmp(impl, "fma") == 0)) {
+            const uint16_t *table = nullptr;
+            cudaError_t e = convert_table(&table, stream);
+            if (e != cudaSuccess) return e;
+            return launch_tab(b, table, num_sms, total, stream);
         }
         switch ((b.hls ? 4 : 0) | (b.light ? 2 : 0) | (b.mask ? 1 : 0)) {
         case 7: melf_convert_vec_kernel<true, true, true><<<gb, 256, 0, stream>>>(b); break;
