@@ -22,8 +22,8 @@ bool melf_match_tc_supported(int tmpl_w, int tmpl_h);
 size_t melf_match_tc_toeplitz_bytes(int tmpl_h);
 void melf_match_tc_build_toeplitz(const uint8_t *tmpl, int tmpl_w, int tmpl_h, uint8_t *out);
 long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames);
-cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, long long n_pass, int num_sms,
-                                 cudaStream_t stream);
+size_t melf_match_tc_scratch_bytes(long long max_items, size_t *wsum_offset);
+cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
 
@@ -32,6 +32,7 @@ std::mutex g_err_mutex;
 std::string g_create_error;
 
 constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
+constexpr long long kTcMaxItems = 4096; // work items per prep + correlation launch pair (~400 MB scratch)
 
 }  // namespace
 
@@ -50,6 +51,8 @@ struct melf_ctx {
     uint32_t *d_ones_words = nullptr;
     uint8_t *d_toeplitz = nullptr;     // tensor-core path operands (NULL: template not supported there)
     bool use_tc = false;
+    uint8_t *d_tc_scratch[3] = {nullptr, nullptr, nullptr};   // [0]: caller-stream path, [1], [2]: pipeline streams
+    long long tc_scratch_items[3] = {0, 0, 0};
     long long sum_t = 0, n_t = 0;
     int tw4p = 0, steps = 0;
     std::vector<int32_t> win_x0, win_y0;
@@ -122,7 +125,7 @@ void fill_match_args(const melf_ctx *ctx, MelfMatchArgs *a)
 // the dp4a kernel (both CUDA, both exact; MELF_MATCH_IMPL=dp4a forces the latter)
 int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
                   size_t row_stride, size_t frame_stride, const MelfGeom &geom, u64 *d_keys,
-                  float *d_result, cudaStream_t stream)
+                  float *d_result, cudaStream_t stream, int scratch_slot)
 {
     MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
     if (ctx->use_tc) {
@@ -139,9 +142,45 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         t.sum_t = ctx->sum_t; t.n_t = ctx->n_t;
         t.match_key = d_keys;
         t.result = d_result;
-        const long long n_pass = melf_match_tc_plan(t, n);
-        MELF_CUDA(ctx, melf_launch_match_tc(t, n_pass, ctx->num_sms, stream));
-        g_launches++;
+        melf_match_tc_plan(t, n);
+        long long cap = t.n_items < kTcMaxItems ? t.n_items : kTcMaxItems;
+        cap += cap & 1;
+        if (ctx->tc_scratch_items[scratch_slot] < cap) {
+            if (ctx->d_tc_scratch[scratch_slot]) cudaFree(ctx->d_tc_scratch[scratch_slot]);
+            ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], melf_match_tc_scratch_bytes(cap, nullptr)));
+            ctx->tc_scratch_items[scratch_slot] = cap;
+        }
+        size_t wsum_off = 0;
+        melf_match_tc_scratch_bytes(ctx->tc_scratch_items[scratch_slot], &wsum_off);
+        t.slabs = ctx->d_tc_scratch[scratch_slot];
+        t.wsum = reinterpret_cast<uint32_t *>(ctx->d_tc_scratch[scratch_slot] + wsum_off);
+        t.max_items = ctx->tc_scratch_items[scratch_slot];
+        // MELF_TC_TIMELINE=<file>: debug dump of CTA 0's per-pass clock64 stamps (synchronises)
+        const char *tl_path = std::getenv("MELF_TC_TIMELINE");
+        long long *d_tl = nullptr;
+        if (tl_path) {
+            MELF_CUDA(ctx, cudaMalloc(&d_tl, 64 * sizeof(long long)));
+            MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
+            t.timeline = d_tl;
+        }
+        for (t.item0 = 0; t.item0 < t.n_items; t.item0 += t.max_items) {
+            MELF_CUDA(ctx, melf_launch_match_tc(t, ctx->num_sms, stream));
+            g_launches += 2;
+        }
+        if (d_tl) {
+            long long h_tl[64];
+            MELF_CUDA(ctx, cudaStreamSynchronize(stream));
+            MELF_CUDA(ctx, cudaMemcpy(h_tl, d_tl, sizeof h_tl, cudaMemcpyDeviceToHost));
+            cudaFree(d_tl);
+            if (FILE *fp = std::fopen(tl_path, "w")) {
+                for (int i = 0; i < 8; i++) {
+                    for (int j = 0; j < 8; j++) std::fprintf(fp, "%lld ", h_tl[8 * i + j] - (j < 7 ? h_tl[0] : 0));
+                    std::fprintf(fp, "\n");
+                }
+                std::fclose(fp);
+            }
+        }
         return MELF_OK;
     }
     MelfMatchArgs m{};
@@ -176,10 +215,10 @@ int ensure_keys(melf_ctx *ctx, int n)
 // locate + read on device-resident frames; keys = per-frame scratch (n entries)
 int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_w,
              size_t row_stride, size_t frame_stride, const MelfGeom &geom, u64 *d_keys, melf_result *d_out, const melf_taps *taps,
-             cudaStream_t stream)
+             cudaStream_t stream, int scratch_slot)
 {
     int rc = launch_locate(ctx, d_bgr, 3, n, frame_h, frame_w, row_stride, frame_stride, geom, d_keys,
-                           nullptr, stream);
+                           nullptr, stream, scratch_slot);
     if (rc) return rc;
     MelfDialsArgs a{};
     a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
@@ -207,6 +246,7 @@ void free_ctx(melf_ctx *ctx)
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_keys);
+    for (int i = 0; i < 3; i++) cudaFree(ctx->d_tc_scratch[i]);
     for (int i = 0; i < 2; i++) {
         if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
         cudaFree(ctx->d_chunk[i]); cudaFree(ctx->d_res[i]); cudaFree(ctx->d_chunk_keys[i]);
@@ -359,7 +399,7 @@ int melf_read_batch_async(melf_ctx *ctx, const uint8_t *d_bgr, int n, int h, int
     rc = ensure_keys(ctx, n);
     if (rc) return rc;
     return run_path(ctx, d_bgr, n, h, w, row_stride, frame_stride, geom, ctx->d_keys, d_out, taps,
-                    (cudaStream_t)stream);
+                    (cudaStream_t)stream, 0);
 }
 
 int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
@@ -433,7 +473,7 @@ int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
             }
         }
         rc = run_path(ctx, ctx->d_chunk[b], nf, geom.crop_h, geom.crop_w, pitch, frame_bytes, cg,
-                      ctx->d_chunk_keys[b], ctx->d_res[b], nullptr, st);
+                      ctx->d_chunk_keys[b], ctx->d_res[b], nullptr, st, 1 + b);
         if (rc) return rc;
         MELF_CUDA(ctx, cudaMemcpyAsync(ctx->h_res + (size_t)b * kChunkFrames, ctx->d_res[b],
                                        sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
@@ -491,7 +531,7 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     rc = launch_locate(ctx, d_img, channels, n, h, w, row_stride, frame_stride, geom, ctx->d_keys,
-                       d_result, st);
+                       d_result, st, 0);
     if (rc) return rc;
     MELF_CUDA(ctx, melf_launch_match_unpack(ctx->d_keys, n, geom.res_w, d_max_xy, d_max_val, st));
     g_launches++;

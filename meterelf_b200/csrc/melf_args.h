@@ -51,6 +51,12 @@ struct MelfMatchTcArgs {
     u64 *match_key;              // [n] atomicMax slot per frame (zeroed before launch)
     float *result;               // optional [n][res_h][res_w]
     uint32_t ones_words[64];     // byte j = 1 for j < tmpl_w
+    // scratch written by the preparation kernel, read by the tensor-core kernel; one launch
+    // pair covers the items [item0, item0 + max_items) (max_items even)
+    uint8_t *slabs;              // [max_items][64 KB] lightness slabs in the UMMA strip layout
+    uint32_t *wsum;              // [max_items][64][137] window sums, x-major
+    long long item0, max_items;
+    long long *timeline;         // optional debug: clock64 stamps of CTA 0's first 8 passes, 8 per pass
 };
 
 struct MelfConvertArgs {

@@ -1,6 +1,7 @@
 // Dial location on the 5th-generation tensor cores: TM_CCOEFF as an exact u8 x u8 -> s32
-// implicit GEMM (tcgen05.mma.kind::i8, accumulators in TMEM), fused with the lightness
-// conversion in front of it and the window sums, score and arg-max behind it.
+// implicit GEMM (tcgen05.mma.kind::i8, accumulators in TMEM), with the lightness conversion
+// and window sums in a small preparation kernel in front of it and the score and arg-max
+// fused behind it.
 //
 // Replaces, like melf_match.cu, ImageFile._find_dials (_image.py:57-66) = cv2.split(hls)[1]
 // + match_template (_utils.py:91-97: cv2.matchTemplate(TM_CCOEFF) + cv2.minMaxLoc).
@@ -21,17 +22,16 @@
 // address.  The Toeplitz operands (119 rows -> 60 pairs x 32 KB) are built once per
 // params on the host, live in L2 and stream through a 2-stage cp.async.bulk pipeline.
 //
-// One CTA (512 threads) per SM, persistent over "passes" of two work items (a work item
-// = one 64-column x <=137-row block of one frame's result map; for the sample geometry,
-// 63 x 132, that is one whole frame).  Per pass:
-//   1. all warps: BGR crop -> lightness (bit-exact float32 order of cv2, no XU pipe ops)
-//      -> two 64 KB slabs in shared memory;
-//   2. one thread streams the Toeplitz pairs (bulk async copies + mbarriers), one thread
-//      issues 60 x (2 items x 2 M-tiles x 8 K-steps) tcgen05.mma of 128 x 128 x 32;
-//   3. all warps: horizontal then vertical window sums of the slabs (the sum_window L
-//      term), into the now idle operand buffers;
-//   4. all warps: TMEM -> registers, exact score (N*sumTL - sumT*sumL)/N -> float32,
-//      64-bit (score, ~raster index) key, warp/block max, one atomicMax per item.
+// A work item = one 64-column x <=137-row block of one frame's result map; for the sample
+// geometry, 63 x 132, that is one whole frame.  Two kernels per batch:
+//   melf_match_prep_kernel  one CTA per item: BGR crop -> lightness (bit-exact float32 order of
+//       cv2, no XU pipe ops) -> slab in the strip layout + window sums, to global scratch
+//       (64 KB + 34 KB per item; L2/HBM traffic that is small next to the MMA time);
+//   melf_match_tc_kernel    persistent, one CTA per SM, two items per pass: slabs by one bulk
+//       copy each, Toeplitz stream, 60 x (2 items x 2 M-tiles x 8 K-steps) tcgen05.mma of
+//       128 x 128 x 32, then TMEM -> registers, exact score (N*sumTL - sumT*sumL)/N -> float32,
+//       64-bit (score, ~raster index) key, warp/block max, one atomicMax per item.  The
+//       operands of the next pass are fetched under the epilogue of the current one.
 // Everything is integer-exact, so results are bit-identical to melf_match.cu and to the
 // oracle.
 #include "melf_common.cuh"
@@ -40,31 +40,27 @@
 namespace {
 
 constexpr int TC_THREADS = 512;
-constexpr int SLAB_ROWS = 256;                       // rows of a lightness slab
+constexpr int SLAB_ROWS = 264;                       // rows of a lightness slab (118 + 144 -> 264)
+constexpr int SLAB_DATA_ROWS = 256;                  // rows that can hold image data (plan cap)
 constexpr int KS = 16;                               // 16-byte K strips: K = 256
-constexpr int STRIP_BYTES = SLAB_ROWS * 16;          // 4096
-constexpr int SLAB_BYTES = KS * STRIP_BYTES;         // 65536
-constexpr int BN = 128;                              // MMA N: two template rows x 64 columns
-constexpr int BSTRIP_BYTES = BN * 16;                // 2048
+constexpr int STRIP_BYTES = SLAB_ROWS * 16;          // 4224
+constexpr int SLAB_BYTES = KS * STRIP_BYTES;         // 67584
+constexpr int BM = 128;                              // MMA M: 64 result columns x two template rows
+constexpr int BSTRIP_BYTES = BM * 16;                // 2048
 constexpr int BSTAGE_BYTES = KS * BSTRIP_BYTES;      // 32768
 constexpr int NSTAGE = 2;
-constexpr int SROWS = 137;                           // max result rows of a work item (odd)
+constexpr int SROWS = 137;                           // max result rows of a work item
+constexpr int NCOLS = 144;                           // TMEM columns of one accumulator = max MMA N
+constexpr int WS_PITCH = 144;                        // window-sum row pitch (words)
 constexpr int SMEM_SLABS = 0;
-constexpr int SMEM_B = 2 * SLAB_BYTES;               // 131072
-constexpr int SMEM_CTRL = SMEM_B + NSTAGE * BSTAGE_BYTES;   // 196608
-constexpr int SMEM_TOTAL = SMEM_CTRL + 512;
+constexpr int SMEM_B = 2 * SLAB_BYTES;               // 135168
+constexpr int SMEM_CTRL = SMEM_B + NSTAGE * BSTAGE_BYTES;   // 200704
 
-// tcgen05 instruction descriptor: D = s32, A = B = u8, both K-major, M = 128, N = 128
-constexpr uint32_t IDESC = (2u << 4) | (0u << 7) | (0u << 10) | ((BN >> 3) << 17) | ((128u >> 4) << 24);
-
-struct Ctrl {
-    unsigned long long full[NSTAGE];
-    unsigned long long empty[NSTAGE];
-    unsigned long long accum;
-    uint32_t tmem_base;
-    uint32_t pad;
-    u64 red[16];
-};
+// tcgen05 instruction descriptor: D = s32, A = B = u8, both K-major, M = 128, N = n
+__host__ __device__ constexpr uint32_t make_idesc(uint32_t n)
+{
+    return (2u << 4) | (0u << 7) | (0u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {
@@ -113,14 +109,15 @@ __device__ __forceinline__ u64 umma_desc(uint32_t addr, uint32_t lbo_bytes)
            ((u64)((128u >> 4) & 0x3fffu) << 32) | (1ull << 46);
 }
 
-__device__ __forceinline__ void umma_i8(uint32_t tmem_d, u64 adesc, u64 bdesc, uint32_t accumulate)
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, u64 adesc, u64 bdesc, uint32_t idesc,
+                                        uint32_t accumulate)
 {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
-        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(IDESC), "r"(accumulate) : "memory");
+        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
@@ -132,11 +129,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld1(uint32_t taddr, uint32_t &v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // geometry of one work item
 struct Item {
-    int frame, x0, y0, w_c, h_c, off1, n_mt;
+    int frame, x0, y0, w_c, h_c, n_cols;
     bool valid;
 };
 
@@ -144,7 +145,7 @@ __device__ __forceinline__ Item get_item(const MelfMatchTcArgs &A, long long idx
 {
     Item it;
     it.valid = idx < A.n_items;
-    if (!it.valid) { it.frame = 0; it.x0 = it.y0 = 0; it.w_c = it.h_c = 0; it.off1 = 0; it.n_mt = 0; return it; }
+    if (!it.valid) { it.frame = 0; it.x0 = it.y0 = 0; it.w_c = it.h_c = 0; it.n_cols = 16; return it; }
     const int per_frame = A.n_tx * A.n_ty;
     it.frame = (int)(idx / per_frame);
     const int rem = (int)(idx - (long long)it.frame * per_frame);
@@ -153,8 +154,7 @@ __device__ __forceinline__ Item get_item(const MelfMatchTcArgs &A, long long idx
     it.y0 = ty * A.chunk_h;
     it.w_c = min(64, A.geom.res_w - it.x0);
     it.h_c = min(A.chunk_h, A.geom.res_h - it.y0);
-    it.n_mt = it.h_c > 127 ? 2 : 1;
-    it.off1 = it.h_c - 127;                    // M-tile 1 covers rows [h_c-127, h_c)
+    it.n_cols = (it.h_c + 1 + 15) & ~15;       // result rows 0..h_c-1 need D columns 0..h_c
     return it;
 }
 
@@ -234,12 +234,170 @@ __device__ __forceinline__ uint4 stage_unit(const MelfMatchTcArgs &A, const Item
 
 extern __shared__ __align__(1024) uint8_t melf_tc_smem[];
 
+// ---------------------------------------------------------------------------------------
+// Kernel 1 of 2: operand preparation.  One CTA per work item: BGR crop -> lightness slab in
+// the UMMA strip layout (written to global scratch so the tensor-core kernel can fetch it with
+// ONE 64 KB bulk copy) and the window sums S(y, x) = sum over the template footprint of L
+// (the "mean(T) * sum_window L" term of TM_CCOEFF), x-major, to global scratch.
+// HBM/L2-bound and small next to the correlation; keeping it out of the tensor-core kernel
+// leaves that kernel's shared memory to the operands and its issue slots to the MMA stream
+// (ncu on the fused v2 kernel: tensor pipe only 52 % active, profiles/r01_v3_ncu_match.txt).
+// ---------------------------------------------------------------------------------------
+constexpr int PREP_THREADS = 512;
+constexpr int PREP_SMEM_H = SLAB_BYTES;                   // H table: 256 rows x 32 words (u16 pairs)
+constexpr int PREP_SMEM_TOTAL = SLAB_BYTES + 32768;
+constexpr int WSUM_WORDS = 64 * WS_PITCH;                 // per work item
+
+__global__ void __launch_bounds__(PREP_THREADS, 2)
+melf_match_prep_kernel(const MelfMatchTcArgs A)
+{
+    uint8_t *smem = melf_tc_smem;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long li = blockIdx.x;                       // item index inside this launch
+    const Item it = get_item(A, A.item0 + li);
+
+    // ---- 1. lightness slab: warp-unit = 8 rows x 4 strips; lane = strip * 8 + row, so that
+    // every quarter warp stores 128 contiguous bytes (conflict-free 128-bit shared stores)
+    for (int u = warp; u < (SLAB_ROWS / 8) * 4; u += PREP_THREADS / 32) {
+        const int rg = u >> 2, sg = u & 3;
+        const int r = rg * 8 + (lane & 7), s = sg * 4 + (lane >> 3);
+        *reinterpret_cast<uint4 *>(smem + s * STRIP_BYTES + r * 16) = stage_unit(A, it, r, s);
+    }
+    __syncthreads();
+
+    // ---- 2. slab -> global scratch (coalesced) ------------------------------------------
+    {
+        uint4 *dst = reinterpret_cast<uint4 *>(A.slabs + (size_t)li * SLAB_BYTES);
+        const uint4 *src = reinterpret_cast<const uint4 *>(smem);
+        for (int i = tid; i < SLAB_BYTES / 16; i += PREP_THREADS) dst[i] = src[i];
+    }
+
+    // ---- 3a. horizontal window sums H(row, x) = sum_{j<tw} L(row, x+j), x < 64 ------------
+    // thread = row; stored as u16 pairs, word (row, xp) at row*32 + (xp ^ (row & 31))
+    if (tid < SLAB_DATA_ROWS) {
+        const int row = tid;
+        const uint8_t *sl = smem + row * 16;
+        uint32_t *Hb = reinterpret_cast<uint32_t *>(smem + PREP_SMEM_H) + row * 32;
+        uint32_t w[16];                       // bytes 0..63 of the row (the leaving bytes)
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(sl + s * STRIP_BYTES);
+            w[4 * s] = v.x; w[4 * s + 1] = v.y; w[4 * s + 2] = v.z; w[4 * s + 3] = v.w;
+        }
+        int h0 = 0;
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(sl + s * STRIP_BYTES);
+            h0 = (int)__dp4a(v.x, A.ones_words[4 * s], (uint32_t)h0);
+            h0 = (int)__dp4a(v.y, A.ones_words[4 * s + 1], (uint32_t)h0);
+            h0 = (int)__dp4a(v.z, A.ones_words[4 * s + 2], (uint32_t)h0);
+            h0 = (int)__dp4a(v.w, A.ones_words[4 * s + 3], (uint32_t)h0);
+        }
+        // entering bytes: columns tw .. tw+62, i.e. 80 bytes from strip tw/16 on
+        const int s0 = A.tmpl_w >> 4;
+        uint32_t e[20];
+#pragma unroll
+        for (int s = 0; s < 5; ++s) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (s0 + s < KS) v = *reinterpret_cast<const uint4 *>(sl + (s0 + s) * STRIP_BYTES);
+            e[4 * s] = v.x; e[4 * s + 1] = v.y; e[4 * s + 2] = v.z; e[4 * s + 3] = v.w;
+        }
+        const uint32_t o = (uint32_t)A.tmpl_w & 15, ws = o >> 2, bs = (o & 3) * 8;
+        uint32_t t[17], g[16];
+#pragma unroll
+        for (int j = 0; j < 17; ++j)
+            t[j] = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) g[j] = __funnelshift_r(t[j], t[j + 1], bs);
+        int h = h0;
+        const int sw = row & 31;
+#pragma unroll
+        for (int xp = 0; xp < 32; ++xp) {
+            const int xa = 2 * xp, xb = 2 * xp + 1;
+            const uint32_t lo = (uint32_t)h;
+            h += (int)((g[xa >> 2] >> (8 * (xa & 3))) & 255) - (int)((w[xa >> 2] >> (8 * (xa & 3))) & 255);
+            const uint32_t hi = (uint32_t)h;
+            h += (int)((g[xb >> 2] >> (8 * (xb & 3))) & 255) - (int)((w[xb >> 2] >> (8 * (xb & 3))) & 255);
+            Hb[xp ^ sw] = lo | (hi << 16);
+        }
+    }
+    __syncthreads();          // H complete; every read of the slab (copy-out, 3a) is done
+
+    // ---- 3b. vertical: S(y, x) = sum_{i<th} H(y+i, x); thread = (segment, x pair) ---------
+    // S goes into the (now dead) slab, x-major: S[x * WS_PITCH + y]
+    {
+        const int seg = tid >> 5, xp = lane;
+        const uint32_t *Hb = reinterpret_cast<const uint32_t *>(smem + PREP_SMEM_H);
+        uint32_t *S = reinterpret_cast<uint32_t *>(smem);
+        const int rs = (it.h_c + 15) >> 4;
+        const int ya = seg * rs, yb = min(it.h_c, ya + rs);
+        if (ya < yb) {
+            uint32_t s0 = 0, s1 = 0;
+            for (int i = 0; i < A.tmpl_h; ++i) {
+                const int row = ya + i;
+                const uint32_t v = Hb[row * 32 + (xp ^ (row & 31))];
+                s0 += v & 0xffff; s1 += v >> 16;
+            }
+            for (int y = ya; y < yb; ++y) {
+                S[(2 * xp) * WS_PITCH + y] = s0;
+                S[(2 * xp + 1) * WS_PITCH + y] = s1;
+                const int rin = y + A.tmpl_h;
+                const uint32_t vin = Hb[rin * 32 + (xp ^ (rin & 31))];      // row <= 255 always
+                const uint32_t vout = Hb[y * 32 + (xp ^ (y & 31))];
+                s0 += (vin & 0xffff) - (vout & 0xffff);
+                s1 += (vin >> 16) - (vout >> 16);
+            }
+        }
+    }
+    __syncthreads();
+    {
+        uint32_t *dst = A.wsum + (size_t)li * WSUM_WORDS;
+        const uint32_t *S = reinterpret_cast<const uint32_t *>(smem);
+        for (int i = tid; i < WSUM_WORDS; i += PREP_THREADS) dst[i] = S[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Kernel 2 of 2: the correlation.  Persistent, one CTA per SM, two work items per pass
+// (they share every Toeplitz stage, which halves the L2 -> SM operand traffic).
+// The Toeplitz pair is the A operand (M = 128 = 64 result columns x 2 template rows, row
+// m = 2 n + q), the lightness slab the B operand (N = result rows + 1, rounded up to 16), so
+// the result-row extent costs exactly what it needs (132 rows -> N = 144) instead of two
+// 128-row M tiles:
+//     D[2n+q][r] += Toep_{2p+q}[n][.] . L(r + 2p, .)        p = 0 .. ceil(th/2)-1
+//     sum T*L (y, x) = D[2x][y] + D[2x+1][y+1]
+//   thread 0   producer: slabs (one 66 KB bulk copy each) and Toeplitz stages
+//   thread 32  issuer:   n_pairs x (2 items x 8 K-steps) tcgen05.mma of 128 x N x 32
+//   all warps  epilogue: window sums prefetched from global, TMEM -> registers (lane pair
+//              2x / 2x+1 holds the two template-row halves of column x), exact integer
+//              numerator, arg-max with float32 rounding only for close calls.
+// As soon as the accumulators are complete the producer refills both slabs and the first
+// Toeplitz stages for the NEXT pass, so those copies run under the epilogue.
+// ---------------------------------------------------------------------------------------
+constexpr int SMEM_TOTAL2 = SMEM_CTRL + 512;
+
+struct Ctrl2 {
+    unsigned long long full[NSTAGE];
+    unsigned long long empty[NSTAGE];
+    unsigned long long accum;
+    unsigned long long slab_full;
+    uint32_t tmem_base;
+    uint32_t pad;
+    u64 red[2][16];            // per pass parity
+};
+
+// exact TM_CCOEFF value of an integer numerator, rounded once to float32 (cv2's result type)
+__device__ __forceinline__ float score_of(long long num, long long n_t)
+{
+    return __double2float_rn(__ddiv_rn((double)num, (double)n_t));
+}
+
 template <bool WRITE_MAP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 melf_match_tc_kernel(const MelfMatchTcArgs A)
 {
     uint8_t *smem = melf_tc_smem;
-    Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + SMEM_CTRL);
+    Ctrl2 *ctrl = reinterpret_cast<Ctrl2 *>(smem + SMEM_CTRL);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t slab_addr = smem_u32(smem + SMEM_SLABS), b_addr = smem_u32(smem + SMEM_B);
 
@@ -249,6 +407,7 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
             mbar_init(smem_u32(&ctrl->empty[s]), 1);
         }
         mbar_init(smem_u32(&ctrl->accum), 1);
+        mbar_init(smem_u32(&ctrl->slab_full), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -262,230 +421,185 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
     tc_fence_after();
     const uint32_t tmem = ctrl->tmem_base;
 
-    uint32_t stage_count = 0;       // Toeplitz stages consumed so far (producer and issuer keep their own copy)
+    const long long n_local = A.n_items - A.item0 < A.max_items ? A.n_items - A.item0 : A.max_items;
+    const long long n_pass = (n_local + 1) / 2;
+    const int n_pre = A.n_pairs < NSTAGE ? A.n_pairs : NSTAGE;     // stages prefetched ahead of a pass
+
+    // producer helpers (thread 0 only).  Stage g of the running stage counter uses ring slot
+    // g % NSTAGE; its "empty" barrier has completed (g / NSTAGE) phases when it may be refilled.
+    auto load_stage = [&](uint32_t g, int p) {
+        const uint32_t st = g % NSTAGE, ph = (g / NSTAGE) & 1;
+        mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
+        mbar_expect_tx(smem_u32(&ctrl->full[st]), BSTAGE_BYTES);
+        bulk_load(b_addr + st * BSTAGE_BYTES, A.toeplitz + (size_t)p * BSTAGE_BYTES, BSTAGE_BYTES,
+                  smem_u32(&ctrl->full[st]));
+    };
+    auto load_slabs = [&](long long pass) {
+        const long long i0 = 2 * pass;
+        const int n = (i0 + 1 < n_local) ? 2 : 1;
+        mbar_expect_tx(smem_u32(&ctrl->slab_full), (uint32_t)(n * SLAB_BYTES));
+        for (int k = 0; k < n; ++k)
+            bulk_load(slab_addr + k * SLAB_BYTES, A.slabs + (size_t)(i0 + k) * SLAB_BYTES, SLAB_BYTES,
+                      smem_u32(&ctrl->slab_full));
+    };
+
+    uint32_t stage_count = 0;       // Toeplitz stages consumed before this pass
     uint32_t pass_count = 0;
-    const long long n_pass = (A.n_items + 1) / 2;
+    if (tid == 0 && (long long)blockIdx.x < n_pass) {
+        load_slabs(blockIdx.x);
+        for (int p = 0; p < n_pre; ++p) load_stage((uint32_t)p, p);
+    }
 
     for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x, ++pass_count) {
         Item items[2];
-        items[0] = get_item(A, 2 * pass);
-        items[1] = get_item(A, 2 * pass + 1);
+        items[0] = get_item(A, A.item0 + 2 * pass);
+        items[1] = get_item(A, A.item0 + 2 * pass + 1);
+        if (2 * pass + 1 >= n_local) items[1].valid = false;
+        const bool has_next = pass + gridDim.x < n_pass;
+        long long *tl = (A.timeline && blockIdx.x == 0 && pass_count < 8) ? A.timeline + pass_count * 8 : nullptr;
 
-        // ---- 1. lightness slabs -----------------------------------------------------------
-        // warp-unit = 8 rows x 4 strips; lane = strip * 8 + row, so that every quarter warp
-        // stores 128 contiguous bytes (conflict-free 128-bit shared stores)
-        for (int u = warp; u < 2 * 32 * 4; u += TC_THREADS / 32) {
-            const int slot = u >> 7, rg = (u >> 2) & 31, sg = u & 3;
-            const int r = rg * 8 + (lane & 7), s = sg * 4 + (lane >> 3);
-            const uint4 v = stage_unit(A, slot ? items[1] : items[0], r, s);
-            *reinterpret_cast<uint4 *>(smem + SMEM_SLABS + slot * SLAB_BYTES + s * STRIP_BYTES + r * 16) = v;
-        }
-        fence_async_smem();          // generic-proxy writes -> visible to the tensor core / bulk copies
-        tc_fence_before();
-        __syncthreads();
-        tc_fence_after();
-
-        // ---- 2. the correlation: Toeplitz stream + MMA -----------------------------------
+        // ---- the correlation: Toeplitz stream + MMA ------------------------------------------
         if (tid == 0) {
-            uint32_t g = stage_count;
-            for (int p = 0; p < A.n_pairs; ++p, ++g) {
-                const uint32_t st = g & 1, ph = (g >> 1) & 1;
-                mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
-                mbar_expect_tx(smem_u32(&ctrl->full[st]), BSTAGE_BYTES);
-                bulk_load(b_addr + st * BSTAGE_BYTES, A.toeplitz + (size_t)p * BSTAGE_BYTES, BSTAGE_BYTES,
-                          smem_u32(&ctrl->full[st]));
-            }
+            for (int p = n_pre; p < A.n_pairs; ++p) load_stage(stage_count + (uint32_t)p, p);
         } else if (tid == 32) {
+            if (tl) tl[0] = clock64();
+            mbar_wait(smem_u32(&ctrl->slab_full), pass_count & 1);
+            tc_fence_after();
+            if (tl) tl[1] = clock64();
+            long long waited = 0;
+            const uint32_t idesc0 = make_idesc((uint32_t)items[0].n_cols);
+            const uint32_t idesc1 = make_idesc((uint32_t)items[1].n_cols);
             uint32_t g = stage_count;
             for (int p = 0; p < A.n_pairs; ++p, ++g) {
-                const uint32_t st = g & 1, ph = (g >> 1) & 1;
+                const uint32_t st = g % NSTAGE, ph = (g / NSTAGE) & 1;
+                const long long w0 = tl ? clock64() : 0;
                 mbar_wait(smem_u32(&ctrl->full[st]), ph);
                 tc_fence_after();
-                const uint32_t bbase = b_addr + st * BSTAGE_BYTES;
+                if (tl) waited += clock64() - w0;
+                const uint32_t abase = b_addr + st * BSTAGE_BYTES;               // Toeplitz pair = A
 #pragma unroll
                 for (int slot = 0; slot < 2; ++slot) {
                     if (!items[slot].valid) continue;
-                    for (int mt = 0; mt < items[slot].n_mt; ++mt) {
-                        const int row0 = (mt ? items[slot].off1 : 0) + 2 * p;
-                        const uint32_t abase = slab_addr + slot * SLAB_BYTES + row0 * 16;
-                        const uint32_t d = tmem + (uint32_t)((slot * 2 + mt) * BN);
+                    const uint32_t bbase = slab_addr + slot * SLAB_BYTES + (2 * p) * 16;   // slab rows 2p.. = B
+                    const uint32_t d = tmem + (uint32_t)(slot * NCOLS);
 #pragma unroll
-                        for (int ks = 0; ks < KS / 2; ++ks)
-                            umma_i8(d, umma_desc(abase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
-                                    umma_desc(bbase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
-                                    (p > 0 || ks > 0) ? 1u : 0u);
-                    }
+                    for (int ks = 0; ks < KS / 2; ++ks)
+                        umma_i8(d, umma_desc(abase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
+                                umma_desc(bbase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
+                                slot ? idesc1 : idesc0, (p > 0 || ks > 0) ? 1u : 0u);
                 }
                 umma_commit(smem_u32(&ctrl->empty[st]));
             }
             umma_commit(smem_u32(&ctrl->accum));
-            mbar_wait(smem_u32(&ctrl->accum), pass_count & 1);
+            if (tl) { tl[2] = clock64(); tl[7] = waited; }
         }
         stage_count += (uint32_t)A.n_pairs;
-        tc_fence_before();
-        __syncthreads();
-        tc_fence_after();
+        __syncwarp();
 
-        // ---- 3a. horizontal window sums H(row, x) = sum_{j<tw} L(row, x+j), x < 64 ----------
-        // thread = (slot, row); stored as u16 pairs, word (row, xp) at row*32 + (xp ^ (row & 31))
-        {
-            const int slot = tid >> 8, row = tid & 255;
-            const uint8_t *sl = smem + SMEM_SLABS + slot * SLAB_BYTES + row * 16;
-            uint32_t *Hb = reinterpret_cast<uint32_t *>(smem + SMEM_B + slot * 32768) + row * 32;
-            uint32_t w[16];                       // bytes 0..63 of the row (the leaving bytes)
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(sl + s * STRIP_BYTES);
-                w[4 * s] = v.x; w[4 * s + 1] = v.y; w[4 * s + 2] = v.z; w[4 * s + 3] = v.w;
-            }
-            int h0 = 0;
-#pragma unroll
-            for (int s = 0; s < KS; ++s) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(sl + s * STRIP_BYTES);
-                h0 = (int)__dp4a(v.x, A.ones_words[4 * s], (uint32_t)h0);
-                h0 = (int)__dp4a(v.y, A.ones_words[4 * s + 1], (uint32_t)h0);
-                h0 = (int)__dp4a(v.z, A.ones_words[4 * s + 2], (uint32_t)h0);
-                h0 = (int)__dp4a(v.w, A.ones_words[4 * s + 3], (uint32_t)h0);
-            }
-            // entering bytes: columns tw .. tw+62, i.e. 80 bytes from strip tw/16 on
-            const int s0 = A.tmpl_w >> 4;
-            uint32_t e[20];
-#pragma unroll
-            for (int s = 0; s < 5; ++s) {
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (s0 + s < KS) v = *reinterpret_cast<const uint4 *>(sl + (s0 + s) * STRIP_BYTES);
-                e[4 * s] = v.x; e[4 * s + 1] = v.y; e[4 * s + 2] = v.z; e[4 * s + 3] = v.w;
-            }
-            const uint32_t o = (uint32_t)A.tmpl_w & 15, ws = o >> 2, bs = (o & 3) * 8;
-            uint32_t t[17], g[16];
-#pragma unroll
-            for (int j = 0; j < 17; ++j)
-                t[j] = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) g[j] = __funnelshift_r(t[j], t[j + 1], bs);
-            int h = h0;
-            const int sw = row & 31;
-#pragma unroll
-            for (int xp = 0; xp < 32; ++xp) {
-                const int xa = 2 * xp, xb = 2 * xp + 1;
-                const uint32_t lo = (uint32_t)h;
-                h += (int)((g[xa >> 2] >> (8 * (xa & 3))) & 255) - (int)((w[xa >> 2] >> (8 * (xa & 3))) & 255);
-                const uint32_t hi = (uint32_t)h;
-                h += (int)((g[xb >> 2] >> (8 * (xb & 3))) & 255) - (int)((w[xb >> 2] >> (8 * (xb & 3))) & 255);
-                Hb[xp ^ sw] = lo | (hi << 16);
-            }
-        }
-        __syncthreads();
-
-        // ---- 3b. vertical: S(y, x) = sum_{i<th} H(y+i, x); thread = (slot, segment, x pair) --
-        // S goes into the (now dead) slab of the slot, x-major: S[x * SROWS + y]
-        {
-            const int slot = tid >> 8, seg = (tid >> 5) & 7, xp = lane;
-            const Item it = slot ? items[1] : items[0];
-            const uint32_t *Hb = reinterpret_cast<const uint32_t *>(smem + SMEM_B + slot * 32768);
-            uint32_t *S = reinterpret_cast<uint32_t *>(smem + SMEM_SLABS + slot * SLAB_BYTES);
-            const int rs = (it.h_c + 7) >> 3;
-            const int ya = seg * rs, yb = min(it.h_c, ya + rs);
-            if (ya < yb) {
-                uint32_t s0 = 0, s1 = 0;
-                for (int i = 0; i < A.tmpl_h; ++i) {
-                    const int row = ya + i;
-                    const uint32_t v = Hb[row * 32 + (xp ^ (row & 31))];
-                    s0 += v & 0xffff; s1 += v >> 16;
-                }
-                for (int y = ya; y < yb; ++y) {
-                    S[(2 * xp) * SROWS + y] = s0;
-                    S[(2 * xp + 1) * SROWS + y] = s1;
-                    const int rin = y + A.tmpl_h;
-                    const uint32_t vin = Hb[rin * 32 + (xp ^ (rin & 31))];      // row <= 255 always
-                    const uint32_t vout = Hb[y * 32 + (xp ^ (y & 31))];
-                    s0 += (vin & 0xffff) - (vout & 0xffff);
-                    s1 += (vin >> 16) - (vout >> 16);
-                }
-            }
-        }
-        __syncthreads();
-
-        // ---- 4. drain: scores + arg-max ----------------------------------------------------
-        const int qd = warp & 3, acc = warp >> 2, slot = acc >> 1, mt = acc & 1;
+        // ---- epilogue set-up (runs while the MMAs do) -----------------------------------------
+        // warp -> TMEM lane quadrant qd (hardware rule: warp % 4), item slot, half of the columns.
+        // Lane pair (2j, 2j+1) holds D[2x][.] and D[2x+1][.] of result column x = 16 qd + j; of
+        // every 16-row chunk the even lane scores rows 0..7 and the odd lane rows 8..15, so each
+        // needs 8 window sums per chunk: all of a warp's window sums are fetched up front.
+        const int qd = warp & 3, slot = (warp >> 2) & 1, half = warp >> 3;
         const Item it = slot ? items[1] : items[0];
-        const bool active = it.valid && mt < it.n_mt;
-        const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(acc * BN);
-        uint32_t *xchg = reinterpret_cast<uint32_t *>(smem + SMEM_B);      // [16 warps][64]
-        if (active) {
-            // lane 0's D_1 row (tile row 32*qd) is the "row below" of the previous quadrant's lane 31
+        const int n_chunks = it.n_cols >> 4;
+        const int c_mid = (n_chunks + 1) >> 1;
+        const int c0 = half ? c_mid : 0, c1 = half ? n_chunks : c_mid;      // <= 5 chunks
+        const int x = 16 * qd + (lane >> 1);                       // result column inside the item
+        const int odd = lane & 1;
+        const bool col_ok = it.valid && x < it.w_c;
+        const uint32_t *S = A.wsum + (size_t)(2 * pass + slot) * WSUM_WORDS + (size_t)x * WS_PITCH + 8 * odd;
+        uint4 sw[5][2];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t v[16];
-                tmem_ld16(taddr + 64 + 16 * c, v);
-                tmem_ld_wait();
-                if (lane == 0)
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) xchg[warp * 64 + 16 * c + i] = v[i];
+        for (int k = 0; k < 5; ++k)
+            if (c0 + k < c1 && col_ok) {
+                sw[k][0] = __ldg(reinterpret_cast<const uint4 *>(S + 16 * (c0 + k)));
+                sw[k][1] = __ldg(reinterpret_cast<const uint4 *>(S + 16 * (c0 + k)) + 1);
             }
+
+        mbar_wait(smem_u32(&ctrl->accum), pass_count & 1);
+        tc_fence_after();
+        if (tl && tid == 64) tl[3] = clock64();
+        // every MMA of this pass has completed: slabs and Toeplitz ring are free again
+        if (tid == 0 && has_next) {
+            load_slabs(pass + gridDim.x);
+            for (int p = 0; p < n_pre; ++p) load_stage(stage_count + (uint32_t)p, p);
         }
-        __syncthreads();
-        u64 best = 0;
-        if (active) {
-            const int trow = 32 * qd + lane;
-            const int yl = (mt ? it.off1 : 0) + trow;                  // row inside the work item
-            const bool row_ok = trow < 127 && yl < it.h_c && (mt == 0 || yl >= 127);
-            const uint32_t *S = reinterpret_cast<const uint32_t *>(smem + SMEM_SLABS + slot * SLAB_BYTES);
-            const uint32_t row_index = (uint32_t)(it.y0 + yl) * (uint32_t)A.geom.res_w + (uint32_t)it.x0;
-            float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
-            long long thr = -0x7fffffffffffffffll - 1;
+        __syncwarp();
+
+        // ---- drain: numerators + arg-max -------------------------------------------------------
+        const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(slot * NCOLS);
+        long long best_num = 0;
+        uint32_t best_idx = 0;
+        bool has = false;
+        float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
+        if (it.valid) {
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t d0[16], d1[16];
-                tmem_ld16(taddr + 16 * c, d0);
-                tmem_ld16(taddr + 64 + 16 * c, d1);
-                tmem_ld_wait();
+            for (int k = 0; k < 5; ++k) {
+                const int c = c0 + k;
+                if (c < c1) {                                // warp-uniform
+                    // 17 columns y0 .. y0+16 of this lane's row: even lanes use D[2x][y0 + i] = d[i],
+                    // odd lanes D[2x+1][y0 + 1 + i] = d[i + 1]
+                    uint32_t d16[16], d[17];
+                    tmem_ld16(taddr + 16 * c, d16);
+                    tmem_ld1(taddr + 16 * c + 16, d[16]);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int x = 16 * c + i;
-                    uint32_t below = __shfl_down_sync(0xffffffffu, d1[i], 1);
-                    if (lane == 31) below = qd < 3 ? xchg[(warp + 1) * 64 + x] : 0u;
-                    if (row_ok && x < it.w_c) {
-                        const long long sum_tl = (long long)(int)(d0[i] + below);
-                        const long long sum_win = (long long)S[x * SROWS + yl];
-                        const long long num = A.n_t * sum_tl - A.sum_t * sum_win;
-                        if (WRITE_MAP || num >= thr) {
-                            const float v = __double2float_rn(__ddiv_rn((double)num, (double)A.n_t));
-                            if (WRITE_MAP) map[row_index + (uint32_t)x] = v;
-                            const u64 key = melf_score_key(v, row_index + (uint32_t)x);
-                            if (key > best) {
-                                best = key;
-                                // a later value can only tie or beat this one if it is within two
-                                // float32 ulps of it; (|num| + n_t) >> 21 is 4x that, in num units
-                                const long long mag = (num < 0 ? -num : num) + A.n_t;
-                                thr = num - (mag >> 21) - 1;
+                    for (int i = 0; i < 16; ++i) d[i] = d16[i];
+                    const uint32_t swv[8] = {sw[k][0].x, sw[k][0].y, sw[k][0].z, sw[k][0].w,
+                                             sw[k][1].x, sw[k][1].y, sw[k][1].z, sw[k][1].w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        // even sends D[2x][y0+8+j] and receives D[2x+1][y0+j+1]; odd the other way round
+                        const uint32_t other = __shfl_xor_sync(0xffffffffu, odd ? d[j + 1] : d[8 + j], 1);
+                        const uint32_t mine = odd ? d[9 + j] : d[j];
+                        const int yl = 16 * c + 8 * odd + j;
+                        if (col_ok && yl < it.h_c) {
+                            const long long sum_tl = (long long)(int)(mine + other);
+                            const long long num = A.n_t * sum_tl - A.sum_t * (long long)swv[j];
+                            const uint32_t idx = (uint32_t)(it.y0 + yl) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
+                            if (WRITE_MAP) map[idx] = score_of(num, A.n_t);
+                            // this lane visits raster indices in increasing order, so a candidate replaces
+                            // the running best only if its float32 score is strictly greater; scores are a
+                            // monotone function of the numerator, and more than 4 float32 ulps of numerator
+                            // distance ((|num| + n_t) >> 21) always separates the rounded values
+                            if (!has) { best_num = num; best_idx = idx; has = true; }
+                            else if (num > best_num) {
+                                const long long mag = (best_num < 0 ? -best_num : best_num) + A.n_t;
+                                if (num - best_num > (mag >> 21) + 1 || score_of(num, A.n_t) > score_of(best_num, A.n_t)) {
+                                    best_num = num; best_idx = idx;
+                                }
                             }
                         }
                     }
                 }
             }
         }
+        if (tl && tid == 64) tl[4] = clock64();
+        u64 best = has ? melf_score_key(score_of(best_num, A.n_t), best_idx) : 0ull;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
             best = other > best ? other : best;
         }
-        if (lane == 0) ctrl->red[warp] = best;
+        if (lane == 0) ctrl->red[pass_count & 1][warp] = best;
+        if (tl && tid == 64) tl[5] = clock64();
         tc_fence_before();
-        __syncthreads();
+        __syncthreads();            // TMEM fully read before the next pass's first MMA overwrites it
         tc_fence_after();
+        if (tl && tid == 64) tl[6] = clock64();
         if (tid < 2) {
+            // warps of slot s: 4 s .. 4 s + 3 and 8 + 4 s .. 8 + 4 s + 3
             const Item mine = tid ? items[1] : items[0];
             u64 b = 0;
             for (int w8 = 0; w8 < 8; ++w8) {
-                const u64 k = ctrl->red[tid * 8 + w8];
+                const u64 k = ctrl->red[pass_count & 1][(w8 & 3) + 4 * tid + 8 * (w8 >> 2)];
                 b = k > b ? k : b;
             }
             if (mine.valid && b) atomicMax(A.match_key + mine.frame, b);
         }
-        // the next pass overwrites the slabs (S tables) and red[]: every reader is past the
-        // barrier above except the two atomics, which only read red[]
-        __syncthreads();
+        __syncwarp();               // red[] alternates per pass: no thread can be two passes behind
     }
 
     tc_fence_before();
@@ -506,27 +620,27 @@ size_t melf_match_tc_toeplitz_bytes(int tmpl_h)
     return (size_t)((tmpl_h + 1) / 2) * BSTAGE_BYTES;
 }
 
-// Toeplitz operand image: [pair p][strip s][n 0..127][16 bytes]; n < 64: template row 2p,
-// n >= 64: template row 2p+1 (zero beyond the template); byte b of strip s is K index
-// k = 16 s + b and holds T(row, k - (n mod 64)).
+// Toeplitz operand image: [pair p][strip s][m 0..127][16 bytes]; row m = 2 n + q belongs to
+// result column n and template row 2p + q (zero beyond the template); byte b of strip s is
+// K index k = 16 s + b and holds T(2p + q, k - n).
 void melf_match_tc_build_toeplitz(const uint8_t *tmpl, int tmpl_w, int tmpl_h, uint8_t *out)
 {
     const int n_pairs = (tmpl_h + 1) / 2;
     for (int p = 0; p < n_pairs; ++p)
         for (int s = 0; s < KS; ++s)
-            for (int n = 0; n < BN; ++n)
+            for (int m = 0; m < BM; ++m)
                 for (int b = 0; b < 16; ++b) {
-                    const int row = 2 * p + (n >> 6), j = 16 * s + b - (n & 63);
+                    const int row = 2 * p + (m & 1), j = 16 * s + b - (m >> 1);
                     uint8_t v = 0;
                     if (row < tmpl_h && j >= 0 && j < tmpl_w) v = tmpl[(size_t)row * tmpl_w + j];
-                    out[(((size_t)p * KS + s) * BN + n) * 16 + b] = v;
+                    out[(((size_t)p * KS + s) * BM + m) * 16 + b] = v;
                 }
 }
 
 // fills the tiling fields of args; returns the number of passes
 long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames)
 {
-    const int max_h = SLAB_ROWS - a.tmpl_h;            // rows r + 2p <= h_c + th - 1 <= 255
+    const int max_h = SLAB_DATA_ROWS - a.tmpl_h;       // image rows r + i <= h_c + th - 2 <= 254
     const int cap = max_h < SROWS ? max_h : SROWS;
     a.n_tx = (a.geom.res_w + 63) / 64;
     a.n_ty = (a.geom.res_h + cap - 1) / cap;
@@ -542,24 +656,37 @@ long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames)
     return (a.n_items + 1) / 2;
 }
 
-cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, long long n_pass, int num_sms,
-                                 cudaStream_t stream)
+size_t melf_match_tc_scratch_bytes(long long max_items, size_t *wsum_offset)
 {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(melf_match_tc_kernel<false>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(melf_match_tc_kernel<true>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    const size_t slabs = (size_t)max_items * SLAB_BYTES;
+    if (wsum_offset) *wsum_offset = slabs;
+    return slabs + (size_t)max_items * WSUM_WORDS * sizeof(uint32_t);
+}
+
+// prep + correlation for the items [args.item0, args.item0 + args.max_items) of the batch
+cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(melf_match_tc_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL2);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(melf_match_tc_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL2);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(melf_match_prep_kernel,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    long long n_local = args.n_items - args.item0;
+    if (n_local > args.max_items) n_local = args.max_items;
+    if (n_local <= 0) return cudaSuccess;
+    melf_match_prep_kernel<<<(unsigned)n_local, PREP_THREADS, PREP_SMEM_TOTAL, stream>>>(args);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const long long n_pass = (n_local + 1) / 2;
     const unsigned grid = (unsigned)(n_pass < num_sms ? n_pass : num_sms);
     if (args.result)
-        melf_match_tc_kernel<true><<<grid, TC_THREADS, SMEM_TOTAL, stream>>>(args);
+        melf_match_tc_kernel<true><<<grid, TC_THREADS, SMEM_TOTAL2, stream>>>(args);
     else
-        melf_match_tc_kernel<false><<<grid, TC_THREADS, SMEM_TOTAL, stream>>>(args);
+        melf_match_tc_kernel<false><<<grid, TC_THREADS, SMEM_TOTAL2, stream>>>(args);
     return cudaGetLastError();
 }
 

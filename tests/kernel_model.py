@@ -196,9 +196,13 @@ def read_dial(T, m0, neg_mom, aoz_turns):
 # Model of the tensor-core TM_CCOEFF kernel (csrc/melf_match_tc.cu): the same shared-memory
 # byte layouts (16-byte column strips), the same per-step operand addressing (a row shift
 # of the lightness slab = a 16-byte step of the descriptor start address), the same
-# Toeplitz operand image (built by the product library's host code), the same M-tile
-# offsets and D_0[y] + D_1[y+1] epilogue.  numpy int64 stands in for tcgen05.mma.
+# Toeplitz operand image (built by the product library's host code; A operand, row
+# m = 2 n + q), the slab as the N-side operand with N = round16(h_c + 1), and the
+# D[2x][y] + D[2x+1][y+1] epilogue.  numpy int64 stands in for tcgen05.mma.
 # ---------------------------------------------------------------------------------------
+SLAB_ROWS = 264
+
+
 def match_tc_model(light, toeplitz, tmpl_w, tmpl_h, plan):
     """light: (crop_h, crop_w) u8; toeplitz: bytes from melf_host_match_tc_toeplitz;
     plan = (n_tx, n_ty, chunk_h, n_pairs).  Returns sum T*L for every result position."""
@@ -213,29 +217,25 @@ def match_tc_model(light, toeplitz, tmpl_w, tmpl_h, plan):
             (x0, y0) = (tx * 64, ty * chunk_h)
             (w_c, h_c) = (min(64, res_w - x0), min(chunk_h, res_h - y0))
             assert 1 <= h_c <= 137 and h_c + tmpl_h - 1 <= 255
+            n_cols = (h_c + 1 + 15) // 16 * 16
             # slab[strip][row][16]: zero outside the crop
-            slab = np.zeros((16, 256, 16), np.int64)
+            slab = np.zeros((16, SLAB_ROWS, 16), np.int64)
             for s in range(16):
                 for b in range(16):
                     cx = x0 + 16 * s + b
                     if cx < crop_w:
-                        rows = min(256, crop_h - y0)
+                        rows = min(SLAB_ROWS, crop_h - y0)
                         slab[s, :rows, b] = light[y0:y0 + rows, cx]
-            tiles = [(0, 0)] + ([(1, h_c - 127)] if h_c > 127 else [])
-            for (mt, off) in tiles:
-                acc = np.zeros((128, 128), np.int64)
-                for p in range(n_pairs):
-                    row0 = off + 2 * p
-                    assert row0 + 127 <= 255
-                    for ks in range(8):
-                        # A[m][k] = slab[2ks + k // 16][row0 + m][k % 16], k < 32
-                        a = np.concatenate([slab[2 * ks, row0:row0 + 128], slab[2 * ks + 1, row0:row0 + 128]], axis=1)
-                        b = np.concatenate([toep[p, 2 * ks], toep[p, 2 * ks + 1]], axis=1)    # [n][k]
-                        acc += a @ b.T
-                for t in range(127):
-                    yl = off + t
-                    if yl >= h_c or (mt == 1 and yl < 127):
-                        continue
-                    out[y0 + yl, x0:x0 + w_c] = acc[t, :w_c] + acc[t + 1, 64:64 + w_c]
+            acc = np.zeros((128, n_cols), np.int64)
+            for p in range(n_pairs):
+                row0 = 2 * p
+                assert row0 + n_cols <= SLAB_ROWS
+                for ks in range(8):
+                    # A[m][k] = toep[p][2ks + k // 16][m][k % 16]; B[r][k] = slab[2ks + k // 16][row0 + r][k % 16]
+                    a = np.concatenate([toep[p, 2 * ks], toep[p, 2 * ks + 1]], axis=1)
+                    b = np.concatenate([slab[2 * ks, row0:row0 + n_cols], slab[2 * ks + 1, row0:row0 + n_cols]], axis=1)
+                    acc += a @ b.T
+            for yl in range(h_c):
+                out[y0 + yl, x0:x0 + w_c] = acc[0:2 * w_c:2, yl] + acc[1:2 * w_c:2, yl + 1]
     assert (out >= 0).all()
     return out
