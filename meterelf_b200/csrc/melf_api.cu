@@ -51,6 +51,7 @@ struct melf_ctx {
     uint32_t *d_ones_words = nullptr;
     uint8_t *d_toeplitz = nullptr;     // tensor-core path operands (NULL: template not supported there)
     bool use_tc = false;
+    int pix_pitch = 0, pix_bytes = 0;       // per-dial shared-memory window of the dial kernel
     uint8_t *d_tc_scratch[3] = {nullptr, nullptr, nullptr};   // [0]: caller-stream path, [1], [2]: pipeline streams
     long long tc_scratch_items[3] = {0, 0, 0};
     long long sum_t = 0, n_t = 0;
@@ -226,6 +227,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     a.dials = ctx->d_dials;
     a.ring_pos = ctx->d_ring_pos; a.ring_angle = ctx->d_ring_angle; a.ring_sqd = ctx->d_ring_sqd;
     a.match_key = d_keys;
+    a.pix_pitch = ctx->pix_pitch; a.pix_bytes = ctx->pix_bytes;
     a.out = d_out;
     if (taps) a.taps = *taps; else std::memset(&a.taps, 0, sizeof a.taps);
     a.threshold = ctx->params.match_threshold;
@@ -233,8 +235,29 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     a.tmpl_w = ctx->params.tmpl_w; a.tmpl_h = ctx->params.tmpl_h;
     a.hue_shift = ctx->params.hue_shift; a.s_tail = ctx->params.s_tail;
     for (int k = 0; k < 4; k++) a.value_order[k] = ctx->params.value_order[k];
+    // MELF_DIALS_TIMELINE=<file>: debug dump of per-phase clock64 stamps (synchronises)
+    const char *tl_path = std::getenv("MELF_DIALS_TIMELINE");
+    long long *d_tl = nullptr;
+    if (tl_path) {
+        MELF_CUDA(ctx, cudaMalloc(&d_tl, 64 * sizeof(long long)));
+        MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
+        a.timeline = d_tl;
+    }
     MELF_CUDA(ctx, melf_launch_dials(a, n, stream));
     g_launches++;
+    if (d_tl) {
+        long long h_tl[64];
+        MELF_CUDA(ctx, cudaStreamSynchronize(stream));
+        MELF_CUDA(ctx, cudaMemcpy(h_tl, d_tl, sizeof h_tl, cudaMemcpyDeviceToHost));
+        cudaFree(d_tl);
+        if (FILE *fp = std::fopen(tl_path, "w")) {
+            for (int i = 0; i < 8; i++) {
+                for (int j = 0; j < 7; j++) std::fprintf(fp, "%lld ", h_tl[8 * i + j] - h_tl[8 * i]);
+                std::fprintf(fp, "\n");
+            }
+            std::fclose(fp);
+        }
+    }
     return MELF_OK;
 }
 
@@ -305,9 +328,18 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
         ctx->params.dials[d].circle_mask = nullptr;
     }
     cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
-    for (int d = 0; d < P->n_dials; d++) {
-        ctx->win_x0.push_back(dials[d].win_x0);
-        ctx->win_y0.push_back(dials[d].win_y0);
+    {
+        int max_w = 1, max_h = 1, max_ring = 0;
+        for (int d = 0; d < P->n_dials; d++) {
+            ctx->win_x0.push_back(dials[d].win_x0);
+            ctx->win_y0.push_back(dials[d].win_y0);
+            max_w = dials[d].win_w > max_w ? dials[d].win_w : max_w;
+            max_h = dials[d].win_h > max_h ? dials[d].win_h : max_h;
+            max_ring = dials[d].n_ring > max_ring ? dials[d].n_ring : max_ring;
+        }
+        ctx->pix_pitch = ((3 * max_w + 15 + 15) / 16) * 16;          // 3 w bytes at any 16-byte phase
+        const int lists = 512 + ((2 * max_ring + 15) / 16) * 16;     // momentum buffer + kept-index list
+        ctx->pix_bytes = max_h * ctx->pix_pitch > lists ? max_h * ctx->pix_pitch : lists;
     }
 
     // template, packed 4 columns per word in the layout the match kernel streams:

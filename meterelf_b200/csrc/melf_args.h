@@ -16,6 +16,8 @@ struct MelfDialsArgs {
     double threshold;
     int32_t n_dials, tmpl_w, tmpl_h, hue_shift, s_tail;
     int32_t value_order[4];
+    int32_t pix_pitch, pix_bytes; // per-dial shared-memory window: row pitch, total bytes (multiples of 16)
+    long long *timeline;         // optional debug: clock64 stamps of (frame 0 .. 7, dial 0), 8 per frame
 };
 
 struct MelfMatchArgs {

@@ -157,6 +157,8 @@ struct DialOut {
 }  // namespace
 
 
+extern __shared__ __align__(16) uint8_t melf_dials_dyn[];
+
 __global__ void __launch_bounds__(32 * MELF_MAX_DIALS)
 melf_dials_kernel(const MelfDialsArgs A)
 {
@@ -184,6 +186,8 @@ melf_dials_kernel(const MelfDialsArgs A)
         return;
     }
 
+    long long *tl = (A.timeline && f < 8 && threadIdx.x == 0) ? A.timeline + 8 * f : nullptr;
+    if (tl) tl[0] = clock64();
     const MelfDialDev &D = A.dials[d];
     // pixel (u, v) of the dials rect -> crop column/row -> frame address
     const uint8_t *frame = A.bgr + (size_t)f * A.frame_stride;
@@ -192,7 +196,9 @@ melf_dials_kernel(const MelfDialsArgs A)
         const int cx = mx + u, cy = my + v;
         const uint8_t *p = frame + (size_t)(A.geom.crop_y0 + cy) * A.row_stride + 3 * (size_t)(A.geom.crop_x0 + cx);
         const int B = p[0], G = p[1], R = p[2];
-        return melf_hls_pixel(B, G, R, A.s_tail && melf_is_tail_col(cx, crop_w), A.hue_shift);
+        if (A.s_tail && melf_is_tail_col(cx, crop_w))       // OpenCV's scalar-tail S association
+            return melf_hls_pixel(B, G, R, true, A.hue_shift);
+        return melf_hls_arith((uint32_t)B, (uint32_t)G, (uint32_t)R, A.hue_shift);
     };
 
     // ---- get_dial_color: rounded mean of the 5x5 patch at int(centre) -----------------
@@ -210,22 +216,59 @@ melf_dials_kernel(const MelfDialsArgs A)
     const int lo_l = max(col_l - D.range_l, 0), hi_l = min(col_l + D.range_l, 255);
     const int lo_s = max(col_s - D.range_s, 0), hi_s = min(col_s + D.range_s, 255);
 
-    // ---- inRange over the window -> row words ----------------------------------------
+    if (tl) tl[1] = clock64();
+    // ---- stage the window's BGR bytes in shared memory ----------------------------------
+    // Row r of the window occupies 3 * win_w bytes starting at an arbitrary address: fetch the
+    // 16-byte chunks that overlap its valid columns (all loads of all rows are independent and
+    // in flight together), keeping the chunk grid aligned to global memory so that the byte
+    // of window column c sits at pix[r * pitch + (rowaddr(r) & 15) + 3 * c].
+    uint8_t *pix = melf_dials_dyn + (size_t)d * A.pix_bytes;
     const u64 V = D.colvalid, RV = D.rowvalid;
+    const uint8_t *win0 = frame + (size_t)(A.geom.crop_y0 + my + D.win_y0) * A.row_stride +
+                          3 * (ptrdiff_t)(A.geom.crop_x0 + mx + D.win_x0);
+    {
+        const int cmin = __ffsll((long long)V) - 1, cmax = 63 - __clzll((long long)V);
+        const int n_chunk = A.pix_pitch >> 4;
+        const int sub = lane >> 4, ch = lane & 15;
+#pragma unroll 4
+        for (int r2 = 0; r2 < D.win_h; r2 += 2) {
+            const int rr = r2 + sub;
+            if (rr < D.win_h && ((RV >> rr) & 1) && ch < n_chunk && V) {
+                const uint8_t *rowp = win0 + (size_t)rr * A.row_stride;
+                const uintptr_t al = reinterpret_cast<uintptr_t>(rowp) & ~(uintptr_t)15;
+                const uintptr_t c_lo = al + 16 * (uintptr_t)ch;
+                const uintptr_t need_lo = reinterpret_cast<uintptr_t>(rowp) + 3 * (uintptr_t)cmin;
+                const uintptr_t need_hi = reinterpret_cast<uintptr_t>(rowp) + 3 * (uintptr_t)(cmax + 1);
+                if (c_lo + 16 > need_lo && c_lo < need_hi)
+                    *reinterpret_cast<uint4 *>(pix + rr * A.pix_pitch + 16 * ch) =
+                        __ldg(reinterpret_cast<const uint4 *>(c_lo));
+            }
+        }
+    }
+    __syncwarp();
+    auto hls_win = [&](int cc, int rr) -> uint32_t {
+        const uint8_t *rowp = win0 + (size_t)rr * A.row_stride;
+        const uint8_t *p = pix + rr * A.pix_pitch + (reinterpret_cast<uintptr_t>(rowp) & 15) + 3 * cc;
+        const uint32_t B = p[0], G = p[1], R = p[2];
+        const int cx = mx + D.win_x0 + cc;
+        if (A.s_tail && melf_is_tail_col(cx, crop_w))       // OpenCV's scalar-tail S association
+            return melf_hls_pixel((int)B, (int)G, (int)R, true, A.hue_shift);
+        return melf_hls_arith(B, G, R, A.hue_shift);
+    };
+
+    // ---- inRange over the window -> row words ----------------------------------------
     u64 m0a = 0, m0b = 0;
+#pragma unroll 2
     for (int rr = 0; rr < D.win_h; ++rr) {
         u64 word = 0;
         if ((RV >> rr) & 1) {
-            const int v = D.win_y0 + rr;
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
                 const int cc = lane + 32 * half;
-                bool bit = false;
-                if (cc < D.win_w && ((V >> cc) & 1)) {
-                    const uint32_t c = hls_at(D.win_x0 + cc, v);
-                    const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
-                    bit = H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
-                }
+                const bool valid = cc < D.win_w && ((V >> cc) & 1);
+                const uint32_t c = hls_win(valid ? cc : 0, rr);
+                const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
+                const bool bit = valid && H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
                 const uint32_t bal = __ballot_sync(0xffffffffu, bit);
                 word |= (u64)bal << (32 * half);
             }
@@ -233,6 +276,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         if ((rr >> 1) == lane) { if (rr & 1) m0b = word; else m0a = word; }
     }
 
+    if (tl) tl[2] = clock64();
     // ---- 3x3 dilate then erode (pixels outside the dials rect do not take part) -------
     const bool rva = (RV >> (2 * lane)) & 1, rvb = (RV >> (2 * lane + 1)) & 1;
     u64 era, erb;
@@ -248,6 +292,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         erb = rvb ? ((pa & pb & pdn) & V) : 0;
     }
 
+    if (tl) tl[3] = clock64();
     // ---- components: largest filled area wins, first discovered wins ties -------------
     u64 rem_a = era & D.disc_nb[2 * lane], rem_b = erb & D.disc_nb[2 * lane + 1];
     u64 best_a = 0, best_b = 0;
@@ -269,6 +314,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         rem_a &= ~fa; rem_b &= ~fb;
     }
 
+    if (tl) tl[4] = clock64();
     DialOut res;
     res.pos = __longlong_as_double(0x7ff8000000000000ll);
     res.flag = 0;
@@ -284,114 +330,109 @@ melf_dials_kernel(const MelfDialsArgs A)
         nm_b = best_area2 > 200 ? best_b : erb;
 
         // ---- momentum (_reading.py:32-41): sequential sums in raster order -----------
+        // Per row: the lanes compact the x terms of the set pixels into a small shared buffer
+        // (lane j owns columns j and j + 32), then every lane runs the same dependent chain of
+        // float64 additions over it, in the reference's raster order.  The loads of the chain
+        // do not depend on the sums, so only the DADD latency remains on the critical path.
         const u64 np_a = nm_a & D.disc[2 * lane], np_b = nm_b & D.disc[2 * lane + 1];
         n_needle = __reduce_add_sync(0xffffffffu, __popcll(np_a) + __popcll(np_b));
-        uint32_t lanes = __ballot_sync(0xffffffffu, (np_a | np_b) != 0);
-        while (lanes) {
-            const int l = __ffs(lanes) - 1;
-            lanes &= lanes - 1;
+        {
+            double *tbuf = reinterpret_cast<double *>(pix);             // 64 doubles; the pixel bytes are dead
+            const double tx_lo = D.termx[lane], tx_hi = D.termx[lane + 32];
+            const uint32_t below = (1u << lane) - 1u;
+            uint32_t lanes = __ballot_sync(0xffffffffu, (np_a | np_b) != 0);
+            while (lanes) {
+                const int l = __ffs(lanes) - 1;
+                lanes &= lanes - 1;
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                u64 w = shfl_u64(half ? np_b : np_a, l);
-                const double ty = D.termy[2 * l + half];
-                while (w) {
-                    const int c = __ffsll((long long)w) - 1;
-                    w &= w - 1;
-                    mom_x = __dadd_rn(mom_x, D.termx[c]);
-                    mom_y = __dadd_rn(mom_y, ty);
+                for (int half = 0; half < 2; ++half) {
+                    const u64 w = shfl_u64(half ? np_b : np_a, l);
+                    if (!w) continue;                                    // warp-uniform
+                    const uint32_t wl = (uint32_t)w, wh = (uint32_t)(w >> 32);
+                    const int n_lo = __popc(wl), n = n_lo + __popc(wh);
+                    __syncwarp();                                       // previous row's reads are done
+                    if ((wl >> lane) & 1) tbuf[__popc(wl & below)] = tx_lo;
+                    if ((wh >> lane) & 1) tbuf[n_lo + __popc(wh & below)] = tx_hi;
+                    __syncwarp();
+                    const double ty = D.termy[2 * l + half];
+#pragma unroll 4
+                    for (int i = 0; i < n; ++i) {
+                        mom_x = __dadd_rn(mom_x, tbuf[i]);
+                        mom_y = __dadd_rn(mom_y, ty);
+                    }
                 }
             }
+            __syncwarp();
         }
         const double sgn = D.neg_mom ? -1.0 : 1.0;
         mom_angle = angle_by_vector(sgn * mom_x, sgn * mom_y);
 
+        if (tl) tl[5] = clock64();
         // ---- ring pixels (_reading.py:51-96) ------------------------------------------
+        // One traversal of the (angle, squared distance)-sorted ring table compacts the indices
+        // of the kept entries into shared memory; the first kept entry has the minimum angle.
         nm_s[d][2 * lane] = nm_a;
         nm_s[d][2 * lane + 1] = nm_b;
         __syncwarp();
         const uint16_t *rpos = A.ring_pos + D.ring_off;
         const double *rang = A.ring_angle + D.ring_off;
         const double *rsqd = A.ring_sqd + D.ring_off;
+        uint16_t *klist = reinterpret_cast<uint16_t *>(pix + 512);     // <= n_ring entries (host sizes pix_bytes)
         double min_angle = 0.0;
+        int n_unwrapped = 0;
         for (int base = 0; base < D.n_ring; base += 32) {
             const int e = base + lane;
-            bool kept = false;
+            bool kept = false, wrapped = false;
             double a = 0.0;
             if (e < D.n_ring) {
                 const int pos = rpos[e];
-                a = rang[e];
-                kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
+                if ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) {
+                    a = rang[e];
+                    kept = near_momentum(a, mom_angle);
+                }
             }
             const uint32_t bal = __ballot_sync(0xffffffffu, kept);
             if (n_kept == 0 && bal) min_angle = __shfl_sync(0xffffffffu, a, __ffs(bal) - 1);
+            if (kept) {
+                wrapped = !(fabs(__dsub_rn(a, min_angle)) < 0.75);
+                klist[n_kept + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)e;
+            }
+            // wrapped entries have the largest angles, i.e. they form the tail of the kept list
+            n_unwrapped += __popc(__ballot_sync(0xffffffffu, kept && !wrapped));
             n_kept += __popc(bal);
         }
+        __syncwarp();
         if (n_kept == 0) {
             res.flag = 2;                                // _reading.py:79-81
         } else {
             double num = 0.0, den = 0.0;
             if (n_kept >= 5) {
-                // sorted()[cut:-cut]: the table is already in sorted order; entries that
-                // get "a - 1" come first (their keys are negative), in table order
+                // sorted()[cut:-cut] (_reading.py:86-91): the wrapped entries ("a - 1", negative
+                // keys) come first, then the others, each group in table order
                 const int cut = min(2, (n_kept - 3) / 2);
-                const int k_lo = cut, k_hi = n_kept - cut;
-                int k = 0;
-                for (int pass = 1; pass >= 0; --pass) {
-                    for (int base = 0; base < D.n_ring; base += 32) {
-                        const int e = base + lane;
-                        bool sel = false;
-                        double a = 0.0, sq = 0.0;
-                        if (e < D.n_ring) {
-                            const int pos = rpos[e];
-                            a = rang[e];
-                            sq = rsqd[e];
-                            const bool kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
-                            const bool wrapped = !(fabs(__dsub_rn(a, min_angle)) < 0.75);
-                            sel = kept && (wrapped == (pass == 1));
-                            if (wrapped) a = __dsub_rn(a, 1.0);
-                        }
-                        uint32_t bal = __ballot_sync(0xffffffffu, sel);
-                        while (bal) {
-                            const int src = __ffs(bal) - 1;
-                            bal &= bal - 1;
-                            if (k >= k_lo && k < k_hi) {
-                                const double aa = __shfl_sync(0xffffffffu, a, src);
-                                const double dd = __shfl_sync(0xffffffffu, sq, src);
-                                num = __dadd_rn(num, __dmul_rn(aa, dd));
-                                den = __dadd_rn(den, dd);
-                            }
-                            ++k;
-                        }
-                    }
+                const int n_wrapped = n_kept - n_unwrapped;
+#pragma unroll 4
+                for (int k = cut; k < n_kept - cut; ++k) {
+                    const bool w = k < n_wrapped;
+                    const int e = klist[w ? n_unwrapped + k : k - n_wrapped];
+                    double aa = rang[e];
+                    if (w) aa = __dsub_rn(aa, 1.0);
+                    const double dd = rsqd[e];
+                    num = __dadd_rn(num, __dmul_rn(aa, dd));
+                    den = __dadd_rn(den, dd);
                 }
             } else {
                 // fewer than 5: no sort, the reference sums in raster order of the points
                 double ea[4], ed[4];
                 int ep[4];
-                int k = 0;
-                for (int base = 0; base < D.n_ring; base += 32) {
-                    const int e = base + lane;
-                    bool kept = false;
-                    double a = 0.0, sq = 0.0;
-                    int pos = 0;
-                    if (e < D.n_ring) {
-                        pos = rpos[e];
-                        a = rang[e];
-                        sq = rsqd[e];
-                        kept = ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) && near_momentum(a, mom_angle);
-                        if (!(fabs(__dsub_rn(a, min_angle)) < 0.75)) a = __dsub_rn(a, 1.0);
-                    }
-                    uint32_t bal = __ballot_sync(0xffffffffu, kept);
-                    while (bal) {
-                        const int src = __ffs(bal) - 1;
-                        bal &= bal - 1;
-                        const double aa = __shfl_sync(0xffffffffu, a, src);
-                        const double dd = __shfl_sync(0xffffffffu, sq, src);
-                        const int pp = __shfl_sync(0xffffffffu, pos, src);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                            if (q == k) { ea[q] = aa; ed[q] = dd; ep[q] = pp; }
-                        ++k;
+                for (int q = 0; q < 4; ++q) {
+                    ea[q] = 0.0; ed[q] = 0.0; ep[q] = 0x7fffffff;
+                    if (q < n_kept) {
+                        const int e = klist[q];
+                        double aa = rang[e];
+                        if (!(fabs(__dsub_rn(aa, min_angle)) < 0.75)) aa = __dsub_rn(aa, 1.0);
+                        ea[q] = aa; ed[q] = rsqd[e]; ep[q] = rpos[e];
                     }
                 }
                 // insertion sort of <= 4 entries by raster position
@@ -417,6 +458,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         }
     }
 
+    if (tl) tl[6] = clock64();
     // ---- taps --------------------------------------------------------------------------
     const size_t fd = (size_t)f * A.n_dials + d;
     if (A.taps.d_mask_orig) { A.taps.d_mask_orig[fd * 64 + 2 * lane] = m0a; A.taps.d_mask_orig[fd * 64 + 2 * lane + 1] = m0b; }
@@ -477,6 +519,10 @@ melf_dials_kernel(const MelfDialsArgs A)
 // host launcher (called from melf_api.cu)
 cudaError_t melf_launch_dials(const MelfDialsArgs &args, int n_frames, cudaStream_t stream)
 {
-    melf_dials_kernel<<<n_frames, 32 * args.n_dials, 0, stream>>>(args);
+    const int smem = args.n_dials * args.pix_bytes;
+    cudaError_t e = cudaFuncSetAttribute(melf_dials_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         smem > 48 * 1024 ? smem : 48 * 1024);
+    if (e != cudaSuccess) return e;
+    melf_dials_kernel<<<n_frames, 32 * args.n_dials, smem, stream>>>(args);
     return cudaGetLastError();
 }
