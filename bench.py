@@ -5,7 +5,8 @@
 
 One "step" = one pass of the whole path (locate dials + read 4 dials + value) over one
 HBM-resident synthetic batch (default 4096 frames of 640x480x3 u8 per GPU = 3.77 GB,
-larger than L2, so no flush between steps).  Frames are "S-planted" (SURVEY.md 8d):
+larger than L2, so no flush between steps; --size 1280x720 gives BASELINE.json's second
+throughput config, 32768 frames split over the GPUs).  Frames are "S-planted" (SURVEY.md 8d):
 uniform noise canvases with decoded sample meter crops pasted at the meter_rect with a
 seeded +-6 px jitter, so every stage runs on every frame and the expected readings are
 known.  Prints ONE JSON line (rank 0).  Frames shard by index over the GPUs: no data-path
@@ -27,7 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, 'tests'))
 
 METRIC = 'meter readings/sec (640x480 frames)'
 UNIT = 'frames/s'
-FRAME_H, FRAME_W = 640, 480        # the sample frames are portrait: 480 wide, 640 tall
+FRAME_H, FRAME_W = 640, 480        # default: the sample frames are portrait, 480 wide x 640 tall
 SMI_QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
              'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
@@ -42,11 +43,17 @@ def load_peaks():
     return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source='fallback')
 
 
+def set_frame_size(size):
+    global FRAME_H, FRAME_W
+    (w, h) = (int(v) for v in size.lower().split('x'))
+    (FRAME_H, FRAME_W) = (h, w)
+
+
 def workload_config(frames):
     return {
-        'workload': 'synthetic %dx%d BGR batch of %d frames per GPU, S-planted sample meter '
+        'workload': 'synthetic %dx%d (w x h) BGR batch of %d frames per GPU, S-planted sample meter '
                     'crops (sample-images1 params, meter_rect 250x250, template 188x119)'
-                    % (FRAME_H if False else 640, 480, frames),
+                    % (FRAME_W, FRAME_H, frames),
         'frames_per_gpu': frames, 'frame_h': FRAME_H, 'frame_w': FRAME_W,
         'bytes_per_frame': FRAME_H * FRAME_W * 3,
         'l2': 'batch (%.2f GB) is larger than L2; no flush between steps' % (
@@ -157,7 +164,7 @@ def run_reference(args):
     from helpers import golden_set
     gs = golden_set(1)
     cores = len(os.sched_getaffinity(0))
-    sample = max(cores * 4, 64)
+    sample = max(cores * 64, 256)              # ~1.5 s of CPU work per step
     frames = make_frames_host(gs, valid_crops(gs), sample, seed=1234)
     times = []
     for i in range(args.warmup + args.steps):
@@ -177,6 +184,16 @@ def run_reference(args):
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
     print(json.dumps(line))
+
+
+def load_traffic():
+    """dram__bytes_read + dram__bytes_write per launch from the committed ncu capture
+    (tools/ncu_summary.py traffic ... > profiles/r01_traffic.json); None when absent."""
+    path = os.path.join(ROOT, 'profiles', 'r01_traffic.json')
+    if os.path.exists(path):
+        with open(path) as fp:
+            return json.load(fp)
+    return {}
 
 
 def run_ours(args):
@@ -215,7 +232,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    warmup = max(args.warmup, 3)
+    for _ in range(warmup):
         step()
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
@@ -238,23 +256,15 @@ def run_ours(args):
     res = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n)
     n_ok = int(np.sum(res['status'] == 0))
 
-    # ---- the dominant kernel alone: TM_CCOEFF locate (BGR in, lightness on the fly) -----
-    d_xy = torch.zeros((n, 2), dtype=torch.int32, device=device)
-    d_val = torch.zeros((n,), dtype=torch.float32, device=device)
-
-    def match_only():
-        eng.match_template_device(d_frames.data_ptr(), 3, n, FRAME_H, FRAME_W, row_stride,
-                                  frame_stride, True, d_xy.data_ptr(), d_val.data_ptr(), 0,
-                                  stream.cuda_stream)
-    match_only()
-    torch.cuda.synchronize()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record(stream)
-    for _ in range(args.steps):
-        match_only()
-    k1.record(stream)
-    torch.cuda.synchronize()
-    match_ms = k0.elapsed_time(k1) / args.steps
+    # ---- per-kernel durations: the same steps again with CUDA events around every launch --
+    ksteps = max(3, min(args.steps, 20))
+    eng.profile_enable(True)
+    for _ in range(ksteps):
+        step()
+    prof = eng.profile_read()
+    eng.profile_enable(False)
+    kernel_ms = {k: (v[0] / ksteps) for (k, v) in prof.items() if v[1]}
+    kernel_launches = {k: v[1] // ksteps for (k, v) in prof.items() if v[1]}
 
     # ---- stage 1 as a standalone fused pass over the full frames (5 B/px) ---------------
     nconv = min(n, 1024)
@@ -268,48 +278,50 @@ def run_ours(args):
     for _ in range(3):
         convert_only()
     torch.cuda.synchronize()
+    csteps = max(5, min(args.steps, 50))
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     c0.record(stream)
-    for _ in range(args.steps):
+    for _ in range(csteps):
         convert_only()
     c1.record(stream)
     torch.cuda.synchronize()
-    conv_ms = c0.elapsed_time(c1) / args.steps
+    conv_ms = c0.elapsed_time(c1) / csteps
     clocks = sampler.stop() if sampler else None
+    del d_l, d_m
 
     # ---- end to end through the public host API: pinned host frames in, results out -----
-    e2e = None
-    if rank == 0 or world > 1:
-        n_e2e = min(n, args.e2e_frames)
-        h_frames = torch.empty((n_e2e, FRAME_H, FRAME_W, 3), dtype=torch.uint8).pin_memory()
-        h_frames.copy_(d_frames[:n_e2e])
-        h_np = h_frames.numpy()
-        eng.read_frames(h_np[:64])
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            h_res = eng.read_frames(h_np)
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        te = torch.tensor([dt], dtype=torch.float64, device=device)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        (x0, y0, x1, y1) = gs.meter_rect
-        e2e = {'value': world * n_e2e * args.steps / float(te.item()), 'unit': UNIT,
-               'h2d_bytes_per_step': int(n_e2e * (y1 - y0) * (x1 - x0) * 3),
-               'd2h_bytes_per_step': int(n_e2e * _engine.RESULT_DTYPE.itemsize),
-               'frames_per_step': n_e2e,
-               'note': 'melf_read_batch: pinned host frames, only meter_rect rows cross PCIe'}
-        assert np.array_equal(h_res['status'], res['status'][:n_e2e])
+    n_e2e = min(n, args.e2e_frames)
+    h_frames = torch.empty((n_e2e, FRAME_H, FRAME_W, 3), dtype=torch.uint8).pin_memory()
+    h_frames.copy_(d_frames[:n_e2e])
+    h_np = h_frames.numpy()
+    eng.read_frames(h_np[:64])
+    esteps = max(2, min(args.steps, 10))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(esteps):
+        h_res = eng.read_frames(h_np)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    te = torch.tensor([dt], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    (x0, y0, x1, y1) = gs.meter_rect
+    e2e = {'value': world * n_e2e * esteps / float(te.item()), 'unit': UNIT,
+           'h2d_bytes_per_step': int(n_e2e * (y1 - y0) * (x1 - x0) * 3),
+           'd2h_bytes_per_step': int(n_e2e * _engine.RESULT_DTYPE.itemsize),
+           'frames_per_step': n_e2e, 'steps': esteps,
+           'note': 'melf_read_batch: pinned host frames, only meter_rect rows cross PCIe '
+                   '(PCIe-bound: profiles/r01_pcie_probe.txt measures 50.4 GB/s for this copy shape)'}
+    assert np.array_equal(h_res['status'], res['status'][:n_e2e])
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- CPU baseline (oracle port) on a bounded sample, same frames -------------------
+    # ---- CPU baseline (oracle port) on a bounded sample of the same frames -------------
     cores = len(os.sched_getaffinity(0))
-    sample = min(n, max(cores * 4, 64))
+    sample = min(n, args.cpu_frames)
     host_sample = d_frames[:sample].cpu().numpy()
     (cpu_res, cpu_dt) = cpu_arm(gs, host_sample, cores)
     mism = 0
@@ -321,31 +333,60 @@ def run_ours(args):
         mism += 0 if same else 1
 
     peaks = load_peaks()
+    traffic = load_traffic()
+    step_ms = ms_total / args.steps
     rw, rh = 250 - 188 + 1, 250 - 119 + 1
     macs = rw * rh * 188 * 119
-    tops = 2.0 * macs * n / (match_ms / 1e3) / 1e12
+    tc_ms = kernel_ms.get('match_tc')
     int8_peak = 2.0 * peaks['bf16_tflops']
+    if tc_ms:
+        tops = 2.0 * macs * n / (tc_ms / 1e3) / 1e12
+        roofline = {
+            'kernel': 'melf_match_tc_kernel (TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
+            'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
+            'frac': tops / int8_peak, 'traffic': traffic.get('melf_match_tc_kernel'),
+            'ms_per_launch': tc_ms,
+            'note': 'algorithmic 2*%d op/frame x %d frames per launch (SURVEY 8d: 63x132 positions x 22372 MAC); '
+                    'peak = 2 x %s bf16 dense (int8:bf16 tensor ratio); issued MACs are 1.50x the algorithmic '
+                    'ones (K 188->256, N 133->144, M 63->64); kernel share of step %.2f'
+                    % (macs, n, peaks['source'], tc_ms / step_ms),
+        }
+    else:
+        roofline = None
     conv_bytes = 5.0 * FRAME_H * FRAME_W * nconv
     conv_gbs = conv_bytes / (conv_ms / 1e3) / 1e9
+    stage = [{
+        'kernel': 'melf_convert_tab_kernel (fused BGR->HLS + hue shift + L plane + mask, full frames)',
+        'bound': 'hbm', 'achieved': conv_gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
+        'frac': conv_gbs / peaks['hbm_gbs'], 'traffic': traffic.get('melf_convert_tab_kernel'),
+        'ms_per_launch': conv_ms,
+        'note': 'algorithmic 5 B/px x %d px; peak %s' % (FRAME_H * FRAME_W * nconv, peaks['source'])}]
+    if kernel_ms.get('match_prep'):
+        prep_bytes = n * (250 * 250 * 3 + 67584 + 64 * 144 * 4)
+        gbs = prep_bytes / (kernel_ms['match_prep'] / 1e3) / 1e9
+        stage.append({
+            'kernel': 'melf_match_prep_kernel (meter_rect BGR -> lightness slab + window sums)',
+            'bound': 'hbm', 'achieved': gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
+            'frac': gbs / peaks['hbm_gbs'], 'traffic': traffic.get('melf_match_prep_kernel'),
+            'ms_per_launch': kernel_ms['match_prep'],
+            'note': 'algorithmic 187500 B in + 67584 + 36864 B out per frame; share of step %.2f'
+                    % (kernel_ms['match_prep'] / step_ms)})
+    if kernel_ms.get('dials'):
+        stage.append({
+            'kernel': 'melf_dials_kernel (per-dial masks, contour selection, angles, value)',
+            'bound': 'issue/latency (SURVEY 8d stage 3)', 'ms_per_launch': kernel_ms['dials'],
+            'frames_per_s': n / (kernel_ms['dials'] / 1e3),
+            'traffic': traffic.get('melf_dials_kernel'),
+            'note': 'share of step %.2f' % (kernel_ms['dials'] / step_ms)})
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-        'warmup': max(args.warmup, 3), 'ms_per_step': ms_total / args.steps,
+        'warmup': warmup, 'ms_per_step': step_ms,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'u8/int32 (correlation), f32 (HLS), f64 (angles)', 'data': 'synthetic',
         'config': workload_config(n),
         'e2e': e2e, 'gpu_launches': int(launches), 'clocks': clocks,
-        'roofline': {
-            'kernel': 'melf_match_kernel (TM_CCOEFF, exact integer correlation)',
-            'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
-            'frac': tops / int8_peak, 'traffic': None,
-            'note': 'algorithmic 2*%d MAC/frame; peak = 2 x %s bf16 dense (int8 tensor rate); '
-                    'kernel share of step %.2f' % (macs, peaks['source'], match_ms / (ms_total / args.steps)),
-        },
-        'stage_rooflines': [{
-            'kernel': 'melf_convert_vec_kernel (fused BGR->HLS + hue shift + L plane + mask, full frames)',
-            'bound': 'hbm', 'achieved': conv_gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
-            'frac': conv_gbs / peaks['hbm_gbs'], 'traffic': None,
-            'note': 'algorithmic 5 B/px x %d px; peak %s' % (FRAME_H * FRAME_W * nconv, peaks['source'])}],
+        'roofline': roofline, 'stage_rooflines': stage,
+        'kernel_ms_per_step': kernel_ms, 'kernel_launches_per_step': kernel_launches,
         'cpu_baseline': {'value': sample / cpu_dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                          'sample': '%d frames of the same batch' % sample,
                          'mismatches_vs_gpu': mism},
@@ -359,12 +400,20 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--frames', type=int, default=4096, help='frames per GPU')
+    ap.add_argument('--size', default='480x640', help='frame size WxH (sample frames are 480x640; '
+                    'BASELINE.json also names 1280x720)')
+    ap.add_argument('--frames', type=int, default=0, help='frames per GPU (default 4096; '
+                    '32768 / n_gpus for 1280x720)')
     ap.add_argument('--e2e-frames', type=int, default=4096)
+    ap.add_argument('--cpu-frames', type=int, default=8192, help='CPU baseline sample (frames)')
     args = ap.parse_args()
+    set_frame_size(args.size)
+    if not args.frames:
+        world = int(os.environ.get('WORLD_SIZE', '1'))
+        args.frames = 4096 if FRAME_H * FRAME_W <= 640 * 480 else max(1, 32768 // max(world, args.gpus, 1))
     if args.impl == 'reference':
         run_reference(args)
     else:

@@ -111,6 +111,19 @@ int melf_abi_version(void);
 /* Top-left corner of dial d's 64x64 tap window in dials-rect coordinates. */
 int melf_dial_window(const melf_ctx *ctx, int dial, int32_t *win_x0, int32_t *win_y0);
 
+/* ---- measurement ----------------------------------------------------------------- */
+/* While enabled, every kernel launch of the path on this ctx is bracketed by CUDA events on
+ * its own stream.  melf_profile_read synchronises the device, adds up the elapsed
+ * milliseconds and launch counts per kernel kind since the last read and clears them.
+ * For bench.py's roofline numbers (no reference counterpart). */
+#define MELF_PROF_MATCH_PREP 0      /* melf_match_prep_kernel: lightness slabs + window sums */
+#define MELF_PROF_MATCH_TC   1      /* melf_match_tc_kernel: tcgen05 correlation + arg-max    */
+#define MELF_PROF_DIALS      2      /* melf_dials_kernel                                      */
+#define MELF_PROF_MATCH_DP4A 3      /* melf_match_kernel: dp4a correlation (large templates)  */
+#define MELF_PROF_KINDS      4
+int melf_profile_enable(melf_ctx *ctx, int on);
+int melf_profile_read(melf_ctx *ctx, float *ms /*[MELF_PROF_KINDS]*/, int32_t *launches /*[MELF_PROF_KINDS]*/);
+
 /* ---- the hot path -------------------------------------------------------------- */
 /* Batched ImageFile.get_dials_hls + get_meter_value (_image.py:23-27, _reading.py:19-115)
  * over n BGR frames of h x w pixels already resident on the device.  Frame f starts at

@@ -75,7 +75,9 @@ _lib_lock = threading.Lock()
 _SYMBOLS = (
     'melf_create', 'melf_destroy', 'melf_last_error', 'melf_abi_version',
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
-    'melf_match_template', 'melf_launch_count')
+    'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read')
+
+PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a')
 
 
 def load_library() -> C.CDLL:
@@ -119,6 +121,8 @@ def load_library() -> C.CDLL:
         lib.melf_match_template.argtypes = [
             C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
             C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
+        lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
         return lib
 
@@ -208,6 +212,16 @@ class Engine:
     def _check(self, rc: int) -> None:
         if rc:
             raise EngineError(rc, (self.lib.melf_last_error(self._ctx) or b'').decode())
+
+    def profile_enable(self, on: bool) -> None:
+        self._check(self.lib.melf_profile_enable(self._ctx, 1 if on else 0))
+
+    def profile_read(self) -> Dict[str, Tuple[float, int]]:
+        """kernel kind -> (milliseconds, launches) since the last read (synchronises)."""
+        ms = (C.c_float * len(PROFILE_KINDS))()
+        cnt = (C.c_int32 * len(PROFILE_KINDS))()
+        self._check(self.lib.melf_profile_read(self._ctx, ms, cnt))
+        return {k: (float(ms[i]), int(cnt[i])) for (i, k) in enumerate(PROFILE_KINDS)}
 
     def dial_window(self, dial: int) -> Tuple[int, int]:
         x = C.c_int32()

@@ -23,6 +23,7 @@ size_t melf_match_tc_toeplitz_bytes(int tmpl_h);
 void melf_match_tc_build_toeplitz(const uint8_t *tmpl, int tmpl_w, int tmpl_h, uint8_t *out);
 long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames);
 size_t melf_match_tc_scratch_bytes(long long max_items, size_t *wsum_offset);
+cudaError_t melf_launch_match_prep(const MelfMatchTcArgs &args, cudaStream_t stream);
 cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
@@ -52,6 +53,11 @@ struct melf_ctx {
     uint8_t *d_toeplitz = nullptr;     // tensor-core path operands (NULL: template not supported there)
     bool use_tc = false;
     int pix_pitch = 0, pix_bytes = 0;       // per-dial shared-memory window of the dial kernel
+
+    // melf_profile_*: CUDA events around every kernel launch while enabled
+    bool profiling = false;
+    struct Span { int kind; cudaEvent_t e0, e1; };
+    std::vector<Span> spans;
     uint8_t *d_tc_scratch[3] = {nullptr, nullptr, nullptr};   // [0]: caller-stream path, [1], [2]: pipeline streams
     long long tc_scratch_items[3] = {0, 0, 0};
     long long sum_t = 0, n_t = 0;
@@ -93,6 +99,23 @@ int cuda_fail(melf_ctx *ctx, cudaError_t e, const char *what)
         cudaError_t e_ = (call);                                     \
         if (e_ != cudaSuccess) return cuda_fail((ctx), e_, #call);   \
     } while (0)
+
+// runs `launch` (a kernel launch on `stream`), bracketed by events of kind `kind` while profiling
+template <typename F>
+cudaError_t timed(melf_ctx *ctx, int kind, cudaStream_t stream, F launch)
+{
+    if (!ctx->profiling) return launch();
+    melf_ctx::Span sp{kind, nullptr, nullptr};
+    cudaError_t e = cudaEventCreate(&sp.e0);
+    if (e != cudaSuccess) return e;
+    e = cudaEventCreate(&sp.e1);
+    if (e != cudaSuccess) return e;
+    cudaEventRecord(sp.e0, stream);
+    e = launch();
+    cudaEventRecord(sp.e1, stream);
+    ctx->spans.push_back(sp);
+    return e;
+}
 
 // numpy-slice clipping of the meter_rect against the frame (_utils.py:52-54)
 int make_geom(melf_ctx *ctx, int h, int w, bool use_rect, MelfGeom *g)
@@ -166,7 +189,8 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             t.timeline = d_tl;
         }
         for (t.item0 = 0; t.item0 < t.n_items; t.item0 += t.max_items) {
-            MELF_CUDA(ctx, melf_launch_match_tc(t, ctx->num_sms, stream));
+            MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_PREP, stream, [&] { return melf_launch_match_prep(t, stream); }));
+            MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_tc(t, ctx->num_sms, stream); }));
             g_launches += 2;
         }
         if (d_tl) {
@@ -197,7 +221,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         mm.match_key = d_keys + f0;
         mm.result = d_result ? d_result + (size_t)f0 * geom.res_w * geom.res_h : nullptr;
         const dim3 grid = melf_match_plan(mm, nf);
-        MELF_CUDA(ctx, melf_launch_match(mm, grid, stream));
+        MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_DP4A, stream, [&] { return melf_launch_match(mm, grid, stream); }));
         g_launches++;
     }
     return MELF_OK;
@@ -243,7 +267,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
         MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
         a.timeline = d_tl;
     }
-    MELF_CUDA(ctx, melf_launch_dials(a, n, stream));
+    MELF_CUDA(ctx, timed(ctx, MELF_PROF_DIALS, stream, [&] { return melf_launch_dials(a, n, stream); }));
     g_launches++;
     if (d_tl) {
         long long h_tl[64];
@@ -406,6 +430,32 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
 }
 
 void melf_destroy(melf_ctx *ctx) { free_ctx(ctx); }
+
+int melf_profile_enable(melf_ctx *ctx, int on)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    ctx->profiling = on != 0;
+    return MELF_OK;
+}
+
+int melf_profile_read(melf_ctx *ctx, float *ms, int32_t *launches)
+{
+    if (!ctx || !ms || !launches) return MELF_ERR_INVALID;
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    MELF_CUDA(ctx, cudaDeviceSynchronize());
+    for (int k = 0; k < MELF_PROF_KINDS; k++) { ms[k] = 0.f; launches[k] = 0; }
+    for (const melf_ctx::Span &sp : ctx->spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.e0, sp.e1) == cudaSuccess && sp.kind >= 0 && sp.kind < MELF_PROF_KINDS) {
+            ms[sp.kind] += t;
+            launches[sp.kind]++;
+        }
+        cudaEventDestroy(sp.e0);
+        cudaEventDestroy(sp.e1);
+    }
+    ctx->spans.clear();
+    return MELF_OK;
+}
 
 int melf_dial_window(const melf_ctx *ctx, int dial, int32_t *win_x0, int32_t *win_y0)
 {

@@ -663,7 +663,19 @@ size_t melf_match_tc_scratch_bytes(long long max_items, size_t *wsum_offset)
     return slabs + (size_t)max_items * WSUM_WORDS * sizeof(uint32_t);
 }
 
-// prep + correlation for the items [args.item0, args.item0 + args.max_items) of the batch
+// prep, then correlation, for the items [args.item0, args.item0 + args.max_items) of the batch
+cudaError_t melf_launch_match_prep(const MelfMatchTcArgs &args, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(melf_match_prep_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    long long n_local = args.n_items - args.item0;
+    if (n_local > args.max_items) n_local = args.max_items;
+    if (n_local <= 0) return cudaSuccess;
+    melf_match_prep_kernel<<<(unsigned)n_local, PREP_THREADS, PREP_SMEM_TOTAL, stream>>>(args);
+    return cudaGetLastError();
+}
+
 cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream)
 {
     cudaError_t e = cudaFuncSetAttribute(melf_match_tc_kernel<false>,
@@ -672,15 +684,9 @@ cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaS
     e = cudaFuncSetAttribute(melf_match_tc_kernel<true>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL2);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(melf_match_prep_kernel,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM_TOTAL);
-    if (e != cudaSuccess) return e;
     long long n_local = args.n_items - args.item0;
     if (n_local > args.max_items) n_local = args.max_items;
     if (n_local <= 0) return cudaSuccess;
-    melf_match_prep_kernel<<<(unsigned)n_local, PREP_THREADS, PREP_SMEM_TOTAL, stream>>>(args);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
     const long long n_pass = (n_local + 1) / 2;
     const unsigned grid = (unsigned)(n_pass < num_sms ? n_pass : num_sms);
     if (args.result)

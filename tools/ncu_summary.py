@@ -59,5 +59,29 @@ def rep(path):
                 print('  %-78s %12s %s' % (h, v, u))
 
 
+def traffic(*paths):
+    """JSON {kernel: dram bytes read + written per launch} from full-set reports, the
+    `roofline.traffic` values bench.py reads from profiles/r01_traffic.json."""
+    import json
+    import re
+    scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    out = {}
+    for path in paths:
+        txt = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], stdout=subprocess.PIPE,
+                             stderr=subprocess.DEVNULL, text=True).stdout
+        rows = list(csv.reader(txt.splitlines()))
+        (hdr, units) = (rows[0], rows[1])
+        for vals in rows[2:]:
+            d = dict(zip(hdr, zip(units, vals)))
+            name = re.sub(r'^void ', '', d['Kernel Name'][1]).split('<')[0].split('(')[0]
+            tot = 0.0
+            for key in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+                (u, v) = d[key]
+                tot += float(v.replace(',', '')) * scale[u]
+            out[name] = int(tot)
+            out[name + ':grid'] = d['Grid Size'][1]
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == '__main__':
-    {'launches': launches, 'rep': rep}[sys.argv[1]](sys.argv[2])
+    {'launches': launches, 'rep': rep, 'traffic': traffic}[sys.argv[1]](*sys.argv[2:])
