@@ -37,6 +37,10 @@
 #include "melf_common.cuh"
 #include "melf_args.h"
 
+#ifndef MELF_TC_TMEM_A
+#define MELF_TC_TMEM_A 0    // 1: Toeplitz pair via tcgen05.cp into tensor memory -- measured slower (the copy serialises with the MMAs: 95 k vs 82 k clk per pass)
+#endif
+
 namespace {
 
 constexpr int TC_THREADS = 512;
@@ -51,6 +55,8 @@ constexpr int BSTAGE_BYTES = KS * BSTRIP_BYTES;      // 32768
 constexpr int NSTAGE = 2;
 constexpr int SROWS = 137;                           // max result rows of a work item
 constexpr int NCOLS = 144;                           // TMEM columns of one accumulator = max MMA N
+constexpr int TMEM_A_COL = 2 * NCOLS;                // Toeplitz pair in tensor memory: 2 buffers of
+constexpr int TMEM_A_COLS = 64;                      //   128 lanes x 64 columns (= 128 x 256 bytes)
 constexpr int WS_PITCH = 144;                        // window-sum row pitch (words)
 constexpr int SMEM_SLABS = 0;
 constexpr int SMEM_B = 2 * SLAB_BYTES;               // 135168
@@ -118,6 +124,35 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, u64 adesc, u64 bdesc, u
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
         "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// A operand from tensor memory (lane = row m, 8 columns = the 32 K bytes of one instruction)
+__device__ __forceinline__ void umma_i8_ta(uint32_t tmem_d, uint32_t tmem_a, u64 bdesc, uint32_t idesc,
+                                           uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t"
+        "}" :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// shared -> tensor memory, 128 rows x 32 bytes (same canonical layout / descriptor as an MMA operand)
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, u64 sdesc)
+{
+    asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" :: "r"(taddr), "l"(sdesc) : "memory");
+}
+
+// one lane of a converged warp; with a warp-uniform branch around it the compiler keeps the
+// descriptors in uniform registers and issues UTCIMMA back to back (a `tid == 32` branch makes it
+// wrap every MMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop: ~94 clk per instruction issued,
+// profiles/r01_v6_mma_rate.txt)
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
@@ -398,7 +433,8 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
 {
     uint8_t *smem = melf_tc_smem;
     Ctrl2 *ctrl = reinterpret_cast<Ctrl2 *>(smem + SMEM_CTRL);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // provably warp-uniform
     const uint32_t slab_addr = smem_u32(smem + SMEM_SLABS), b_addr = smem_u32(smem + SMEM_B);
 
     if (tid == 0) {
@@ -461,11 +497,13 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
         // ---- the correlation: Toeplitz stream + MMA ------------------------------------------
         if (tid == 0) {
             for (int p = n_pre; p < A.n_pairs; ++p) load_stage(stage_count + (uint32_t)p, p);
-        } else if (tid == 32) {
-            if (tl) tl[0] = clock64();
+        } else if (warp == 1) {
+            // the whole warp walks the loop (every lane polls the barriers), one elected lane issues
+            const bool lead = elect_one();
+            if (tl && lead) tl[0] = clock64();
             mbar_wait(smem_u32(&ctrl->slab_full), pass_count & 1);
             tc_fence_after();
-            if (tl) tl[1] = clock64();
+            if (tl && lead) tl[1] = clock64();
             long long waited = 0;
             const uint32_t idesc0 = make_idesc((uint32_t)items[0].n_cols);
             const uint32_t idesc1 = make_idesc((uint32_t)items[1].n_cols);
@@ -477,6 +515,19 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
                 tc_fence_after();
                 if (tl) waited += clock64() - w0;
                 const uint32_t abase = b_addr + st * BSTAGE_BYTES;               // Toeplitz pair = A
+#if MELF_TC_TMEM_A
+                // the pair moves to tensor memory once (tcgen05.cp and tcgen05.mma run in issue
+                // order, so neither the copy -> MMA nor the MMA -> next copy hazard needs a barrier)
+                // and both items read it from there: shared memory then only streams the slabs
+                const uint32_t ta = tmem + TMEM_A_COL + (g & 1u) * TMEM_A_COLS;
+                if (lead) {
+#pragma unroll
+                    for (int ks = 0; ks < KS / 2; ++ks)
+                        tmem_cp_128x256b(ta + 8 * ks, umma_desc(abase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES));
+                    umma_commit(smem_u32(&ctrl->empty[st]));
+                }
+#endif
+                if (lead) {
 #pragma unroll
                 for (int slot = 0; slot < 2; ++slot) {
                     if (!items[slot].valid) continue;
@@ -484,14 +535,24 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
                     const uint32_t d = tmem + (uint32_t)(slot * NCOLS);
 #pragma unroll
                     for (int ks = 0; ks < KS / 2; ++ks)
+#if MELF_TC_TMEM_A
+                        umma_i8_ta(d, ta + 8 * ks,
+                                   umma_desc(bbase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
+                                   slot ? idesc1 : idesc0, (p > 0 || ks > 0) ? 1u : 0u);
+#else
                         umma_i8(d, umma_desc(abase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
                                 umma_desc(bbase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
                                 slot ? idesc1 : idesc0, (p > 0 || ks > 0) ? 1u : 0u);
+#endif
                 }
+#if !MELF_TC_TMEM_A
                 umma_commit(smem_u32(&ctrl->empty[st]));
+#endif
+                }
+                __syncwarp();
             }
-            umma_commit(smem_u32(&ctrl->accum));
-            if (tl) { tl[2] = clock64(); tl[7] = waited; }
+            if (lead) umma_commit(smem_u32(&ctrl->accum));
+            if (tl && lead) { tl[2] = clock64(); tl[7] = waited; }
         }
         stage_count += (uint32_t)A.n_pairs;
         __syncwarp();
