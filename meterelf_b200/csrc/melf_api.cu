@@ -25,6 +25,8 @@ long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames);
 size_t melf_match_tc_scratch_bytes(long long max_items, size_t *wsum_offset);
 cudaError_t melf_launch_match_prep(const MelfMatchTcArgs &args, cudaStream_t stream);
 cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
+size_t melf_match_fused_scratch_bytes(int num_sms);
+cudaError_t melf_launch_match_fused(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
 
@@ -167,19 +169,35 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         t.match_key = d_keys;
         t.result = d_result;
         melf_match_tc_plan(t, n);
-        long long cap = t.n_items < kTcMaxItems ? t.n_items : kTcMaxItems;
-        cap += cap & 1;
-        if (ctx->tc_scratch_items[scratch_slot] < cap) {
-            if (ctx->d_tc_scratch[scratch_slot]) cudaFree(ctx->d_tc_scratch[scratch_slot]);
-            ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
-            MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], melf_match_tc_scratch_bytes(cap, nullptr)));
-            ctx->tc_scratch_items[scratch_slot] = cap;
+        // MELF_MATCH_TWO_KERNEL=1 selects the older preparation + correlation kernel pair (A/B runs)
+        static const bool two_kernel = std::getenv("MELF_MATCH_TWO_KERNEL") && std::atoi(std::getenv("MELF_MATCH_TWO_KERNEL"));
+        if (two_kernel) {
+            long long cap = t.n_items < kTcMaxItems ? t.n_items : kTcMaxItems;
+            cap += cap & 1;
+            if (ctx->tc_scratch_items[scratch_slot] < cap) {
+                if (ctx->d_tc_scratch[scratch_slot]) cudaFree(ctx->d_tc_scratch[scratch_slot]);
+                ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
+                MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], melf_match_tc_scratch_bytes(cap, nullptr)));
+                ctx->tc_scratch_items[scratch_slot] = cap;
+            }
+            size_t wsum_off = 0;
+            melf_match_tc_scratch_bytes(ctx->tc_scratch_items[scratch_slot], &wsum_off);
+            t.slabs = ctx->d_tc_scratch[scratch_slot];
+            t.wsum = reinterpret_cast<uint32_t *>(ctx->d_tc_scratch[scratch_slot] + wsum_off);
+            t.max_items = ctx->tc_scratch_items[scratch_slot];
+        } else {
+            // fused kernel: per-CTA scratch (slabs of the next pass + window sums of the current one)
+            if (ctx->tc_scratch_items[scratch_slot] != -1) {
+                if (ctx->d_tc_scratch[scratch_slot]) cudaFree(ctx->d_tc_scratch[scratch_slot]);
+                ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
+                const size_t bytes = melf_match_fused_scratch_bytes(ctx->num_sms);
+                MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], bytes));
+                MELF_CUDA(ctx, cudaMemset(ctx->d_tc_scratch[scratch_slot], 0, bytes));
+                ctx->tc_scratch_items[scratch_slot] = -1;         // marks "fused layout"
+            }
+            t.slabs = ctx->d_tc_scratch[scratch_slot];
+            t.max_items = t.n_items;
         }
-        size_t wsum_off = 0;
-        melf_match_tc_scratch_bytes(ctx->tc_scratch_items[scratch_slot], &wsum_off);
-        t.slabs = ctx->d_tc_scratch[scratch_slot];
-        t.wsum = reinterpret_cast<uint32_t *>(ctx->d_tc_scratch[scratch_slot] + wsum_off);
-        t.max_items = ctx->tc_scratch_items[scratch_slot];
         // MELF_TC_TIMELINE=<file>: debug dump of CTA 0's per-pass clock64 stamps (synchronises)
         const char *tl_path = std::getenv("MELF_TC_TIMELINE");
         long long *d_tl = nullptr;
@@ -188,6 +206,10 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
             t.timeline = d_tl;
         }
+        if (!two_kernel) {
+            MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_fused(t, ctx->num_sms, stream); }));
+            g_launches += 1;
+        } else
         for (t.item0 = 0; t.item0 < t.n_items; t.item0 += t.max_items) {
             MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_PREP, stream, [&] { return melf_launch_match_prep(t, stream); }));
             MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_tc(t, ctx->num_sms, stream); }));
@@ -200,7 +222,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             cudaFree(d_tl);
             if (FILE *fp = std::fopen(tl_path, "w")) {
                 for (int i = 0; i < 8; i++) {
-                    for (int j = 0; j < 8; j++) std::fprintf(fp, "%lld ", h_tl[8 * i + j] - (j < 7 ? h_tl[0] : 0));
+                    for (int j = 0; j < 8; j++) std::fprintf(fp, "%lld ", h_tl[8 * i + j] - ((j < 7 || !two_kernel) ? h_tl[0] : 0));
                     std::fprintf(fp, "\n");
                 }
                 std::fclose(fp);

@@ -669,6 +669,566 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
 }
 
+// =======================================================================================
+// Fused variant (default): ONE persistent kernel.  The operand preparation of the two-kernel
+// version above runs in the shadow of the MMAs instead of in front of them: while warp 1
+// streams the 960 tcgen05.mma of a pass (~82 k clk during which the other 14 warps used to
+// idle), warps 2..15
+//   (b) compute the window sums of the CURRENT pass's items from the lightness slabs that
+//       already sit in shared memory -> a per-CTA global scratch (L2), read back in the drain;
+//   (a) convert the BGR crop of the NEXT pass's items to lightness slabs -> per-CTA global
+//       scratch (L2), from where the producer fetches them with one bulk copy each as soon as
+//       the accumulators are complete.
+// Scratch is 204 KB per CTA (30 MB per launch, L2-resident) instead of 99 KB per frame, so the
+// only DRAM traffic left is the one read of the meter_rect crop.
+// =======================================================================================
+namespace {
+
+#ifndef MELF_F_NSTAGE
+#define MELF_F_NSTAGE 2
+#define MELF_F_KSTEPS 8
+#endif
+constexpr int F_NSTAGE = MELF_F_NSTAGE;                       // Toeplitz ring
+constexpr int F_KSTEPS = MELF_F_KSTEPS;                       // K-steps (of 32) per stage
+constexpr int F_SPP = 8 / F_KSTEPS;                           // stages per template-row pair
+constexpr int F_STAGE_BYTES = 2 * F_KSTEPS * BSTRIP_BYTES;    // 4096 per K-step
+constexpr int F_SMEM_B = 2 * SLAB_BYTES;                      // 135168
+constexpr int F_SMEM_H = F_SMEM_B + F_NSTAGE * F_STAGE_BYTES; // H table, 256 rows x 16 words, + segment totals
+constexpr int F_SMEM_CTRL = F_SMEM_H + 16384 + 4096;
+constexpr int F_SMEM_TOTAL = F_SMEM_CTRL + 512;
+constexpr int F_WORKERS = TC_THREADS - 64;                    // warps 2..15
+constexpr int F_WORKER_WARPS = F_WORKERS / 32;
+constexpr size_t F_SCRATCH_PER_CTA = 2 * (size_t)SLAB_BYTES + 2 * (size_t)WSUM_WORDS * 4;
+
+struct CtrlF {
+    unsigned long long full[F_NSTAGE];
+    unsigned long long empty[F_NSTAGE];
+    unsigned long long accum;
+    unsigned long long slab_full;
+    unsigned long long prep_done;
+    uint32_t tmem_base;
+    uint32_t pad;
+    u64 red[2][16];
+};
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void worker_sync()
+{
+    asm volatile("bar.sync 1, %0;" :: "n"(F_WORKERS) : "memory");
+}
+__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Lightness of 16 consecutive pixels (48 bytes = words v[0..11]) -> 16 bytes.
+// max / min of (B, G, R) are taken on packed 16-bit lanes (VIMNMX3.U16x2: one instruction per
+// pixel pair) with the colour byte in the HIGH byte of each lane -- the low byte is whatever the
+// byte permute left there and can only break ties between equal colour bytes.  The float part
+// is melf_lightness()'s operation order, two pixels per packed f32x2 instruction:
+//     vmax = fl(max * k), vmin = fl(min * k)   as fma(2^23 + v, k, -2^23 k): exact product, one rounding
+//     L = rint(fl(fl(vmax + vmin) * 127.5))    (x * .5) * 255 == x * 127.5; rint = + 1.5 * 2^23
+__device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12])
+{
+    const float2 k = melf_f2(1.f / 255.f), c = melf_f2(-8388608.f * (1.f / 255.f));
+    const float2 half255 = melf_f2(127.5f), M = melf_f2(MELF_MAGIC_RINT);
+    uint32_t o[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        uint32_t lb[4];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int b0 = 12 * g + 6 * q;                   // byte index of B of the first pixel of the pair
+            uint32_t ch[3];
+#pragma unroll
+            for (int cidx = 0; cidx < 3; ++cidx) {
+                // bytes (b0 + cidx) and (b0 + cidx + 3) -> bytes 1 and 3
+                const int ba = b0 + cidx, bb = ba + 3;
+                const int wa = ba >> 2, wb = bb >> 2;        // wb == wa or wa + 1
+                const uint32_t sa = (uint32_t)(ba & 3), sb = (uint32_t)((bb & 3) + (wb == wa ? 0 : 4));
+                ch[cidx] = __byte_perm(v[wa], v[wb == wa ? wa : wb], (sb << 12) | (sb << 8) | (sa << 4) | sa);
+            }
+            const uint32_t mx = __vmaxu2(__vmaxu2(ch[0], ch[1]), ch[2]);
+            const uint32_t mn = __vminu2(__vminu2(ch[0], ch[1]), ch[2]);
+            // byte 1 / byte 3 -> 2^23 + value as float32
+            const float2 hi = make_float2(__uint_as_float(__byte_perm(mx, 0x4B000000u, 0x7541u)),
+                                          __uint_as_float(__byte_perm(mx, 0x4B000000u, 0x7543u)));
+            const float2 lo = make_float2(__uint_as_float(__byte_perm(mn, 0x4B000000u, 0x7541u)),
+                                          __uint_as_float(__byte_perm(mn, 0x4B000000u, 0x7543u)));
+            const float2 sm = melf_add2(melf_fma2(hi, k, c), melf_fma2(lo, k, c));
+            const float2 Lf = melf_add2_after_mul(melf_mul2(sm, half255), M);
+            lb[2 * q] = __float_as_uint(Lf.x);
+            lb[2 * q + 1] = __float_as_uint(Lf.y);
+        }
+        const uint32_t lo2 = __byte_perm(lb[0], lb[1], 0x0040), hi2 = __byte_perm(lb[2], lb[3], 0x0040);
+        o[g] = __byte_perm(lo2, hi2, 0x5410);
+    }
+    return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// 16 consecutive pixels of slab row r / strip s of an item (fused kernel's version of stage_unit)
+__device__ __forceinline__ uint4 stage_unit_f(const MelfMatchTcArgs &A, const Item &it, int r, int s)
+{
+    const int cy = it.y0 + r, cx = it.x0 + 16 * s;
+    if (cy >= A.geom.crop_h || cx >= A.geom.crop_w) return make_uint4(0, 0, 0, 0);
+    const uint8_t *src = A.img + (size_t)it.frame * A.frame_stride +
+                         (size_t)(A.geom.crop_y0 + cy) * A.row_stride +
+                         (size_t)A.channels * (size_t)(A.geom.crop_x0 + cx);
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(src);
+    const uint4 *al = reinterpret_cast<const uint4 *>(addr & ~(uintptr_t)15);
+    const uint32_t off = (uint32_t)(addr & 15);
+    const uint32_t ws = off >> 2, bs = (off & 3) * 8;
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+    const int nchunk = A.channels == 3 ? 4 : 2;
+    uint32_t e[16];
+#pragma unroll
+    for (int cidx = 0; cidx < 4; ++cidx) {
+        uint4 q = make_uint4(0, 0, 0, 0);
+        if (cidx < nchunk && reinterpret_cast<uintptr_t>(al + cidx) < limit) q = __ldg(al + cidx);
+        e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+    }
+    uint32_t v[12];
+    // shift right by `off` bytes; the word part is uniform across a warp whenever the row stride
+    // is a multiple of 16, so the branches normally do not diverge
+    switch (ws) {
+    case 0:
+#pragma unroll
+        for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j], e[j + 1], bs);
+        break;
+    case 1:
+#pragma unroll
+        for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 1], e[j + 2], bs);
+        break;
+    case 2:
+#pragma unroll
+        for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 2], e[j + 3], bs);
+        break;
+    default:
+#pragma unroll
+        for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 3], j + 4 < 16 ? e[j + 4] : 0u, bs);
+        break;
+    }
+    if (A.channels == 1) return make_uint4(v[0], v[1], v[2], v[3]);
+    return lightness16(v);
+}
+
+// Window sums of one item, S(y, x) = sum_{i<th} sum_{j<tw} L(y + i, x + j), from the slab in
+// shared memory to global scratch (y-major [y][64]); called by all F_WORKERS threads.
+// Two x-halves of 32 columns, each in three steps separated by worker barriers:
+//   H   thread = slab row: horizontal sums H(row, x) sliding along x (the start value of the
+//       second half is carried in a register), u16 pairs, word (row, xp) at row*16 + (xp ^ (row & 15))
+//   V1  thread = (8-row segment, x pair): segment totals C[seg][xp]
+//   V2  thread = (8 result rows, x pair): first window = whole segments + (th & 7) single rows,
+//       then sliding down its 8 rows
+__device__ __forceinline__ void window_sums(const MelfMatchTcArgs &A, const Item &it, const uint8_t *slab,
+                                            uint32_t *Htab, uint32_t *S, int wt)
+{
+    uint2 *Ctab = reinterpret_cast<uint2 *>(Htab + 256 * 16);          // [32 segments][16 x pairs]
+    const int n_rows = min(SLAB_DATA_ROWS, it.h_c + A.tmpl_h);          // H rows that are read
+    const int row = wt;                                                 // n_rows <= 256 < F_WORKERS
+    const uint8_t *sl = slab + row * 16;
+    const uint32_t o = (uint32_t)A.tmpl_w & 15, ws = o >> 2, bs = (o & 3) * 8;
+    int h = 0;
+    if (row < n_rows) {
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+            const uint4 q = *reinterpret_cast<const uint4 *>(sl + s * STRIP_BYTES);
+            h = (int)__dp4a(q.x, A.ones_words[4 * s], (uint32_t)h);
+            h = (int)__dp4a(q.y, A.ones_words[4 * s + 1], (uint32_t)h);
+            h = (int)__dp4a(q.z, A.ones_words[4 * s + 2], (uint32_t)h);
+            h = (int)__dp4a(q.w, A.ones_words[4 * s + 3], (uint32_t)h);
+        }
+    }
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+        if (row < n_rows) {
+            // leaving bytes: columns 32 half .. +31; entering bytes: columns tw + 32 half .. +31
+            uint32_t w[8], e[12], g[8];
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+                const uint4 q = *reinterpret_cast<const uint4 *>(sl + (2 * half + s) * STRIP_BYTES);
+                w[4 * s] = q.x; w[4 * s + 1] = q.y; w[4 * s + 2] = q.z; w[4 * s + 3] = q.w;
+            }
+            const int s0 = (A.tmpl_w >> 4) + 2 * half;
+#pragma unroll
+            for (int s = 0; s < 3; ++s) {
+                uint4 q = make_uint4(0, 0, 0, 0);
+                if (s0 + s < KS) q = *reinterpret_cast<const uint4 *>(sl + (s0 + s) * STRIP_BYTES);
+                e[4 * s] = q.x; e[4 * s + 1] = q.y; e[4 * s + 2] = q.z; e[4 * s + 3] = q.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t t0 = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
+                const uint32_t t1 = ws == 0 ? e[j + 1] : ws == 1 ? e[j + 2] : ws == 2 ? e[j + 3] : e[j + 4];
+                g[j] = __funnelshift_r(t0, t1, bs);
+            }
+            uint32_t *Hb = Htab + row * 16;
+            const int sw = row & 15;
+#pragma unroll
+            for (int xp = 0; xp < 16; ++xp) {
+                const int xa = 2 * xp, xb = 2 * xp + 1;
+                const uint32_t lo = (uint32_t)h;
+                h += (int)((g[xa >> 2] >> (8 * (xa & 3))) & 255) - (int)((w[xa >> 2] >> (8 * (xa & 3))) & 255);
+                const uint32_t hi = (uint32_t)h;
+                h += (int)((g[xb >> 2] >> (8 * (xb & 3))) & 255) - (int)((w[xb >> 2] >> (8 * (xb & 3))) & 255);
+                Hb[xp ^ sw] = lo | (hi << 16);
+            }
+        }
+        worker_sync();
+        // V1: totals of the 8-row segments (rows beyond n_rows are never part of a window that is used)
+        for (int t = wt; t < 32 * 16; t += F_WORKERS) {
+            const int seg = t >> 4, xp = t & 15;
+            uint32_t c0 = 0, c1 = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = 8 * seg + i;
+                const uint32_t q = Htab[r * 16 + (xp ^ (r & 15))];
+                c0 += q & 0xffff; c1 += q >> 16;
+            }
+            Ctab[t] = make_uint2(c0, c1);
+        }
+        worker_sync();
+        // V2
+        {
+            const int yseg = wt >> 4, xp = wt & 15;
+            const int ya = 8 * yseg, yb = min(it.h_c, ya + 8);
+            if (ya < yb) {
+                uint32_t s0 = 0, s1 = 0;
+                const int n_seg = A.tmpl_h >> 3;
+                for (int k = 0; k < n_seg; ++k) {
+                    const uint2 c = Ctab[(yseg + k) * 16 + xp];
+                    s0 += c.x; s1 += c.y;
+                }
+                for (int r = ya + 8 * n_seg; r < ya + A.tmpl_h; ++r) {
+                    const uint32_t q = Htab[r * 16 + (xp ^ (r & 15))];
+                    s0 += q & 0xffff; s1 += q >> 16;
+                }
+                for (int y = ya; y < yb; ++y) {
+                    *reinterpret_cast<uint2 *>(S + y * 64 + 32 * half + 2 * xp) = make_uint2(s0, s1);
+                    const int rin = y + A.tmpl_h;                                  // <= 255 (plan cap)
+                    const uint32_t vin = Htab[rin * 16 + (xp ^ (rin & 15))];
+                    const uint32_t vout = Htab[y * 16 + (xp ^ (y & 15))];
+                    s0 += (vin & 0xffff) - (vout & 0xffff);
+                    s1 += (vin >> 16) - (vout >> 16);
+                }
+            }
+        }
+        worker_sync();                          // H table free again
+    }
+}
+
+// lightness slabs of the (up to two) items of one pass -> this CTA's global scratch
+__device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item (&its)[2], uint8_t *scratch,
+                                            int wwarp, int lane, int n_wwarps = F_WORKER_WARPS)
+{
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int n_units = ((n_rows + 7) >> 3) * 4;
+        uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        // warp-unit = 8 rows x 4 strips; lane = strip * 8 + row: every quarter warp stores 128
+        // contiguous bytes and reads 8 rows x 192 contiguous bytes of the frame
+        for (int u = wwarp; u < n_units; u += n_wwarps) {
+            const int rg = u >> 2, sg = u & 3;
+            const int r = rg * 8 + (lane & 7), s = sg * 4 + (lane >> 3);
+            *reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16) = stage_unit_f(A, it, r, s);
+        }
+    }
+}
+
+}  // namespace
+
+template <bool WRITE_MAP>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+melf_match_fused_kernel(const MelfMatchTcArgs A)
+{
+    uint8_t *smem = melf_tc_smem;
+    CtrlF *ctrl = reinterpret_cast<CtrlF *>(smem + F_SMEM_CTRL);
+    uint32_t *Htab = reinterpret_cast<uint32_t *>(smem + F_SMEM_H);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // provably warp-uniform
+    const uint32_t slab_addr = smem_u32(smem + SMEM_SLABS), b_addr = smem_u32(smem + F_SMEM_B);
+    uint8_t *scratch = A.slabs + (size_t)blockIdx.x * F_SCRATCH_PER_CTA;        // [slab 0][slab 1][S 0][S 1]
+    uint32_t *wsum = reinterpret_cast<uint32_t *>(scratch + 2 * (size_t)SLAB_BYTES);
+
+    if (tid == 0) {
+        for (int s = 0; s < F_NSTAGE; ++s) {
+            mbar_init(smem_u32(&ctrl->full[s]), 1);
+            mbar_init(smem_u32(&ctrl->empty[s]), 1);
+        }
+        mbar_init(smem_u32(&ctrl->accum), 1);
+        mbar_init(smem_u32(&ctrl->slab_full), 1);
+        mbar_init(smem_u32(&ctrl->prep_done), F_WORKERS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;"
+                     :: "r"(smem_u32(&ctrl->tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctrl->tmem_base;
+
+    const long long n_pass = (A.n_items + 1) / 2;
+    const int n_stages = F_SPP * A.n_pairs;                           // per pass
+    const int n_pre = n_stages < F_NSTAGE ? n_stages : F_NSTAGE;      // stages prefetched ahead of a pass
+    const bool producer = warp == 0 && elect_one();
+
+    // producer helpers.  Stage g of the running stage counter uses ring slot g % F_NSTAGE; its
+    // "empty" barrier has completed (g / F_NSTAGE) phases when it may be refilled.
+    auto load_stage = [&](uint32_t g, int s) {
+        const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
+        mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
+        mbar_expect_tx(smem_u32(&ctrl->full[st]), F_STAGE_BYTES);
+        bulk_load(b_addr + st * F_STAGE_BYTES, A.toeplitz + (size_t)s * F_STAGE_BYTES, F_STAGE_BYTES,
+                  smem_u32(&ctrl->full[st]));
+    };
+    auto load_slabs = [&](long long pass) {
+        const int n = (2 * pass + 1 < A.n_items) ? 2 : 1;
+        fence_async_all();                 // the workers' generic-proxy writes (global) / reads (slabs) first
+        mbar_expect_tx(smem_u32(&ctrl->slab_full), (uint32_t)(n * SLAB_BYTES));
+        for (int k = 0; k < n; ++k)
+            bulk_load(slab_addr + k * SLAB_BYTES, scratch + (size_t)k * SLAB_BYTES, SLAB_BYTES,
+                      smem_u32(&ctrl->slab_full));
+    };
+    auto pass_items = [&](long long pass, Item (&its)[2]) {
+        its[0] = get_item(A, 2 * pass);
+        its[1] = get_item(A, 2 * pass + 1);
+    };
+
+    uint32_t stage_count = 0;       // Toeplitz stages consumed before this pass
+    uint32_t pass_count = 0;
+
+    // ---- prologue: slabs of this CTA's first pass --------------------------------------------
+    if ((long long)blockIdx.x < n_pass) {
+        if (warp >= 2) {
+            Item its[2];
+            pass_items(blockIdx.x, its);
+            stage_slabs(A, its, scratch, warp - 2, lane);
+            fence_async_all();
+            mbar_arrive(smem_u32(&ctrl->prep_done));
+        } else if (producer) {
+            for (int s = 0; s < n_pre; ++s) load_stage((uint32_t)s, s);
+            mbar_wait(smem_u32(&ctrl->prep_done), 0);
+            load_slabs(blockIdx.x);
+        }
+    }
+    __syncwarp();
+
+    for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x, ++pass_count) {
+        Item items[2];
+        pass_items(pass, items);
+        const bool has_next = pass + gridDim.x < n_pass;
+        long long *tl = (A.timeline && blockIdx.x == 0 && pass_count < 8) ? A.timeline + pass_count * 8 : nullptr;
+
+        if (warp == 0) {
+            // ---- producer: the rest of the Toeplitz stream --------------------------------------
+            if (producer)
+                for (int s = n_pre; s < n_stages; ++s) load_stage(stage_count + (uint32_t)s, s);
+        } else if (warp == 1) {
+            // ---- issuer: the whole warp walks the loop, one elected lane issues -----------------
+            const bool lead = elect_one();
+            if (tl && lead) tl[0] = clock64();
+            mbar_wait(smem_u32(&ctrl->slab_full), pass_count & 1);
+            tc_fence_after();
+            if (tl && lead) tl[1] = clock64();
+            const uint32_t idesc0 = make_idesc((uint32_t)items[0].n_cols);
+            const uint32_t idesc1 = make_idesc((uint32_t)items[1].n_cols);
+            uint32_t g = stage_count;
+            for (int s = 0; s < n_stages; ++s, ++g) {
+                const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
+                mbar_wait(smem_u32(&ctrl->full[st]), ph);
+                tc_fence_after();
+                if (lead) {
+                    const int p = s / F_SPP, k0 = (s % F_SPP) * F_KSTEPS;          // pair, first K-step
+                    const uint32_t abase = b_addr + st * F_STAGE_BYTES;               // Toeplitz half pair = A
+#pragma unroll
+                    for (int slot = 0; slot < 2; ++slot) {
+                        if (!(slot ? items[1].valid : items[0].valid)) continue;
+                        const uint32_t bbase = slab_addr + slot * SLAB_BYTES + (2 * p) * 16 +
+                                               k0 * 2 * STRIP_BYTES;                  // slab rows 2p.. = B
+                        const uint32_t d = tmem + (uint32_t)(slot * NCOLS);
+#pragma unroll
+                        for (int ks = 0; ks < F_KSTEPS; ++ks)
+                            umma_i8(d, umma_desc(abase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
+                                    umma_desc(bbase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
+                                    slot ? idesc1 : idesc0, (s > 0 || ks > 0) ? 1u : 0u);
+                    }
+                    umma_commit(smem_u32(&ctrl->empty[st]));
+                }
+                __syncwarp();
+            }
+            if (lead) umma_commit(smem_u32(&ctrl->accum));
+            if (tl && lead) tl[2] = clock64();
+        } else {
+            // ---- workers: window sums of this pass, slabs of the next one -------------------------
+            const int wt = tid - 64;
+            mbar_wait(smem_u32(&ctrl->slab_full), pass_count & 1);
+#pragma unroll 1
+            for (int slot = 0; slot < 2; ++slot) {
+                const Item cur = slot ? items[1] : items[0];
+#ifdef MELF_TC_EXP
+                if (!(MELF_TC_EXP & 1))
+#endif
+                if (cur.valid)
+                    window_sums(A, cur, smem + SMEM_SLABS + slot * SLAB_BYTES, Htab, wsum + slot * WSUM_WORDS, wt);
+            }
+            if (tl && wt == 0) tl[6] = clock64();
+            if (has_next) {
+                Item nxt[2];
+                pass_items(pass + gridDim.x, nxt);
+#if defined(MELF_TC_EXP) && (MELF_TC_EXP & 4)
+                // experiment: keep the workers off the issuer's scheduler (warp % 4 == 1)
+                if ((warp & 3) != 1) stage_slabs(A, nxt, scratch, warp - 2 - ((warp - 2) >> 2), lane, 11);
+#elif defined(MELF_TC_EXP) && (MELF_TC_EXP & 8)
+                // experiment: keep the workers off the producer's scheduler (warp % 4 == 0)
+                if ((warp & 3) != 0) stage_slabs(A, nxt, scratch, warp - 2 - ((warp - 1) >> 2), lane, 11);
+#else
+#ifdef MELF_TC_EXP
+                if (!(MELF_TC_EXP & 2))
+#endif
+                stage_slabs(A, nxt, scratch, warp - 2, lane);
+#endif
+            }
+            if (tl && wt == 0) tl[7] = clock64();
+            fence_async_all();
+            mbar_arrive(smem_u32(&ctrl->prep_done));
+        }
+        stage_count += (uint32_t)n_stages;
+        __syncwarp();
+
+        // ---- epilogue ----------------------------------------------------------------------------
+        // warp -> TMEM lane quadrant qd (hardware rule: warp % 4), item slot, half of the columns.
+        // Lane pair (2j, 2j+1) holds D[2x][.] and D[2x+1][.] of result column x = 16 qd + j; of
+        // every 16-row chunk the even lane scores rows 0..7 and the odd lane rows 8..15.
+        const int qd = warp & 3, slot = (warp >> 2) & 1, half = warp >> 3;
+        const Item it = slot ? items[1] : items[0];
+        const int n_chunks = it.n_cols >> 4;
+        const int c_mid = (n_chunks + 1) >> 1;
+        const int c0 = half ? c_mid : 0, c1 = half ? n_chunks : c_mid;      // <= 5 chunks
+        const int x = 16 * qd + (lane >> 1);                       // result column inside the item
+        const int odd = lane & 1;
+        const bool col_ok = it.valid && x < it.w_c;
+
+        mbar_wait(smem_u32(&ctrl->prep_done), (pass_count + 1) & 1);       // window sums + next slabs written
+        const uint32_t *S = wsum + slot * WSUM_WORDS + x;
+        uint32_t sw[5][8];
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+            if (c0 + k < c1 && col_ok) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int yl = 16 * (c0 + k) + 8 * odd + j;
+                    sw[k][j] = yl < it.h_c ? __ldcg(S + yl * 64) : 0u;
+                }
+            }
+
+        mbar_wait(smem_u32(&ctrl->accum), pass_count & 1);
+        tc_fence_after();
+        if (tl && tid == 64) tl[3] = clock64();
+        // every MMA of this pass has completed: slabs and Toeplitz ring are free again
+        if (producer && has_next) {
+            load_slabs(pass + gridDim.x);
+            for (int s = 0; s < n_pre; ++s) load_stage(stage_count + (uint32_t)s, s);
+        }
+        __syncwarp();
+
+        const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(slot * NCOLS);
+        long long best_num = 0;
+        uint32_t best_idx = 0;
+        bool has = false;
+        float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
+        if (it.valid) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                const int c = c0 + k;
+                if (c < c1) {                                // warp-uniform
+                    uint32_t d16[16], d[17];
+                    tmem_ld16(taddr + 16 * c, d16);
+                    tmem_ld1(taddr + 16 * c + 16, d[16]);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) d[i] = d16[i];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        // even sends D[2x][y0+8+j] and receives D[2x+1][y0+j+1]; odd the other way round
+                        const uint32_t other = __shfl_xor_sync(0xffffffffu, odd ? d[j + 1] : d[8 + j], 1);
+                        const uint32_t mine = odd ? d[9 + j] : d[j];
+                        const int yl = 16 * c + 8 * odd + j;
+                        if (col_ok && yl < it.h_c) {
+                            const long long sum_tl = (long long)(int)(mine + other);
+                            const long long num = A.n_t * sum_tl - A.sum_t * (long long)sw[k][j];
+                            const uint32_t idx = (uint32_t)(it.y0 + yl) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
+                            if (WRITE_MAP) map[idx] = score_of(num, A.n_t);
+                            // see melf_match_tc_kernel: raster order per lane, float32 rounding only for close calls
+                            if (!has) { best_num = num; best_idx = idx; has = true; }
+                            else if (num > best_num) {
+                                const long long mag = (best_num < 0 ? -best_num : best_num) + A.n_t;
+                                if (num - best_num > (mag >> 21) + 1 || score_of(num, A.n_t) > score_of(best_num, A.n_t)) {
+                                    best_num = num; best_idx = idx;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (tl && tid == 64) tl[4] = clock64();
+        u64 best = has ? melf_score_key(score_of(best_num, A.n_t), best_idx) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if (lane == 0) ctrl->red[pass_count & 1][warp] = best;
+        tc_fence_before();
+        __syncthreads();            // TMEM fully read before the next pass's first MMA overwrites it
+        tc_fence_after();
+        if (tl && tid == 64) tl[5] = clock64();
+        if (tid < 2) {
+            // warps of slot s: 4 s .. 4 s + 3 and 8 + 4 s .. 8 + 4 s + 3
+            const Item mine = tid ? items[1] : items[0];
+            u64 b = 0;
+            for (int w8 = 0; w8 < 8; ++w8) {
+                const u64 k = ctrl->red[pass_count & 1][(w8 & 3) + 4 * tid + 8 * (w8 >> 2)];
+                b = k > b ? k : b;
+            }
+            if (mine.valid && b) atomicMax(A.match_key + mine.frame, b);
+        }
+        __syncwarp();               // red[] alternates per pass: no thread can be two passes behind
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
+}
+
+size_t melf_match_fused_scratch_bytes(int num_sms) { return (size_t)num_sms * F_SCRATCH_PER_CTA; }
+
+cudaError_t melf_launch_match_fused(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(melf_match_fused_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(melf_match_fused_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    if (args.n_items <= 0) return cudaSuccess;
+    const long long n_pass = (args.n_items + 1) / 2;
+    const unsigned grid = (unsigned)(n_pass < num_sms ? n_pass : num_sms);
+    if (args.result)
+        melf_match_fused_kernel<true><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+    else
+        melf_match_fused_kernel<false><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+    return cudaGetLastError();
+}
+
 // ---- host side ---------------------------------------------------------------------------
 
 bool melf_match_tc_supported(int tmpl_w, int tmpl_h)
