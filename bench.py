@@ -339,13 +339,21 @@ def run_ours(args):
     macs = rw * rh * 188 * 119
     tc_ms = kernel_ms.get('match_tc')
     int8_peak = 2.0 * peaks['bf16_tflops']
+    fused = not kernel_ms.get('match_prep')
+    tc_name = 'melf_match_fused_kernel' if fused else 'melf_match_tc_kernel'
     if tc_ms:
         tops = 2.0 * macs * n / (tc_ms / 1e3) / 1e12
+        crop_bytes = 250 * 250 * 3 * n
         roofline = {
-            'kernel': 'melf_match_tc_kernel (TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
+            'kernel': tc_name + (' (BGR crop -> lightness + window sums in the shadow of the MMAs; ' if fused else ' (') +
+                      'TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
             'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
-            'frac': tops / int8_peak, 'traffic': traffic.get('melf_match_tc_kernel'),
+            'frac': tops / int8_peak, 'traffic': traffic.get(tc_name),
             'ms_per_launch': tc_ms,
+            'hbm_view': {'algorithmic_bytes': crop_bytes, 'achieved_gbs': crop_bytes / (tc_ms / 1e3) / 1e9,
+                         'frac_of_hbm_peak': crop_bytes / (tc_ms / 1e3) / 1e9 / peaks['hbm_gbs'],
+                         'note': 'the only DRAM traffic of the fused kernel is one read of the meter_rect crop '
+                                 '(187500 B/frame); it is far from HBM-bound'} if fused else None,
             'note': 'algorithmic 2*%d op/frame x %d frames per launch (SURVEY 8d: 63x132 positions x 22372 MAC); '
                     'peak = 2 x %s bf16 dense (int8:bf16 tensor ratio); issued MACs are 1.50x the algorithmic '
                     'ones (K 188->256, N 133->144, M 63->64); kernel share of step %.2f'

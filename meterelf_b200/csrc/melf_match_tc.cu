@@ -690,7 +690,6 @@ namespace {
 #endif
 constexpr int F_NSTAGE = MELF_F_NSTAGE;                       // Toeplitz ring
 constexpr int F_KSTEPS = MELF_F_KSTEPS;                       // K-steps (of 32) per stage
-constexpr int F_SPP = 8 / F_KSTEPS;                           // stages per template-row pair
 constexpr int F_STAGE_BYTES = 2 * F_KSTEPS * BSTRIP_BYTES;    // 4096 per K-step
 constexpr int F_SMEM_B = 2 * SLAB_BYTES;                      // 135168
 constexpr int F_SMEM_H = F_SMEM_B + F_NSTAGE * F_STAGE_BYTES; // H table, 256 rows x 16 words, + segment totals
@@ -720,6 +719,68 @@ __device__ __forceinline__ void worker_sync()
     asm volatile("bar.sync 1, %0;" :: "n"(F_WORKERS) : "memory");
 }
 __device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// L2 residency: the frames stream through L2 once (evict-first), the per-CTA scratch is written
+// and read back every pass and must stay there (evict-last); without the hints ncu shows the
+// scratch bouncing through DRAM (profiles/r01_v7_ncu_match_fused.txt: 1.25 GB per launch for
+// 0.77 GB of crops)
+__device__ __forceinline__ u64 policy_evict_first()
+{
+    u64 p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ u64 policy_evict_last()
+{
+    u64 p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+#ifndef MELF_HINT_STREAM
+#define MELF_HINT_STREAM 2      // 1 (L1::no_allocate + L2 evict-first) measured 0.85 -> 1.06 ms: the misaligned 64-byte
+#endif                          // spans of neighbouring lanes overlap and want L1; 2 = evict-first with L1 allocation
+#ifndef MELF_HINT_KEEP
+#define MELF_HINT_KEEP 1
+#endif
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *ptr, u64 pol)
+{
+#if !MELF_HINT_STREAM
+    return __ldg(ptr);
+#endif
+    uint4 v;
+#if MELF_HINT_STREAM == 2
+    asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
+#else
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
+#endif
+    return v;
+}
+__device__ __forceinline__ void stg_keep(uint4 *ptr, uint4 v, u64 pol)
+{
+#if !MELF_HINT_KEEP
+    *ptr = v; return;
+#endif
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;"
+                 :: "l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void stg_keep2(uint2 *ptr, uint2 v, u64 pol)
+{
+#if !MELF_HINT_KEEP
+    *ptr = v; return;
+#endif
+    asm volatile("st.global.L2::cache_hint.v2.u32 [%0], {%1, %2}, %3;"
+                 :: "l"(ptr), "r"(v.x), "r"(v.y), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_load_keep(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, u64 pol)
+{
+#if !MELF_HINT_KEEP
+    bulk_load(dst, src, bytes, bar); return;
+#endif
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
 
 // Lightness of 16 consecutive pixels (48 bytes = words v[0..11]) -> 16 bytes.
 // max / min of (B, G, R) are taken on packed 16-bit lanes (VIMNMX3.U16x2: one instruction per
@@ -767,7 +828,7 @@ __device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12])
 }
 
 // 16 consecutive pixels of slab row r / strip s of an item (fused kernel's version of stage_unit)
-__device__ __forceinline__ uint4 stage_unit_f(const MelfMatchTcArgs &A, const Item &it, int r, int s)
+__device__ __forceinline__ uint4 stage_unit_f(const MelfMatchTcArgs &A, const Item &it, int r, int s, u64 pol_stream)
 {
     const int cy = it.y0 + r, cx = it.x0 + 16 * s;
     if (cy >= A.geom.crop_h || cx >= A.geom.crop_w) return make_uint4(0, 0, 0, 0);
@@ -784,7 +845,7 @@ __device__ __forceinline__ uint4 stage_unit_f(const MelfMatchTcArgs &A, const It
 #pragma unroll
     for (int cidx = 0; cidx < 4; ++cidx) {
         uint4 q = make_uint4(0, 0, 0, 0);
-        if (cidx < nchunk && reinterpret_cast<uintptr_t>(al + cidx) < limit) q = __ldg(al + cidx);
+        if (cidx < nchunk && reinterpret_cast<uintptr_t>(al + cidx) < limit) q = ldg_stream(al + cidx, pol_stream);
         e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
     }
     uint32_t v[12];
@@ -824,6 +885,7 @@ __device__ __forceinline__ void window_sums(const MelfMatchTcArgs &A, const Item
                                             uint32_t *Htab, uint32_t *S, int wt)
 {
     uint2 *Ctab = reinterpret_cast<uint2 *>(Htab + 256 * 16);          // [32 segments][16 x pairs]
+    const u64 pol_keep = policy_evict_last();
     const int n_rows = min(SLAB_DATA_ROWS, it.h_c + A.tmpl_h);          // H rows that are read
     const int row = wt;                                                 // n_rows <= 256 < F_WORKERS
     const uint8_t *sl = slab + row * 16;
@@ -904,7 +966,7 @@ __device__ __forceinline__ void window_sums(const MelfMatchTcArgs &A, const Item
                     s0 += q & 0xffff; s1 += q >> 16;
                 }
                 for (int y = ya; y < yb; ++y) {
-                    *reinterpret_cast<uint2 *>(S + y * 64 + 32 * half + 2 * xp) = make_uint2(s0, s1);
+                    stg_keep2(reinterpret_cast<uint2 *>(S + y * 64 + 32 * half + 2 * xp), make_uint2(s0, s1), pol_keep);
                     const int rin = y + A.tmpl_h;                                  // <= 255 (plan cap)
                     const uint32_t vin = Htab[rin * 16 + (xp ^ (rin & 15))];
                     const uint32_t vout = Htab[y * 16 + (xp ^ (y & 15))];
@@ -928,12 +990,13 @@ __device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item
         const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
         const int n_units = ((n_rows + 7) >> 3) * 4;
         uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        const u64 pol_stream = policy_evict_first(), pol_keep = policy_evict_last();
         // warp-unit = 8 rows x 4 strips; lane = strip * 8 + row: every quarter warp stores 128
         // contiguous bytes and reads 8 rows x 192 contiguous bytes of the frame
         for (int u = wwarp; u < n_units; u += n_wwarps) {
             const int rg = u >> 2, sg = u & 3;
             const int r = rg * 8 + (lane & 7), s = sg * 4 + (lane >> 3);
-            *reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16) = stage_unit_f(A, it, r, s);
+            stg_keep(reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16), stage_unit_f(A, it, r, s, pol_stream), pol_keep);
         }
     }
 }
@@ -975,26 +1038,29 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
     const uint32_t tmem = ctrl->tmem_base;
 
     const long long n_pass = (A.n_items + 1) / 2;
-    const int n_stages = F_SPP * A.n_pairs;                           // per pass
+    const int n_ksteps = 8 * A.n_pairs;                               // K-steps of 32 per item
+    const int n_stages = (n_ksteps + F_KSTEPS - 1) / F_KSTEPS;        // per pass
     const int n_pre = n_stages < F_NSTAGE ? n_stages : F_NSTAGE;      // stages prefetched ahead of a pass
     const bool producer = warp == 0 && elect_one();
+    const u64 pol_keep = policy_evict_last();
 
     // producer helpers.  Stage g of the running stage counter uses ring slot g % F_NSTAGE; its
     // "empty" barrier has completed (g / F_NSTAGE) phases when it may be refilled.
     auto load_stage = [&](uint32_t g, int s) {
         const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
         mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
-        mbar_expect_tx(smem_u32(&ctrl->full[st]), F_STAGE_BYTES);
-        bulk_load(b_addr + st * F_STAGE_BYTES, A.toeplitz + (size_t)s * F_STAGE_BYTES, F_STAGE_BYTES,
-                  smem_u32(&ctrl->full[st]));
+        const uint32_t bytes = (uint32_t)min(F_KSTEPS, n_ksteps - s * F_KSTEPS) * (2 * BSTRIP_BYTES);
+        mbar_expect_tx(smem_u32(&ctrl->full[st]), bytes);
+        bulk_load_keep(b_addr + st * F_STAGE_BYTES, A.toeplitz + (size_t)s * F_STAGE_BYTES, bytes,
+                       smem_u32(&ctrl->full[st]), pol_keep);
     };
     auto load_slabs = [&](long long pass) {
         const int n = (2 * pass + 1 < A.n_items) ? 2 : 1;
         fence_async_all();                 // the workers' generic-proxy writes (global) / reads (slabs) first
         mbar_expect_tx(smem_u32(&ctrl->slab_full), (uint32_t)(n * SLAB_BYTES));
         for (int k = 0; k < n; ++k)
-            bulk_load(slab_addr + k * SLAB_BYTES, scratch + (size_t)k * SLAB_BYTES, SLAB_BYTES,
-                      smem_u32(&ctrl->slab_full));
+            bulk_load_keep(slab_addr + k * SLAB_BYTES, scratch + (size_t)k * SLAB_BYTES, SLAB_BYTES,
+                           smem_u32(&ctrl->slab_full), pol_keep);
     };
     auto pass_items = [&](long long pass, Item (&its)[2]) {
         its[0] = get_item(A, 2 * pass);
@@ -1040,31 +1106,39 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
             const uint32_t idesc0 = make_idesc((uint32_t)items[0].n_cols);
             const uint32_t idesc1 = make_idesc((uint32_t)items[1].n_cols);
             uint32_t g = stage_count;
+            long long waited = 0;                   // debug: clocks spent waiting for Toeplitz stages
             for (int s = 0; s < n_stages; ++s, ++g) {
                 const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
+                const long long w0 = tl ? clock64() : 0;
                 mbar_wait(smem_u32(&ctrl->full[st]), ph);
                 tc_fence_after();
+                if (tl) waited += clock64() - w0;
                 if (lead) {
-                    const int p = s / F_SPP, k0 = (s % F_SPP) * F_KSTEPS;          // pair, first K-step
-                    const uint32_t abase = b_addr + st * F_STAGE_BYTES;               // Toeplitz half pair = A
+                    const int kk0 = s * F_KSTEPS;                                     // first K-step of the stage
+                    const uint32_t abase = b_addr + st * F_STAGE_BYTES;               // Toeplitz K-steps = A
 #pragma unroll
                     for (int slot = 0; slot < 2; ++slot) {
                         if (!(slot ? items[1].valid : items[0].valid)) continue;
-                        const uint32_t bbase = slab_addr + slot * SLAB_BYTES + (2 * p) * 16 +
-                                               k0 * 2 * STRIP_BYTES;                  // slab rows 2p.. = B
                         const uint32_t d = tmem + (uint32_t)(slot * NCOLS);
 #pragma unroll
-                        for (int ks = 0; ks < F_KSTEPS; ++ks)
-                            umma_i8(d, umma_desc(abase + ks * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
-                                    umma_desc(bbase + ks * 2 * STRIP_BYTES, STRIP_BYTES),
-                                    slot ? idesc1 : idesc0, (s > 0 || ks > 0) ? 1u : 0u);
+                        for (int j = 0; j < F_KSTEPS; ++j) {
+                            const int kk = kk0 + j;
+                            if (kk < n_ksteps) {
+                                // template rows 2p, 2p+1 against slab rows 2p.. (= B), K-step ks of the pair
+                                const int pp = kk >> 3, ks = kk & 7;
+                                const uint32_t bbase = slab_addr + slot * SLAB_BYTES + (2 * pp) * 16 + ks * 2 * STRIP_BYTES;
+                                umma_i8(d, umma_desc(abase + j * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
+                                        umma_desc(bbase, STRIP_BYTES),
+                                        slot ? idesc1 : idesc0, kk > 0 ? 1u : 0u);
+                            }
+                        }
                     }
                     umma_commit(smem_u32(&ctrl->empty[st]));
                 }
                 __syncwarp();
             }
             if (lead) umma_commit(smem_u32(&ctrl->accum));
-            if (tl && lead) tl[2] = clock64();
+            if (tl && lead) tl[2] = tl[0] + waited;   // reported relative to tl[0] like the stamps
         } else {
             // ---- workers: window sums of this pass, slabs of the next one -------------------------
             const int wt = tid - 64;

@@ -1,0 +1,11 @@
+# round-1 v7 measurement script (run under gpurun): parity tests, bench lines, ncu launch list and full captures
+set -x
+timeout 200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_v7.log 2>&1; tail -2 gpurun_out/pytest_gpu_v7.log
+python bench.py > gpurun_out/bench_v7.json 2> gpurun_out/bench_v7.err || exit 1
+python bench.py --size 1280x720 --frames 4096 --steps 20 > gpurun_out/bench_v7_1280x720.json 2>> gpurun_out/bench_v7.err
+CMD="python bench.py --steps 2 --warmup 1 --cpu-frames 64 --e2e-frames 256"
+$CMD > gpurun_out/b2.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:melf -c 400 --csv --log-file gpurun_out/v7_launches.csv $CMD > gpurun_out/ncu1.log 2>&1
+$CMD > gpurun_out/b3.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:melf_match_fused -s 1 -c 1 -o gpurun_out/v7_fused -f $CMD > gpurun_out/ncu2.log 2>&1
+ls -la gpurun_out
