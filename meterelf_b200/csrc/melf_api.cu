@@ -48,6 +48,7 @@ struct melf_ctx {
     // static device data
     MelfDialDev *d_dials = nullptr;
     uint16_t *d_ring_pos = nullptr;
+    uint16_t *d_need_pos = nullptr;
     double *d_ring_angle = nullptr;
     double *d_ring_sqd = nullptr;
     uint32_t *d_tmpl_words = nullptr;
@@ -271,7 +272,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
     a.geom = geom;
     a.dials = ctx->d_dials;
-    a.ring_pos = ctx->d_ring_pos; a.ring_angle = ctx->d_ring_angle; a.ring_sqd = ctx->d_ring_sqd;
+    a.need_pos = ctx->d_need_pos; a.ring_pos = ctx->d_ring_pos; a.ring_angle = ctx->d_ring_angle; a.ring_sqd = ctx->d_ring_sqd;
     a.match_key = d_keys;
     a.pix_pitch = ctx->pix_pitch; a.pix_bytes = ctx->pix_bytes;
     a.out = d_out;
@@ -311,7 +312,7 @@ void free_ctx(melf_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_ring_angle);
+    cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_need_pos); cudaFree(ctx->d_ring_angle);
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_keys);
@@ -438,6 +439,12 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
     }
     MELF_CREATE_CUDA(cudaMalloc(&ctx->d_dials, dials.size() * sizeof(MelfDialDev)));
     MELF_CREATE_CUDA(cudaMemcpy(ctx->d_dials, dials.data(), dials.size() * sizeof(MelfDialDev), cudaMemcpyHostToDevice));
+    {
+        const size_t nn = rings.need.size() ? rings.need.size() : 1;
+        MELF_CREATE_CUDA(cudaMalloc(&ctx->d_need_pos, nn * sizeof(uint16_t)));
+        if (!rings.need.empty())
+            MELF_CREATE_CUDA(cudaMemcpy(ctx->d_need_pos, rings.need.data(), nn * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    }
     const size_t nr = rings.pos.size() ? rings.pos.size() : 1;
     MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ring_pos, nr * sizeof(uint16_t)));
     MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ring_angle, nr * sizeof(double)));

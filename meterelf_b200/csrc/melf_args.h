@@ -7,6 +7,7 @@ struct MelfDialsArgs {
     size_t row_stride, frame_stride;
     MelfGeom geom;
     const MelfDialDev *dials;
+    const uint16_t *need_pos;    // MelfDialDev::need_off slices
     const uint16_t *ring_pos;
     const double *ring_angle;
     const double *ring_sqd;

@@ -256,24 +256,40 @@ melf_dials_kernel(const MelfDialsArgs A)
         return melf_hls_arith(B, G, R, A.hue_shift);
     };
 
-    // ---- inRange over the window -> row words ----------------------------------------
+    // ---- inRange over the needed window pixels -> row words -----------------------------
+    // Only pixels within 2 px of disc | ring can reach a bit of the closed mask that is used
+    // (MelfDialDev::row_base): they are visited in a flat raster list, 32 per ballot, and the
+    // ballot words are cut back into 64-bit row words afterwards.
     u64 m0a = 0, m0b = 0;
+    {
+        uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[d]);       // 128 words >= 4096 / 32
+        const uint16_t *need = A.need_pos + D.need_off;
+        const int n_need = D.n_need;
 #pragma unroll 2
-    for (int rr = 0; rr < D.win_h; ++rr) {
-        u64 word = 0;
-        if ((RV >> rr) & 1) {
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const int cc = lane + 32 * half;
-                const bool valid = cc < D.win_w && ((V >> cc) & 1);
-                const uint32_t c = hls_win(valid ? cc : 0, rr);
-                const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
-                const bool bit = valid && H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
-                const uint32_t bal = __ballot_sync(0xffffffffu, bit);
-                word |= (u64)bal << (32 * half);
-            }
+        for (int base = 0; base < n_need; base += 32) {
+            const int p = base + lane;
+            const bool valid = p < n_need;
+            const uint32_t pos = valid ? need[p] : need[0];
+            const uint32_t c = hls_win((int)(pos & 255u), (int)(pos >> 8));
+            const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
+            const bool bit = valid && H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            if (lane == 0) bal_s[base >> 5] = bal;
         }
-        if ((rr >> 1) == lane) { if (rr & 1) m0b = word; else m0a = word; }
+        __syncwarp();
+        auto row_word = [&](int r) -> u64 {
+            const int b0 = D.row_base[r], n = D.row_base[r + 1] - b0;
+            if (n <= 0) return 0ull;
+            const int wi = b0 >> 5, sh = b0 & 31;
+            const int last = (n_need - 1) >> 5;
+            const u64 w0 = bal_s[wi], w1 = wi + 1 <= last ? bal_s[wi + 1] : 0u, w2 = wi + 2 <= last ? bal_s[wi + 2] : 0u;
+            u64 v = ((w0 | (w1 << 32)) >> sh) | (sh ? (w2 << (64 - sh)) : 0ull);
+            if (n < 64) v &= (1ull << n) - 1ull;
+            return v << D.row_c0[r];
+        };
+        m0a = row_word(2 * lane);
+        m0b = row_word(2 * lane + 1);
+        __syncwarp();                                       // bal_s (= nm_s[d]) is reused by the ring phase
     }
 
     if (tl) tl[2] = clock64();

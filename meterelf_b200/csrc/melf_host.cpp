@@ -139,6 +139,33 @@ int melf_host_build_dial(const melf_params *P, int d, MelfDialDev *out,
             }
         }
     }
+    // needed inRange pixels: 2-px Chebyshev neighbourhood of disc | ring inside the rect
+    {
+        uint64_t dr[64], need[64];
+        for (int r = 0; r < 64; r++) dr[r] = out->disc[r] | out->ring[r];
+        for (int r = 0; r < 64; r++) {
+            uint64_t v = 0;
+            for (int k = -2; k <= 2; k++)
+                if (r + k >= 0 && r + k < 64) v |= dr[r + k];
+            v = v | (v << 1) | (v << 2) | (v >> 1) | (v >> 2);
+            need[r] = ((out->rowvalid >> r) & 1) ? (v & out->colvalid) : 0;
+        }
+        out->need_off = (int32_t)rings->need.size();
+        int base = 0;
+        for (int r = 0; r < 64; r++) {
+            out->row_base[r] = (uint16_t)base;
+            out->row_c0[r] = 0;
+            if (!need[r]) continue;
+            int c0 = 0, c1 = 63;
+            while (!((need[r] >> c0) & 1)) c0++;
+            while (!((need[r] >> c1) & 1)) c1--;
+            out->row_c0[r] = (uint8_t)c0;
+            for (int c = c0; c <= c1; c++) rings->need.push_back((uint16_t)((r << 8) | c));
+            base += c1 - c0 + 1;
+        }
+        out->row_base[64] = (uint16_t)base;
+        out->n_need = base;
+    }
     std::stable_sort(entries.begin(), entries.end(), [](const Entry &p, const Entry &q) {
         if (p.a != q.a) return p.a < q.a;
         return p.s < q.s;

@@ -26,6 +26,12 @@ struct MelfDialDev {
     uint64_t ring[64];           // DialData.circle_mask
     double termx[64];            // sgn(dx)*dx^2 for dx = (win_x0+c) - center_x (_reading.py:36)
     double termy[64];            // same for rows (_reading.py:37)
+    // Pixels whose inRange bit can reach the closed mask inside disc | ring: the 5x5 dilation of
+    // disc | ring, clipped to the dials rect.  Row r contributes the columns row_c0[r] ..
+    // row_c0[r] + (row_base[r+1] - row_base[r]) - 1; flat index = row_base[r] + (c - row_c0[r]).
+    int32_t n_need, need_off;    // slice of the need table (one (row << 8) | col entry per flat index)
+    uint16_t row_base[65];
+    uint8_t row_c0[64];
 };
 
 // Ring tables: the pixels of circle_mask sorted by (angle, squared distance), which is
@@ -34,6 +40,7 @@ struct MelfRingTables {
     std::vector<uint16_t> pos;   // (row << 8) | col inside the window; also raster order key
     std::vector<double> angle;   // get_angle_by_vector(pixel - center)  (_utils.py:18-42)
     std::vector<double> sqd;     // x**2 + y**2                          (_reading.py:66)
+    std::vector<uint16_t> need;  // (row << 8) | col of every needed window pixel, raster order, all dials
 };
 
 // Host-only (no CUDA): returns MELF_OK or an error code with a message in err.

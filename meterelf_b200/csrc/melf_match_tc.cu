@@ -1213,6 +1213,7 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
         __syncwarp();
 
         const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(slot * NCOLS);
+        const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;      // <= 193 * 128 (* 255)
         long long best_num = 0;
         uint32_t best_idx = 0;
         bool has = false;
@@ -1235,8 +1236,9 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
                         const uint32_t mine = odd ? d[9 + j] : d[j];
                         const int yl = 16 * c + 8 * odd + j;
                         if (col_ok && yl < it.h_c) {
-                            const long long sum_tl = (long long)(int)(mine + other);
-                            const long long num = A.n_t * sum_tl - A.sum_t * (long long)sw[k][j];
+                            // all four factors are below 2^32: two 32 x 32 -> 64-bit multiplies
+                            const long long num = (long long)((u64)n_t32 * (u64)(mine + other)) -
+                                                  (long long)((u64)sum_t32 * (u64)sw[k][j]);
                             const uint32_t idx = (uint32_t)(it.y0 + yl) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
                             if (WRITE_MAP) map[idx] = score_of(num, A.n_t);
                             // see melf_match_tc_kernel: raster order per lane, float32 rounding only for close calls
