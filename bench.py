@@ -210,6 +210,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     device = torch.device('cuda', local)
     if world > 1:
+        # NCCL's version banner goes to stdout by default; stdout carries exactly one JSON line
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=device)
 
     gs = golden_set(1)
