@@ -160,6 +160,16 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
                         size_t row_stride, size_t frame_stride, int use_rect,
                         int32_t *d_max_xy, float *d_max_val, float *d_result, void *stream);
 
+/* ---- offline calibration -------------------------------------------------- */
+/* get_average_meter_image (_calibration.py:63-66): every frame translated so that its matched
+ * dials rect (d_match_xy, n*2 int32 as written by melf_match_template) lands on
+ * (anchor_x, anchor_y) = (30, 116) in the reference (_image.py:39-44, cv2.warpAffine with zero
+ * border), then the running float64 mean of the /255 normalised frames in frame order
+ * (_utils.py:64-88) and uint8(avg * 255 + 0.5).  d_out: h*w*3 bytes.  All buffers on `device`. */
+int melf_average_translated(int device, const uint8_t *d_bgr, int n, int h, int w,
+                            size_t row_stride, size_t frame_stride, const int32_t *d_match_xy,
+                            int anchor_x, int anchor_y, uint8_t *d_out, void *stream);
+
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 uint64_t melf_launch_count(void);
 

@@ -75,7 +75,8 @@ _lib_lock = threading.Lock()
 _SYMBOLS = (
     'melf_create', 'melf_destroy', 'melf_last_error', 'melf_abi_version',
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
-    'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read')
+    'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
+    'melf_average_translated')
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a')
 
@@ -121,6 +122,9 @@ def load_library() -> C.CDLL:
         lib.melf_match_template.argtypes = [
             C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
             C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.melf_average_translated.argtypes = [
+            C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p,
+            C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
         lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
@@ -274,6 +278,17 @@ def convert_hls_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stri
                               lo_b, hi_b, d_mask or None, stream or None)
     if rc:
         raise EngineError(rc, (lib.melf_last_error(None) or b'').decode())
+
+
+def average_translated_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stride: int,
+                              frame_stride: int, d_match_xy: int, anchor: Sequence[int],
+                              d_out: int, stream: int = 0) -> None:
+    """``melf_average_translated``: the average meter image of the offline calibration."""
+    lib = load_library()
+    rc = lib.melf_average_translated(device, d_bgr, n, h, w, row_stride, frame_stride, d_match_xy,
+                                     int(anchor[0]), int(anchor[1]), d_out, stream or None)
+    if rc:
+        raise EngineError(rc, 'melf_average_translated failed')
 
 
 def launch_count() -> int:

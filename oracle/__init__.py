@@ -235,3 +235,29 @@ def read_batch(params: OracleParams, frames: np.ndarray, n_threads: int = 1) -> 
     if rc:
         raise ValueError('frame smaller than the template')
     return res
+
+
+def average_translated(frames: np.ndarray, match_xy: np.ndarray, anchor=(30, 116)) -> np.ndarray:
+    """CPU restatement (numpy, test infrastructure) of ``get_average_meter_image``
+    (``_calibration.py:63-66``): ``get_bgr_image_t``'s integer translation with zero border
+    (``_image.py:34-44``; cv2.warpAffine of an integer shift copies pixels exactly),
+    ``normalize_image`` (``_utils.py:64-65``), the running mean of ``_image_avg_reducer``
+    (``_utils.py:83-88``: ``prev * ((n - 1) / n) + img / n``) and ``denormalize_image``
+    (``_utils.py:68-69``)."""
+    frames = np.asarray(frames)
+    (n, h, w) = frames.shape[:3]
+    avg = None
+    for f in range(n):
+        (tx, ty) = (int(anchor[0]) - int(match_xy[f][0]), int(anchor[1]) - int(match_xy[f][1]))
+        shifted = np.zeros_like(frames[f])
+        (dx0, dx1) = (max(0, tx), min(w, w + tx))
+        (dy0, dy1) = (max(0, ty), min(h, h + ty))
+        if dx0 < dx1 and dy0 < dy1:
+            shifted[dy0:dy1, dx0:dx1] = frames[f][dy0 - ty:dy1 - ty, dx0 - tx:dx1 - tx]
+        norm = shifted.astype(np.float64) / 255.0
+        if avg is None:
+            avg = norm
+        else:
+            cnt = f + 1
+            avg = avg * ((cnt - 1) / cnt) + (norm / cnt)
+    return ((avg * 255.0) + 0.5).astype(np.uint8)

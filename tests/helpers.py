@@ -138,3 +138,27 @@ def synthetic_blob_frames(rng, n, h, w, fg=(40, 60, 200), bg=(120, 130, 125), ce
         img = img + rng.integers(-noise, noise + 1, size=(h, w, 3))
         frames[i] = np.clip(img, 0, 255).astype(np.uint8)
     return frames
+
+
+def write_params_file(gs, directory):
+    """params.yml + dials.png for golden set `gs` in `directory` (no reference tree needed);
+    returns the path of params.yml."""
+    import cv2
+    import yaml
+    cv2.imwrite(os.path.join(str(directory), 'dials.png'), gs.template)
+    needle_data = [dict(
+        name=gs.names[i], color_range=dict(zip('hls', gs.dials[i]['color_range'])),
+        dist_from_center=int(gs.dist_from_center[i]), circle_thickness=int(gs.circle_thickness[i]),
+        angle_of_zero=gs.dials[i]['angle_of_zero'], center=list(gs.dials[i]['center']),
+        diameter=int(gs.diameters[i]), negative_momentum=gs.dials[i]['negative_momentum'])
+        for i in range(len(gs.names))]
+    (x0, y0, x1, y1) = gs.meter_rect
+    doc = dict(image_glob='*.png', meter_rect=dict(top_left=[x0, y0], bottom_right=[x1, y1]),
+               dials_template='dials.png', dials_template_match_threshold=int(gs.match_threshold),
+               dials_template_size=[gs.tmpl_w, gs.tmpl_h], hue_shift=gs.hue_shift,
+               needle_color=dict(h=125, l=80, s=130), needle_color_range=dict(h=9, l=45, s=35),
+               needle_data=needle_data)
+    path = os.path.join(str(directory), 'params.yml')
+    with open(path, 'w') as fp:
+        fp.write(yaml.safe_dump(doc))
+    return path
