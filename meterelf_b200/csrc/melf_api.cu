@@ -70,6 +70,8 @@ struct melf_ctx {
     // scratch for the async path
     u64 *d_keys = nullptr;
     int keys_cap = 0;
+    MelfDialSlot *d_dial_slots[3] = {nullptr, nullptr, nullptr};   // per scratch slot, like d_tc_scratch
+    int dial_slots_cap[3] = {0, 0, 0};
 
     // pipeline resources of melf_read_batch
     cudaStream_t streams[2] = {nullptr, nullptr};
@@ -268,7 +270,15 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     int rc = launch_locate(ctx, d_bgr, 3, n, frame_h, frame_w, row_stride, frame_stride, geom, d_keys,
                            nullptr, stream, scratch_slot);
     if (rc) return rc;
+    if (ctx->dial_slots_cap[scratch_slot] < n) {
+        if (ctx->d_dial_slots[scratch_slot]) cudaFree(ctx->d_dial_slots[scratch_slot]);
+        ctx->d_dial_slots[scratch_slot] = nullptr; ctx->dial_slots_cap[scratch_slot] = 0;
+        MELF_CUDA(ctx, cudaMalloc(&ctx->d_dial_slots[scratch_slot], (size_t)n * sizeof(MelfDialSlot)));
+        MELF_CUDA(ctx, cudaMemset(ctx->d_dial_slots[scratch_slot], 0, (size_t)n * sizeof(MelfDialSlot)));
+        ctx->dial_slots_cap[scratch_slot] = n;
+    }
     MelfDialsArgs a{};
+    a.slots = ctx->d_dial_slots[scratch_slot]; a.n_frames = n;
     a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
     a.geom = geom;
     a.dials = ctx->d_dials;
@@ -316,6 +326,7 @@ void free_ctx(melf_ctx *ctx)
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_keys);
+    for (int i = 0; i < 3; i++) cudaFree(ctx->d_dial_slots[i]);
     for (int i = 0; i < 3; i++) cudaFree(ctx->d_tc_scratch[i]);
     for (int i = 0; i < 2; i++) {
         if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);

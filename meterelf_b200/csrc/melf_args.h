@@ -2,6 +2,16 @@
 #pragma once
 #include "melf_common.cuh"
 
+// per-frame hand-over between the dial warps of melf_dials_kernel (they sit in different CTAs):
+// each warp deposits its dial, the last one to arrive (count) assembles the frame result and
+// resets count for the next launch
+struct MelfDialSlot {
+    double pos[MELF_MAX_DIALS];
+    int32_t flag[MELF_MAX_DIALS];   // 0 read, 1 no contours, 2 unreadable
+    uint32_t count;
+    uint32_t pad;
+};
+
 struct MelfDialsArgs {
     const uint8_t *bgr;
     size_t row_stride, frame_stride;
@@ -13,6 +23,8 @@ struct MelfDialsArgs {
     const double *ring_sqd;
     const u64 *match_key;
     melf_result *out;
+    MelfDialSlot *slots;         // [n_frames], count zero on entry
+    int32_t n_frames;
     melf_taps taps;
     double threshold;
     int32_t n_dials, tmpl_w, tmpl_h, hue_shift, s_tail;

@@ -159,22 +159,30 @@ struct DialOut {
 
 extern __shared__ __align__(16) uint8_t melf_dials_dyn[];
 
-__global__ void __launch_bounds__(32 * MELF_MAX_DIALS)
+// Work distribution: a CTA is DIALS_WPB warps that all read the SAME dial d of consecutive frames
+// (blockIdx = frame group * n_dials + d), so the warps of a CTA do equal work -- with one CTA per
+// frame the warps of the small dials idled 18 % of all warp samples at the closing barrier
+// (profiles/r01_v7_ncu_dials.txt).  The frame result is assembled by whichever dial warp of
+// the frame finishes last (MelfDialSlot).
+constexpr int DIALS_WPB = 4;
+
+__global__ void __launch_bounds__(32 * DIALS_WPB)
 melf_dials_kernel(const MelfDialsArgs A)
 {
-    __shared__ u64 nm_s[MELF_MAX_DIALS][64];
-    __shared__ DialOut dial_out[MELF_MAX_DIALS];
+    __shared__ u64 nm_s[DIALS_WPB][64];
 
-    const int f = blockIdx.x;
-    const int d = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wslot = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int d = (int)(blockIdx.x % (unsigned)A.n_dials);
+    const int f = (int)(blockIdx.x / (unsigned)A.n_dials) * DIALS_WPB + wslot;
+    if (f >= A.n_frames) return;                         // no block-wide barrier below
 
     const u64 key = A.match_key[f];
     const float max_val = melf_key_score(key);
     const uint32_t midx = melf_key_index(key);
     const int mx = (int)(midx % (uint32_t)A.geom.res_w), my = (int)(midx / (uint32_t)A.geom.res_w);
 
-    if ((double)max_val < A.threshold) {                 // _image.py:62-64 (block-uniform)
-        if (threadIdx.x == 0) {
+    if ((double)max_val < A.threshold) {                 // _image.py:62-64 (uniform over the frame's warps)
+        if (d == 0 && lane == 0) {
             melf_result r;
             r.status = MELF_ST_DIALS_NOT_FOUND;
             r.match_x = mx; r.match_y = my; r.max_val = max_val;
@@ -186,7 +194,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         return;
     }
 
-    long long *tl = (A.timeline && f < 8 && threadIdx.x == 0) ? A.timeline + 8 * f : nullptr;
+    long long *tl = (A.timeline && f < 8 && d == 0 && lane == 0) ? A.timeline + 8 * f : nullptr;
     if (tl) tl[0] = clock64();
     const MelfDialDev &D = A.dials[d];
     // pixel (u, v) of the dials rect -> crop column/row -> frame address
@@ -222,7 +230,7 @@ melf_dials_kernel(const MelfDialsArgs A)
     // 16-byte chunks that overlap its valid columns (all loads of all rows are independent and
     // in flight together), keeping the chunk grid aligned to global memory so that the byte
     // of window column c sits at pix[r * pitch + (rowaddr(r) & 15) + 3 * c].
-    uint8_t *pix = melf_dials_dyn + (size_t)d * A.pix_bytes;
+    uint8_t *pix = melf_dials_dyn + (size_t)wslot * A.pix_bytes;
     const u64 V = D.colvalid, RV = D.rowvalid;
     const uint8_t *win0 = frame + (size_t)(A.geom.crop_y0 + my + D.win_y0) * A.row_stride +
                           3 * (ptrdiff_t)(A.geom.crop_x0 + mx + D.win_x0);
@@ -262,7 +270,7 @@ melf_dials_kernel(const MelfDialsArgs A)
     // ballot words are cut back into 64-bit row words afterwards.
     u64 m0a = 0, m0b = 0;
     {
-        uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[d]);       // 128 words >= 4096 / 32
+        uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[wslot]);       // 128 words >= 4096 / 32
         const uint16_t *need = A.need_pos + D.need_off;
         const int n_need = D.n_need;
 #pragma unroll 2
@@ -289,7 +297,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         };
         m0a = row_word(2 * lane);
         m0b = row_word(2 * lane + 1);
-        __syncwarp();                                       // bal_s (= nm_s[d]) is reused by the ring phase
+        __syncwarp();                                       // bal_s (= nm_s[wslot]) is reused by the ring phase
     }
 
     if (tl) tl[2] = clock64();
@@ -387,8 +395,8 @@ melf_dials_kernel(const MelfDialsArgs A)
         // ---- ring pixels (_reading.py:51-96) ------------------------------------------
         // One traversal of the (angle, squared distance)-sorted ring table compacts the indices
         // of the kept entries into shared memory; the first kept entry has the minimum angle.
-        nm_s[d][2 * lane] = nm_a;
-        nm_s[d][2 * lane + 1] = nm_b;
+        nm_s[wslot][2 * lane] = nm_a;
+        nm_s[wslot][2 * lane + 1] = nm_b;
         __syncwarp();
         const uint16_t *rpos = A.ring_pos + D.ring_off;
         const double *rang = A.ring_angle + D.ring_off;
@@ -402,7 +410,7 @@ melf_dials_kernel(const MelfDialsArgs A)
             double a = 0.0;
             if (e < D.n_ring) {
                 const int pos = rpos[e];
-                if ((nm_s[d][pos >> 8] >> (pos & 255)) & 1) {
+                if ((nm_s[wslot][pos >> 8] >> (pos & 255)) & 1) {
                     a = rang[e];
                     kept = near_momentum(a, mom_angle);
                 }
@@ -491,12 +499,23 @@ melf_dials_kernel(const MelfDialsArgs A)
         if (A.taps.d_momentum) {
             A.taps.d_momentum[fd * 3 + 0] = mom_x; A.taps.d_momentum[fd * 3 + 1] = mom_y; A.taps.d_momentum[fd * 3 + 2] = mom_angle;
         }
-        dial_out[d] = res;
     }
-    __syncthreads();
 
-    // ---- frame result (_reading.py:98-115, 163-182) -------------------------------------
-    if (threadIdx.x == 0) {
+    // ---- frame result (_reading.py:98-115, 163-182): the last dial warp of the frame ------
+    if (lane == 0) {
+        MelfDialSlot *S = A.slots + f;
+        S->pos[d] = res.pos;
+        S->flag[d] = res.flag;
+        __threadfence();
+        const uint32_t prev = atomicAdd(&S->count, 1u);
+        if (prev != (uint32_t)A.n_dials - 1u) return;
+        __threadfence();
+        S->count = 0;                                   // ready for the next launch
+        DialOut dial_out[MELF_MAX_DIALS];
+        for (int i = 0; i < A.n_dials; i++) {
+            dial_out[i].pos = __ldcg(&S->pos[i]);
+            dial_out[i].flag = __ldcg(&S->flag[i]);
+        }
         const double nan = __longlong_as_double(0x7ff8000000000000ll);
         melf_result r;
         r.match_x = mx; r.match_y = my; r.max_val = max_val;
@@ -535,10 +554,11 @@ melf_dials_kernel(const MelfDialsArgs A)
 // host launcher (called from melf_api.cu)
 cudaError_t melf_launch_dials(const MelfDialsArgs &args, int n_frames, cudaStream_t stream)
 {
-    const int smem = args.n_dials * args.pix_bytes;
+    const int smem = DIALS_WPB * args.pix_bytes;
     cudaError_t e = cudaFuncSetAttribute(melf_dials_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          smem > 48 * 1024 ? smem : 48 * 1024);
     if (e != cudaSuccess) return e;
-    melf_dials_kernel<<<n_frames, 32 * args.n_dials, smem, stream>>>(args);
+    const unsigned grid = (unsigned)(((n_frames + DIALS_WPB - 1) / DIALS_WPB) * args.n_dials);
+    melf_dials_kernel<<<grid, 32 * DIALS_WPB, smem, stream>>>(args);
     return cudaGetLastError();
 }
