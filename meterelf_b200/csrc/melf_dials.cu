@@ -273,14 +273,35 @@ melf_dials_kernel(const MelfDialsArgs A)
         uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[wslot]);       // 128 words >= 4096 / 32
         const uint16_t *need = A.need_pos + D.need_off;
         const int n_need = D.n_need;
+        const float s_lo_f = (float)(lo_s - 1), s_hi_f = (float)(hi_s + 1);
 #pragma unroll 2
         for (int base = 0; base < n_need; base += 32) {
             const int p = base + lane;
             const bool valid = p < n_need;
             const uint32_t pos = valid ? need[p] : need[0];
-            const uint32_t c = hls_win((int)(pos & 255u), (int)(pos >> 8));
-            const int H = c & 255, L = (c >> 8) & 255, S = (c >> 16) & 255;
-            const bool bit = valid && H >= lo_h && H <= hi_h && L >= lo_l && L <= hi_l && S >= lo_s && S <= hi_s;
+            // cheap tests first: when no pixel of the 32 can pass the lightness and saturation ranges
+            // (dial face against a red needle: most groups), the saturation division and the hue are skipped
+            const int cc = (int)(pos & 255u), rr = (int)(pos >> 8);
+            const uint8_t *rowp = win0 + (size_t)rr * A.row_stride;
+            const uint8_t *pp = pix + rr * A.pix_pitch + (reinterpret_cast<uintptr_t>(rowp) & 15) + 3 * cc;
+            const uint32_t Bv = pp[0], Gv = pp[1], Rv = pp[2];
+            const bool tail = A.s_tail && melf_is_tail_col(mx + D.win_x0 + cc, crop_w);
+            const MelfHlsStage1 st1 = melf_hls_stage1(Bv, Gv, Rv);
+            // conservative saturation pre-test without the division: S = rint(255 diff / den) can only lie
+            // in [lo_s, hi_s] if 255 diff lies in [(lo_s - 1) den, (hi_s + 1) den] (half a unit of slack on
+            // each side against float32 rounding errors of ~1e-7 relative)
+            const float d255 = __fmul_rn(__fsub_rn(st1.vmax, st1.vmin), 255.f);
+            const float den0 = fminf(st1.sm, __fsub_rn(2.f, st1.sm));
+            const bool s_maybe = d255 >= __fmul_rn(s_lo_f, den0) && d255 <= __fmul_rn(s_hi_f, den0);
+            const bool l_ok = valid && (int)st1.L >= lo_l && (int)st1.L <= hi_l && (s_maybe || tail);
+            bool bit = false;
+            if (__any_sync(0xffffffffu, l_ok)) {
+                // OpenCV's scalar-tail columns differ in S only; L is the same in both forms
+                const uint32_t c = tail ? melf_hls_pixel((int)Bv, (int)Gv, (int)Rv, true, A.hue_shift)
+                                        : melf_hls_stage2(st1, A.hue_shift);
+                const int H = c & 255, S = (c >> 16) & 255;
+                bit = l_ok && H >= lo_h && H <= hi_h && S >= lo_s && S <= hi_s;
+            }
             const uint32_t bal = __ballot_sync(0xffffffffu, bit);
             if (lane == 0) bal_s[base >> 5] = bal;
         }
