@@ -1214,9 +1214,15 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
 
         const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(slot * NCOLS);
         const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;      // <= 193 * 128 (* 255)
-        long long best_num = 0;
+        // Running arg-max per lane.  The lane visits its raster indices in increasing order, so a
+        // candidate replaces the running best only if its float32 score is strictly greater.  Scores
+        // are a monotone function of the numerator and more than 4 float32 ulps of numerator distance
+        // always separate the rounded values: beyond `far` (that distance for the largest possible
+        // |numerator| = n_t * 255 * sum_t) the integer comparison decides, closer calls (rare) round.
+        const long long kNone = -(1ll << 62);
+        const long long far = (((long long)((u64)n_t32 * 255ull) * (long long)sum_t32 + A.n_t) >> 21) + 1;
+        long long best_num = kNone;
         uint32_t best_idx = 0;
-        bool has = false;
         float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
         if (it.valid) {
 #pragma unroll
@@ -1229,31 +1235,29 @@ melf_match_fused_kernel(const MelfMatchTcArgs A)
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 16; ++i) d[i] = d16[i];
+                    const int yl0 = 16 * c + 8 * odd;
+                    uint32_t idx = (uint32_t)(it.y0 + yl0) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
+                    for (int j = 0; j < 8; ++j, idx += (uint32_t)A.geom.res_w) {
                         // even sends D[2x][y0+8+j] and receives D[2x+1][y0+j+1]; odd the other way round
                         const uint32_t other = __shfl_xor_sync(0xffffffffu, odd ? d[j + 1] : d[8 + j], 1);
                         const uint32_t mine = odd ? d[9 + j] : d[j];
-                        const int yl = 16 * c + 8 * odd + j;
-                        if (col_ok && yl < it.h_c) {
-                            // all four factors are below 2^32: two 32 x 32 -> 64-bit multiplies
-                            const long long num = (long long)((u64)n_t32 * (u64)(mine + other)) -
-                                                  (long long)((u64)sum_t32 * (u64)sw[k][j]);
-                            const uint32_t idx = (uint32_t)(it.y0 + yl) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
-                            if (WRITE_MAP) map[idx] = score_of(num, A.n_t);
-                            // see melf_match_tc_kernel: raster order per lane, float32 rounding only for close calls
-                            if (!has) { best_num = num; best_idx = idx; has = true; }
-                            else if (num > best_num) {
-                                const long long mag = (best_num < 0 ? -best_num : best_num) + A.n_t;
-                                if (num - best_num > (mag >> 21) + 1 || score_of(num, A.n_t) > score_of(best_num, A.n_t)) {
-                                    best_num = num; best_idx = idx;
-                                }
-                            }
-                        }
+                        // all four factors are below 2^32: two 32 x 32 -> 64-bit multiplies
+                        const long long num = (long long)((u64)n_t32 * (u64)(mine + other)) -
+                                              (long long)((u64)sum_t32 * (u64)sw[k][j]);
+                        const bool ok = col_ok && yl0 + j < it.h_c;
+                        if (WRITE_MAP) { if (ok) map[idx] = score_of(num, A.n_t); }
+                        const long long gain = num - best_num;
+                        bool take = ok && gain > far;
+                        if (ok && gain > 0 && !take)         // close call
+                            take = score_of(num, A.n_t) > score_of(best_num, A.n_t);
+                        best_num = take ? num : best_num;
+                        best_idx = take ? idx : best_idx;
                     }
                 }
             }
         }
+        const bool has = best_num != kNone;
         if (tl && tid == 64) tl[4] = clock64();
         u64 best = has ? melf_score_key(score_of(best_num, A.n_t), best_idx) : 0ull;
 #pragma unroll
