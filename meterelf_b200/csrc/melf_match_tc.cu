@@ -736,6 +736,9 @@ __device__ __forceinline__ u64 policy_evict_last()
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
     return p;
 }
+#ifndef MELF_STAGE_PREFETCH
+#define MELF_STAGE_PREFETCH 1
+#endif
 #ifndef MELF_HINT_STREAM
 #define MELF_HINT_STREAM 2      // 1 (L1::no_allocate + L2 evict-first) measured 0.85 -> 1.06 ms: the misaligned 64-byte
 #endif                          // spans of neighbouring lanes overlap and want L1; 2 = evict-first with L1 allocation
@@ -996,6 +999,21 @@ __device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item
         for (int u = wwarp; u < n_units; u += n_wwarps) {
             const int rg = u >> 2, sg = u & 3;
             const int r = rg * 8 + (lane & 7), s = sg * 4 + (lane >> 3);
+#if MELF_STAGE_PREFETCH
+            {
+                // pull the next unit's bytes into L1 while this one is converted (no registers held)
+                const int un = u + n_wwarps;
+                const int rn = (un >> 2) * 8 + (lane & 7), sn = (un & 3) * 4 + (lane >> 3);
+                const int cy = it.y0 + rn, cx = it.x0 + 16 * sn;
+                if (un < n_units && cy < A.geom.crop_h && cx < A.geom.crop_w) {
+                    const uint8_t *src = A.img + (size_t)it.frame * A.frame_stride +
+                                         (size_t)(A.geom.crop_y0 + cy) * A.row_stride +
+                                         (size_t)A.channels * (size_t)(A.geom.crop_x0 + cx);
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(src));
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(src + 16 * A.channels - 1));
+                }
+            }
+#endif
             stg_keep(reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16), stage_unit_f(A, it, r, s, pol_stream), pol_keep);
         }
     }
