@@ -310,7 +310,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
         if (FILE *fp = std::fopen(tl_path, "w")) {
             for (int i = 0; i < 8; i++) {
                 for (int j = 0; j < 7; j++) std::fprintf(fp, "%lld ", h_tl[8 * i + j] - h_tl[8 * i]);
-                std::fprintf(fp, "\n");
+                std::fprintf(fp, "%lld\n", h_tl[8 * i + 7]);     // 32-pixel groups converted in full
             }
             std::fclose(fp);
         }

@@ -209,6 +209,40 @@ melf_dials_kernel(const MelfDialsArgs A)
         return melf_hls_arith((uint32_t)B, (uint32_t)G, (uint32_t)R, A.hue_shift);
     };
 
+    const uint16_t *need = A.need_pos + D.need_off;      // flat list of the window pixels inRange visits
+    const int n_need = D.n_need;
+    uint32_t pos_nx = lane < n_need ? need[lane] : 0u;
+
+    // ---- stage the window's BGR bytes in shared memory ----------------------------------
+    // Row r of the window occupies 3 * win_w bytes starting at an arbitrary address: fetch the
+    // 16-byte chunks that overlap its valid columns with cp.async (global -> shared without
+    // registers, so every chunk of every row is in flight at once), keeping the chunk grid
+    // aligned to global memory so that the byte of window column c sits at
+    // pix[r * pitch + (rowaddr(r) & 15) + 3 * c].  The dial colour below is computed while
+    // the copies fly.
+    uint8_t *pix = melf_dials_dyn + (size_t)wslot * A.pix_bytes;
+    const u64 V = D.colvalid, RV = D.rowvalid;
+    const uint8_t *win0 = frame + (size_t)(A.geom.crop_y0 + my + D.win_y0) * A.row_stride +
+                          3 * (ptrdiff_t)(A.geom.crop_x0 + mx + D.win_x0);
+    {
+        const int cmin = __ffsll((long long)V) - 1, cmax = 63 - __clzll((long long)V);
+        const int n_chunk = A.pix_pitch >> 4;
+        const int sub = lane >> 4, ch = lane & 15;
+        const uint32_t pix_s = (uint32_t)__cvta_generic_to_shared(pix);
+        if (ch < n_chunk && V) {
+#pragma unroll 4
+            for (int rr = sub; rr < D.win_h; rr += 2) {
+                if (!((RV >> rr) & 1)) continue;
+                const uintptr_t rowp = reinterpret_cast<uintptr_t>(win0 + (size_t)rr * A.row_stride);
+                const uintptr_t c_lo = (rowp & ~(uintptr_t)15) + 16 * (uintptr_t)ch;
+                if (c_lo + 16 > rowp + 3 * (uintptr_t)cmin && c_lo < rowp + 3 * (uintptr_t)(cmax + 1))
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                                 :: "r"(pix_s + (uint32_t)(rr * A.pix_pitch + 16 * ch)), "l"(c_lo) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
     // ---- get_dial_color: rounded mean of the 5x5 patch at int(centre) -----------------
     int sh = 0, sl = 0, ss = 0;
     if (lane < 25) {
@@ -225,34 +259,7 @@ melf_dials_kernel(const MelfDialsArgs A)
     const int lo_s = max(col_s - D.range_s, 0), hi_s = min(col_s + D.range_s, 255);
 
     if (tl) tl[1] = clock64();
-    // ---- stage the window's BGR bytes in shared memory ----------------------------------
-    // Row r of the window occupies 3 * win_w bytes starting at an arbitrary address: fetch the
-    // 16-byte chunks that overlap its valid columns (all loads of all rows are independent and
-    // in flight together), keeping the chunk grid aligned to global memory so that the byte
-    // of window column c sits at pix[r * pitch + (rowaddr(r) & 15) + 3 * c].
-    uint8_t *pix = melf_dials_dyn + (size_t)wslot * A.pix_bytes;
-    const u64 V = D.colvalid, RV = D.rowvalid;
-    const uint8_t *win0 = frame + (size_t)(A.geom.crop_y0 + my + D.win_y0) * A.row_stride +
-                          3 * (ptrdiff_t)(A.geom.crop_x0 + mx + D.win_x0);
-    {
-        const int cmin = __ffsll((long long)V) - 1, cmax = 63 - __clzll((long long)V);
-        const int n_chunk = A.pix_pitch >> 4;
-        const int sub = lane >> 4, ch = lane & 15;
-#pragma unroll 4
-        for (int r2 = 0; r2 < D.win_h; r2 += 2) {
-            const int rr = r2 + sub;
-            if (rr < D.win_h && ((RV >> rr) & 1) && ch < n_chunk && V) {
-                const uint8_t *rowp = win0 + (size_t)rr * A.row_stride;
-                const uintptr_t al = reinterpret_cast<uintptr_t>(rowp) & ~(uintptr_t)15;
-                const uintptr_t c_lo = al + 16 * (uintptr_t)ch;
-                const uintptr_t need_lo = reinterpret_cast<uintptr_t>(rowp) + 3 * (uintptr_t)cmin;
-                const uintptr_t need_hi = reinterpret_cast<uintptr_t>(rowp) + 3 * (uintptr_t)(cmax + 1);
-                if (c_lo + 16 > need_lo && c_lo < need_hi)
-                    *reinterpret_cast<uint4 *>(pix + rr * A.pix_pitch + 16 * ch) =
-                        __ldg(reinterpret_cast<const uint4 *>(c_lo));
-            }
-        }
-    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     auto hls_win = [&](int cc, int rr) -> uint32_t {
         const uint8_t *rowp = win0 + (size_t)rr * A.row_stride;
@@ -264,6 +271,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         return melf_hls_arith(B, G, R, A.hue_shift);
     };
 
+    if (tl) tl[7] = clock64() - tl[0];                   // debug: window staged
     // ---- inRange over the needed window pixels -> row words -----------------------------
     // Only pixels within 2 px of disc | ring can reach a bit of the closed mask that is used
     // (MelfDialDev::row_base): they are visited in a flat raster list, 32 per ballot, and the
@@ -271,14 +279,14 @@ melf_dials_kernel(const MelfDialsArgs A)
     u64 m0a = 0, m0b = 0;
     {
         uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[wslot]);       // 128 words >= 4096 / 32
-        const uint16_t *need = A.need_pos + D.need_off;
-        const int n_need = D.n_need;
         const float s_lo_f = (float)(lo_s - 1), s_hi_f = (float)(hi_s + 1);
 #pragma unroll 2
         for (int base = 0; base < n_need; base += 32) {
             const int p = base + lane;
             const bool valid = p < n_need;
-            const uint32_t pos = valid ? need[p] : need[0];
+            // the list entry was fetched one iteration ahead (its L2 latency is off the critical path)
+            const uint32_t pos = pos_nx;
+            pos_nx = p + 32 < n_need ? need[p + 32] : 0u;
             // cheap tests first: when no pixel of the 32 can pass the lightness and saturation ranges
             // (dial face against a red needle: most groups), the saturation division and the hue are skipped
             const int cc = (int)(pos & 255u), rr = (int)(pos >> 8);
@@ -425,16 +433,22 @@ melf_dials_kernel(const MelfDialsArgs A)
         uint16_t *klist = reinterpret_cast<uint16_t *>(pix + 512);     // <= n_ring entries (host sizes pix_bytes)
         double min_angle = 0.0;
         int n_unwrapped = 0;
+#pragma unroll 2
         for (int base = 0; base < D.n_ring; base += 32) {
             const int e = base + lane;
             bool kept = false, wrapped = false;
             double a = 0.0;
+            bool inmask = false;
             if (e < D.n_ring) {
                 const int pos = rpos[e];
-                if ((nm_s[wslot][pos >> 8] >> (pos & 255)) & 1) {
-                    a = rang[e];
-                    kept = near_momentum(a, mom_angle);
-                }
+                inmask = (nm_s[wslot][pos >> 8] >> (pos & 255)) & 1;
+            }
+            // the table is sorted by angle and the needle crosses the ring in a narrow sector: most
+            // groups of 32 entries have no pixel in the needle mask at all
+            if (!__any_sync(0xffffffffu, inmask)) continue;
+            if (inmask) {
+                a = rang[e];
+                kept = near_momentum(a, mom_angle);
             }
             const uint32_t bal = __ballot_sync(0xffffffffu, kept);
             if (n_kept == 0 && bal) min_angle = __shfl_sync(0xffffffffu, a, __ffs(bal) - 1);
