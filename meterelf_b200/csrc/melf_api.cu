@@ -280,6 +280,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     MelfDialsArgs a{};
     a.slots = ctx->d_dial_slots[scratch_slot]; a.n_frames = n;
     a.bgr = d_bgr; a.row_stride = row_stride; a.frame_stride = frame_stride;
+    a.bgr_end = d_bgr + (size_t)(n - 1) * frame_stride + (size_t)(frame_h - 1) * row_stride + (size_t)frame_w * 3;
     a.geom = geom;
     a.dials = ctx->d_dials;
     a.need_pos = ctx->d_need_pos; a.ring_pos = ctx->d_ring_pos; a.ring_angle = ctx->d_ring_angle; a.ring_sqd = ctx->d_ring_sqd;

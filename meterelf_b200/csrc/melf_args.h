@@ -14,6 +14,7 @@ struct MelfDialSlot {
 
 struct MelfDialsArgs {
     const uint8_t *bgr;
+    const uint8_t *bgr_end;      // one past the last readable byte of the frame memory
     size_t row_stride, frame_stride;
     MelfGeom geom;
     const MelfDialDev *dials;

@@ -229,15 +229,23 @@ melf_dials_kernel(const MelfDialsArgs A)
         const int n_chunk = A.pix_pitch >> 4;
         const int sub = lane >> 4, ch = lane & 15;
         const uint32_t pix_s = (uint32_t)__cvta_generic_to_shared(pix);
+        const uintptr_t end = reinterpret_cast<uintptr_t>(A.bgr_end);
         if (ch < n_chunk && V) {
 #pragma unroll 4
             for (int rr = sub; rr < D.win_h; rr += 2) {
                 if (!((RV >> rr) & 1)) continue;
                 const uintptr_t rowp = reinterpret_cast<uintptr_t>(win0 + (size_t)rr * A.row_stride);
                 const uintptr_t c_lo = (rowp & ~(uintptr_t)15) + 16 * (uintptr_t)ch;
-                if (c_lo + 16 > rowp + 3 * (uintptr_t)cmin && c_lo < rowp + 3 * (uintptr_t)(cmax + 1))
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
-                                 :: "r"(pix_s + (uint32_t)(rr * A.pix_pitch + 16 * ch)), "l"(c_lo) : "memory");
+                if (c_lo + 16 > rowp + 3 * (uintptr_t)cmin && c_lo < rowp + 3 * (uintptr_t)(cmax + 1)) {
+                    if (c_lo + 16 <= end) {
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                                     :: "r"(pix_s + (uint32_t)(rr * A.pix_pitch + 16 * ch)), "l"(c_lo) : "memory");
+                    } else {
+                        // the chunk straddles the end of the frame memory: copy only what exists
+                        for (uintptr_t q = c_lo; q < end; ++q)
+                            pix[rr * A.pix_pitch + 16 * ch + (int)(q - c_lo)] = *reinterpret_cast<const uint8_t *>(q);
+                    }
+                }
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
