@@ -9,6 +9,7 @@ the coarse momentum direction (CUDA libm vs glibc), which feeds a < 0.25 compari
 never the result itself.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -375,3 +376,28 @@ def test_large_batches_are_deterministic_and_match_the_oracle(n_frames):
     for (g, wnt) in zip(got[:k], want):
         assert_results_equal(g, wnt, len(gs.names))
     assert int(np.sum(got['status'] == 0)) > 0.5 * n_frames
+
+
+def test_two_kernel_locate_path_still_matches(tmp_path):
+    """MELF_MATCH_TWO_KERNEL=1 (the superseded preparation + correlation kernel pair kept for A/B
+    runs) is read once per process: check it in a child process against the fused default."""
+    import subprocess
+    import sys
+    gs = golden_set(2)
+    crops = gs.subset()['crops'][:10]
+    want = gs.engine(cropped_input=True).read_frames(crops)
+    np.save(str(tmp_path / 'crops.npy'), crops)
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from helpers import golden_set\n"
+        "gs = golden_set(2)\n"
+        "out = gs.engine(cropped_input=True).read_frames(np.load(%r))\n"
+        "np.save(%r, out)\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+         os.path.dirname(os.path.abspath(__file__)),
+         str(tmp_path / 'crops.npy'), str(tmp_path / 'out.npy'))
+    env = dict(os.environ, MELF_MATCH_TWO_KERNEL='1')
+    subprocess.run([sys.executable, '-c', code], check=True, env=env, timeout=300)
+    got = np.load(str(tmp_path / 'out.npy'))
+    assert got.tobytes() == want.tobytes()
