@@ -441,16 +441,16 @@ melf_dials_kernel(const MelfDialsArgs A)
         uint16_t *klist = reinterpret_cast<uint16_t *>(pix + 512);     // <= n_ring entries (host sizes pix_bytes)
         double min_angle = 0.0;
         int n_unwrapped = 0;
+        int rpos_nx = lane < D.n_ring ? (int)rpos[lane] : 0;      // fetched one iteration ahead
 #pragma unroll 2
         for (int base = 0; base < D.n_ring; base += 32) {
             const int e = base + lane;
             bool kept = false, wrapped = false;
             double a = 0.0;
             bool inmask = false;
-            if (e < D.n_ring) {
-                const int pos = rpos[e];
-                inmask = (nm_s[wslot][pos >> 8] >> (pos & 255)) & 1;
-            }
+            const int pos = rpos_nx;
+            rpos_nx = e + 32 < D.n_ring ? (int)rpos[e + 32] : 0;
+            if (e < D.n_ring) inmask = (nm_s[wslot][pos >> 8] >> (pos & 255)) & 1;
             // the table is sorted by angle and the needle crosses the ring in a narrow sector: most
             // groups of 32 entries have no pixel in the needle mask at all
             if (!__any_sync(0xffffffffu, inmask)) continue;
