@@ -27,6 +27,8 @@ cudaError_t melf_launch_match_prep(const MelfMatchTcArgs &args, cudaStream_t str
 cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 size_t melf_match_fused_scratch_bytes(int num_sms);
 cudaError_t melf_launch_match_fused(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
+size_t melf_match_fused_ov_scratch_bytes(int num_sms);
+cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
 
@@ -193,7 +195,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             if (ctx->tc_scratch_items[scratch_slot] != -1) {
                 if (ctx->d_tc_scratch[scratch_slot]) cudaFree(ctx->d_tc_scratch[scratch_slot]);
                 ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
-                const size_t bytes = melf_match_fused_scratch_bytes(ctx->num_sms);
+                const size_t bytes = melf_match_fused_ov_scratch_bytes(ctx->num_sms);     // the larger of the two layouts
                 MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], bytes));
                 MELF_CUDA(ctx, cudaMemset(ctx->d_tc_scratch[scratch_slot], 0, bytes));
                 ctx->tc_scratch_items[scratch_slot] = -1;         // marks "fused layout"
@@ -209,8 +211,13 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
             t.timeline = d_tl;
         }
+        // default: drain of pass k under the MMAs of pass k + 1 (three TMEM accumulators);
+        // MELF_MATCH_OVERLAP=0 selects the kernel with the drain between the passes (A/B runs)
+        static const bool overlap = !(std::getenv("MELF_MATCH_OVERLAP") && !std::atoi(std::getenv("MELF_MATCH_OVERLAP")));
         if (!two_kernel) {
-            MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_fused(t, ctx->num_sms, stream); }));
+            MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] {
+                return overlap ? melf_launch_match_fused_ov(t, ctx->num_sms, stream)
+                               : melf_launch_match_fused(t, ctx->num_sms, stream); }));
             g_launches += 1;
         } else
         for (t.item0 = 0; t.item0 < t.n_items; t.item0 += t.max_items) {

@@ -698,6 +698,7 @@ constexpr int F_SMEM_TOTAL = F_SMEM_CTRL + 512;
 constexpr int F_WORKERS = TC_THREADS - 64;                    // warps 2..15
 constexpr int F_WORKER_WARPS = F_WORKERS / 32;
 constexpr size_t F_SCRATCH_PER_CTA = 2 * (size_t)SLAB_BYTES + 2 * (size_t)WSUM_WORDS * 4;
+constexpr size_t F_SCRATCH_PER_CTA_OV = 2 * (size_t)SLAB_BYTES + 4 * (size_t)WSUM_WORDS * 4;   // window sums per pass parity
 
 struct CtrlF {
     unsigned long long full[F_NSTAGE];
@@ -1324,6 +1325,338 @@ cudaError_t melf_launch_match_fused(const MelfMatchTcArgs &args, int num_sms, cu
         melf_match_fused_kernel<true><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
     else
         melf_match_fused_kernel<false><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+    return cudaGetLastError();
+}
+
+
+// =======================================================================================
+// Overlapped variant of the fused kernel: the drain of pass k runs under the MMAs of pass k+1.
+// Three accumulator buffers rotate through tensor memory (item i of the CTA -> buffer i % 3,
+// 432 of 512 columns); warps 0 (producer) and 1 (issuer) never drain, so the issuer walks straight
+// into the next pass; the 14 worker warps drain (slot 0 first: its buffer is the one pass k+1 needs
+// for its second item), then do their window sums / slab staging.  No block-wide barrier inside
+// the pass loop: every hand-over is an mbarrier.
+// =======================================================================================
+namespace {
+
+struct CtrlO {
+    unsigned long long full[F_NSTAGE];
+    unsigned long long empty[F_NSTAGE];
+    unsigned long long accum;
+    unsigned long long slab_full;
+    unsigned long long prep_done;
+    unsigned long long drained[2];     // accumulator of the pass's slot 0 / slot 1 read out (14 warp arrivals)
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+}  // namespace
+
+template <bool WRITE_MAP>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
+{
+    uint8_t *smem = melf_tc_smem;
+    CtrlO *ctrl = reinterpret_cast<CtrlO *>(smem + F_SMEM_CTRL);
+    uint32_t *Htab = reinterpret_cast<uint32_t *>(smem + F_SMEM_H);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);          // provably warp-uniform
+    const uint32_t slab_addr = smem_u32(smem + SMEM_SLABS), b_addr = smem_u32(smem + F_SMEM_B);
+    // per-CTA scratch: [slab 0][slab 1][S 0][S 1] of even passes, then [S 0][S 1] of odd passes
+    uint8_t *scratch = A.slabs + (size_t)blockIdx.x * F_SCRATCH_PER_CTA_OV;
+    uint32_t *wsum_base = reinterpret_cast<uint32_t *>(scratch + 2 * (size_t)SLAB_BYTES);
+
+    if (tid == 0) {
+        for (int s = 0; s < F_NSTAGE; ++s) {
+            mbar_init(smem_u32(&ctrl->full[s]), 1);
+            mbar_init(smem_u32(&ctrl->empty[s]), 1);
+        }
+        mbar_init(smem_u32(&ctrl->accum), 1);
+        mbar_init(smem_u32(&ctrl->slab_full), 1);
+        mbar_init(smem_u32(&ctrl->prep_done), F_WORKERS);
+        mbar_init(smem_u32(&ctrl->drained[0]), F_WORKER_WARPS);
+        mbar_init(smem_u32(&ctrl->drained[1]), F_WORKER_WARPS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;"
+                     :: "r"(smem_u32(&ctrl->tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctrl->tmem_base;
+
+    const long long n_pass = (A.n_items + 1) / 2;
+    const int n_ksteps = 8 * A.n_pairs;                               // K-steps of 32 per item
+    const int n_stages = (n_ksteps + F_KSTEPS - 1) / F_KSTEPS;        // per pass
+    const int n_pre = n_stages < F_NSTAGE ? n_stages : F_NSTAGE;      // stages prefetched ahead of a pass
+    const u64 pol_keep = policy_evict_last();
+    auto pass_items = [&](long long pass, Item (&its)[2]) {
+        its[0] = get_item(A, 2 * pass);
+        its[1] = get_item(A, 2 * pass + 1);
+    };
+    // accumulator buffer of slot `slot` of this CTA's pc-th pass
+    auto acc_col = [&](uint32_t pc, int slot) -> uint32_t { return ((2u * pc + (uint32_t)slot) % 3u) * (uint32_t)NCOLS; };
+
+    if ((long long)blockIdx.x < n_pass) {
+    if (warp == 0) {
+        // =============================== producer ===============================================
+        if (elect_one()) {
+            auto load_stage = [&](uint32_t g, int s) {
+                const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
+                mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
+                const uint32_t bytes = (uint32_t)min(F_KSTEPS, n_ksteps - s * F_KSTEPS) * (2 * BSTRIP_BYTES);
+                mbar_expect_tx(smem_u32(&ctrl->full[st]), bytes);
+                bulk_load_keep(b_addr + st * F_STAGE_BYTES, A.toeplitz + (size_t)s * F_STAGE_BYTES, bytes,
+                               smem_u32(&ctrl->full[st]), pol_keep);
+            };
+            auto load_slabs = [&](long long pass) {
+                const int n = (2 * pass + 1 < A.n_items) ? 2 : 1;
+                fence_async_all();         // the workers' generic-proxy writes (global) / reads (slabs) first
+                mbar_expect_tx(smem_u32(&ctrl->slab_full), (uint32_t)(n * SLAB_BYTES));
+                for (int k = 0; k < n; ++k)
+                    bulk_load_keep(slab_addr + k * SLAB_BYTES, scratch + (size_t)k * SLAB_BYTES, SLAB_BYTES,
+                                   smem_u32(&ctrl->slab_full), pol_keep);
+            };
+            uint32_t stage_count = 0, pc = 0;
+            for (int s = 0; s < n_pre; ++s) load_stage((uint32_t)s, s);
+            mbar_wait(smem_u32(&ctrl->prep_done), 0);
+            load_slabs(blockIdx.x);
+            for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x, ++pc) {
+                for (int s = n_pre; s < n_stages; ++s) load_stage(stage_count + (uint32_t)s, s);
+                stage_count += (uint32_t)n_stages;
+                // every MMA of this pass complete (slabs, ring free) and the next slabs staged
+                mbar_wait(smem_u32(&ctrl->accum), pc & 1);
+                mbar_wait(smem_u32(&ctrl->prep_done), (pc + 1) & 1);
+                if (pass + gridDim.x < n_pass) {
+                    load_slabs(pass + gridDim.x);
+                    for (int s = 0; s < n_pre; ++s) load_stage(stage_count + (uint32_t)s, s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // =============================== issuer =================================================
+        // the whole warp walks the loop (every lane polls the barriers), one elected lane issues
+        const bool lead = elect_one();
+        uint32_t g = 0, pc = 0;
+        for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x, ++pc) {
+            Item items[2];
+            pass_items(pass, items);
+            long long *tl = (A.timeline && blockIdx.x == 0 && pc < 8) ? A.timeline + pc * 8 : nullptr;
+            if (tl && lead) tl[0] = clock64();
+            mbar_wait(smem_u32(&ctrl->slab_full), pc & 1);
+            tc_fence_after();
+            if (tl && lead) tl[1] = clock64();
+            const uint32_t idesc0 = make_idesc((uint32_t)items[0].n_cols);
+            const uint32_t idesc1 = make_idesc((uint32_t)items[1].n_cols);
+            const uint32_t d0 = tmem + acc_col(pc, 0), d1 = tmem + acc_col(pc, 1);
+            long long waited = 0;
+            for (int s = 0; s < n_stages; ++s, ++g) {
+                const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
+                const long long w0 = tl ? clock64() : 0;
+                mbar_wait(smem_u32(&ctrl->full[st]), ph);
+                tc_fence_after();
+                if (tl) waited += clock64() - w0;
+                const int kk0 = s * F_KSTEPS;                                     // first K-step of the stage
+                const uint32_t abase = b_addr + st * F_STAGE_BYTES;               // Toeplitz K-steps = A
+                if (lead && items[0].valid) {
+#pragma unroll
+                    for (int j = 0; j < F_KSTEPS; ++j) {
+                        const int kk = kk0 + j;
+                        if (kk < n_ksteps) {
+                            const int pp = kk >> 3, ks = kk & 7;
+                            umma_i8(d0, umma_desc(abase + j * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
+                                    umma_desc(slab_addr + (2 * pp) * 16 + ks * 2 * STRIP_BYTES, STRIP_BYTES),
+                                    idesc0, kk > 0 ? 1u : 0u);
+                        }
+                    }
+                }
+                if (s == 0 && pc >= 1) {
+                    // slot 1's buffer held slot 0 of the previous pass: wait until it has been read out
+                    mbar_wait(smem_u32(&ctrl->drained[0]), (pc - 1) & 1);
+                    tc_fence_after();
+                }
+                if (lead) {
+                    if (items[1].valid) {
+#pragma unroll
+                        for (int j = 0; j < F_KSTEPS; ++j) {
+                            const int kk = kk0 + j;
+                            if (kk < n_ksteps) {
+                                const int pp = kk >> 3, ks = kk & 7;
+                                umma_i8(d1, umma_desc(abase + j * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
+                                        umma_desc(slab_addr + SLAB_BYTES + (2 * pp) * 16 + ks * 2 * STRIP_BYTES, STRIP_BYTES),
+                                        idesc1, kk > 0 ? 1u : 0u);
+                            }
+                        }
+                    }
+                    umma_commit(smem_u32(&ctrl->empty[st]));
+                }
+                __syncwarp();
+            }
+            // slot 0 of the NEXT pass reuses the buffer of slot 1 of the PREVIOUS pass: it must have been
+            // read out (waiting here, before this pass's commit, keeps the barrier at most one phase ahead)
+            if (pc >= 1) {
+                mbar_wait(smem_u32(&ctrl->drained[1]), (pc - 1) & 1);
+                tc_fence_after();
+            }
+            if (lead) umma_commit(smem_u32(&ctrl->accum));
+            if (tl && lead) { tl[2] = tl[0] + waited; tl[3] = clock64(); }
+        }
+    } else {
+        // =============================== workers ================================================
+        const int wt = tid - 64, wwarp = warp - 2;
+        const int qd = warp & 3;                               // TMEM lane quadrant this warp can read
+        // drain duty inside the quadrant: quadrants 0, 1 have the warps 4,8,12 / 5,9,13; 2, 3 have four
+        const int q_members = qd < 2 ? 3 : 4;
+        const int q_index = (warp - (qd < 2 ? 4 + qd : qd)) >> 2;
+        const int x = 16 * qd + (lane >> 1);                       // result column inside the item
+        const int odd = lane & 1;
+        const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;      // <= 193 * 128 (* 255)
+        const long long kNone = -(1ll << 62);
+        const long long far = (((long long)((u64)n_t32 * 255ull) * (long long)sum_t32 + A.n_t) >> 21) + 1;
+        {
+            // prologue: slabs of this CTA's first pass
+            Item its[2];
+            pass_items(blockIdx.x, its);
+            stage_slabs(A, its, scratch, wwarp, lane);
+            fence_async_all();
+            mbar_arrive(smem_u32(&ctrl->prep_done));
+        }
+        uint32_t pc = 0;
+        for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x, ++pc) {
+            Item items[2];
+            pass_items(pass, items);
+            const bool has_next = pass + gridDim.x < n_pass;
+            long long *tl = (A.timeline && blockIdx.x == 0 && pc < 8) ? A.timeline + pc * 8 : nullptr;
+            uint32_t *wsum = wsum_base + (pc & 1) * 2 * WSUM_WORDS;
+
+            // ---- window sums of this pass, slabs of the next one ----------------------------------
+            mbar_wait(smem_u32(&ctrl->slab_full), pc & 1);
+#pragma unroll 1
+            for (int slot = 0; slot < 2; ++slot) {
+                const Item cur = slot ? items[1] : items[0];
+                if (cur.valid)
+                    window_sums(A, cur, smem + SMEM_SLABS + slot * SLAB_BYTES, Htab, wsum + slot * WSUM_WORDS, wt);
+            }
+            if (tl && wt == 0) tl[6] = clock64();
+            if (has_next) {
+                Item nxt[2];
+                pass_items(pass + gridDim.x, nxt);
+                stage_slabs(A, nxt, scratch, wwarp, lane);
+            }
+            if (tl && wt == 0) tl[7] = clock64();
+            fence_async_all();
+            mbar_arrive(smem_u32(&ctrl->prep_done));
+
+            // ---- drain (under the MMAs of the next pass) ------------------------------------------
+            mbar_wait(smem_u32(&ctrl->prep_done), (pc + 1) & 1);   // every worker's window sums are visible
+            mbar_wait(smem_u32(&ctrl->accum), pc & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int slot = 0; slot < 2; ++slot) {
+                const Item it = slot ? items[1] : items[0];
+                const int n_chunks = it.n_cols >> 4;
+                const bool col_ok = it.valid && x < it.w_c;
+                const uint32_t taddr = tmem + ((uint32_t)(32 * qd) << 16) + acc_col(pc, slot);
+                const uint32_t *S = wsum + slot * WSUM_WORDS + x;
+                float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
+                long long best_num = kNone;
+                uint32_t best_idx = 0;
+                if (it.valid) {
+                    // the window sums of a chunk are fetched (L2) while the previous chunk is scored
+                    uint32_t sw_nx[8];
+                    auto fetch_s = [&](int c) {
+                        const int y0c = 16 * c + 8 * odd;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            sw_nx[j] = (c < n_chunks && col_ok && y0c + j < it.h_c) ? __ldcg(S + (y0c + j) * 64) : 0u;
+                    };
+                    fetch_s(q_index);
+                    // ... and so are its accumulator columns (a tcgen05.ld queues behind the MMAs in flight)
+                    uint32_t d16_nx[16], d1_nx = 0;
+                    if (q_index < n_chunks) {
+                        tmem_ld16(taddr + 16 * q_index, d16_nx);
+                        tmem_ld1(taddr + 16 * q_index + 16, d1_nx);
+                    }
+#pragma unroll 1
+                    for (int c = q_index; c < n_chunks; c += q_members) {
+                        const int yl0 = 16 * c + 8 * odd;
+                        uint32_t sw[8], d[17];
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) sw[j] = sw_nx[j];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) d[i] = d16_nx[i];
+                        d[16] = d1_nx;
+                        fetch_s(c + q_members);
+                        if (c + q_members < n_chunks) {
+                            tmem_ld16(taddr + 16 * (c + q_members), d16_nx);
+                            tmem_ld1(taddr + 16 * (c + q_members) + 16, d1_nx);
+                        }
+                        uint32_t idx = (uint32_t)(it.y0 + yl0) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j, idx += (uint32_t)A.geom.res_w) {
+                            // even sends D[2x][y0+8+j] and receives D[2x+1][y0+j+1]; odd the other way round
+                            const uint32_t other = __shfl_xor_sync(0xffffffffu, odd ? d[j + 1] : d[8 + j], 1);
+                            const uint32_t mine = odd ? d[9 + j] : d[j];
+                            const long long num = (long long)((u64)n_t32 * (u64)(mine + other)) -
+                                                  (long long)((u64)sum_t32 * (u64)sw[j]);
+                            const bool ok = col_ok && yl0 + j < it.h_c;
+                            if (WRITE_MAP) { if (ok) map[idx] = score_of(num, A.n_t); }
+                            // see melf_match_fused_kernel: raster order per lane, rounding only for close calls
+                            const long long gain = num - best_num;
+                            bool take = ok && gain > far;
+                            if (ok && gain > 0 && !take)
+                                take = score_of(num, A.n_t) > score_of(best_num, A.n_t);
+                            best_num = take ? num : best_num;
+                            best_idx = take ? idx : best_idx;
+                        }
+                    }
+                }
+                // this warp is done with the slot's accumulator
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&ctrl->drained[slot]));
+                u64 best = best_num != kNone ? melf_score_key(score_of(best_num, A.n_t), best_idx) : 0ull;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
+                    best = other > best ? other : best;
+                }
+                if (lane == 0 && it.valid && best) atomicMax(A.match_key + it.frame, best);
+            }
+            if (tl && wt == 0) tl[4] = clock64();
+        }
+    }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
+}
+
+size_t melf_match_fused_ov_scratch_bytes(int num_sms) { return (size_t)num_sms * F_SCRATCH_PER_CTA_OV; }
+
+cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(melf_match_fused_ov_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(melf_match_fused_ov_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_TOTAL);
+    if (e != cudaSuccess) return e;
+    if (args.n_items <= 0) return cudaSuccess;
+    const long long n_pass = (args.n_items + 1) / 2;
+    const unsigned grid = (unsigned)(n_pass < num_sms ? n_pass : num_sms);
+    if (args.result)
+        melf_match_fused_ov_kernel<true><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+    else
+        melf_match_fused_ov_kernel<false><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
     return cudaGetLastError();
 }
 

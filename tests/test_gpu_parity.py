@@ -378,9 +378,11 @@ def test_large_batches_are_deterministic_and_match_the_oracle(n_frames):
     assert int(np.sum(got['status'] == 0)) > 0.5 * n_frames
 
 
-def test_two_kernel_locate_path_still_matches(tmp_path):
-    """MELF_MATCH_TWO_KERNEL=1 (the superseded preparation + correlation kernel pair kept for A/B
-    runs) is read once per process: check it in a child process against the fused default."""
+@pytest.mark.parametrize('env_switch', [{'MELF_MATCH_TWO_KERNEL': '1'}, {'MELF_MATCH_OVERLAP': '0'}])
+def test_alternative_locate_kernels_still_match(tmp_path, env_switch):
+    """The A/B switches (read once per process): MELF_MATCH_TWO_KERNEL=1 = the superseded preparation +
+    correlation kernel pair, MELF_MATCH_OVERLAP=0 = the fused kernel with the drain between the passes.
+    Checked in a child process against the default (fused, overlapped drain)."""
     import subprocess
     import sys
     gs = golden_set(2)
@@ -397,7 +399,7 @@ def test_two_kernel_locate_path_still_matches(tmp_path):
     ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
          os.path.dirname(os.path.abspath(__file__)),
          str(tmp_path / 'crops.npy'), str(tmp_path / 'out.npy'))
-    env = dict(os.environ, MELF_MATCH_TWO_KERNEL='1')
+    env = dict(os.environ, **env_switch)
     subprocess.run([sys.executable, '-c', code], check=True, env=env, timeout=300)
     got = np.load(str(tmp_path / 'out.npy'))
     assert got.tobytes() == want.tobytes()
