@@ -342,12 +342,13 @@ def run_ours(args):
     tc_ms = kernel_ms.get('match_tc')
     int8_peak = 2.0 * peaks['bf16_tflops']
     fused = not kernel_ms.get('match_prep')
-    tc_name = 'melf_match_fused_kernel' if fused else 'melf_match_tc_kernel'
+    overlap = os.environ.get('MELF_MATCH_OVERLAP', '1') not in ('0', '')
+    tc_name = ('melf_match_fused_ov_kernel' if overlap else 'melf_match_fused_kernel') if fused else 'melf_match_tc_kernel'
     if tc_ms:
         tops = 2.0 * macs * n / (tc_ms / 1e3) / 1e12
         crop_bytes = 250 * 250 * 3 * n
         roofline = {
-            'kernel': tc_name + (' (BGR crop -> lightness + window sums in the shadow of the MMAs; ' if fused else ' (') +
+            'kernel': tc_name + (' (BGR crop -> lightness + window sums in the shadow of the MMAs, drain under the next pass; ' if fused else ' (') +
                       'TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
             'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
             'frac': tops / int8_peak, 'traffic': traffic.get(tc_name),
