@@ -13,6 +13,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, '_build', 'libmelf_oracle.so')
+_JPEG_LIB_PATH = os.path.join(_HERE, '_build', 'libjpeg_oracle.so')
 MAX_DIALS = 8
 
 
@@ -52,9 +53,13 @@ RESULT_DTYPE = np.dtype([
 _lib = None
 
 
+def _stale(lib_path: str, src: str) -> bool:
+    return not os.path.exists(lib_path) or (
+        os.path.getmtime(lib_path) < os.path.getmtime(os.path.join(_HERE, src)))
+
+
 def build(force: bool = False) -> str:
-    if force or not os.path.exists(_LIB_PATH) or (
-            os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, 'melf_oracle.c'))):
+    if force or _stale(_LIB_PATH, 'melf_oracle.c') or _stale(_JPEG_LIB_PATH, 'jpeg_oracle.c'):
         subprocess.check_call(['make', '-C', _HERE, '-s'] + (['-B'] if force else []))
     return _LIB_PATH
 
@@ -261,3 +266,52 @@ def average_translated(frames: np.ndarray, match_xy: np.ndarray, anchor=(30, 116
             cnt = f + 1
             avg = avg * ((cnt - 1) / cnt) + (norm / cnt)
     return ((avg * 255.0) + 0.5).astype(np.uint8)
+
+
+# ---- ingest row: JPEG -> BGR as cv2.imread returns it (oracle/jpeg_oracle.c) ----
+_jpeg_lib = None
+
+
+def _jpeg() -> C.CDLL:
+    global _jpeg_lib
+    if _jpeg_lib is None:
+        build()
+        _jpeg_lib = C.CDLL(_JPEG_LIB_PATH)
+        _jpeg_lib.jo_decode_bgr.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                            C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        _jpeg_lib.jo_decode_coefficients.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.c_void_p,
+                                                     C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    return _jpeg_lib
+
+
+class JpegError(ValueError):
+    pass
+
+
+def decode_jpeg(data: bytes) -> np.ndarray:
+    """``cv2.imread`` of a baseline JPEG held in memory: (h, w, 3) uint8 BGR (_image.py:49)."""
+    data = bytes(data)
+    (w, h) = (C.c_int(), C.c_int())
+    rc = _jpeg().jo_decode_bgr(data, len(data), None, 0, w, h)
+    if rc:
+        raise JpegError('jpeg oracle: code %d' % rc)
+    out = np.empty((h.value, w.value, 3), np.uint8)
+    rc = _jpeg().jo_decode_bgr(data, len(data), out.ctypes.data, out.size, w, h)
+    if rc:
+        raise JpegError('jpeg oracle: code %d' % rc)
+    return out
+
+
+def decode_jpeg_coefficients(data: bytes, component: int) -> np.ndarray:
+    """Quantised DCT coefficients of one component: (blocks_h, blocks_w, 64) int16, natural order,
+    over the MCU-padded block grid."""
+    data = bytes(data)
+    (bw, bh) = (C.c_int(), C.c_int())
+    rc = _jpeg().jo_decode_coefficients(data, len(data), component, None, 0, bw, bh)
+    if rc:
+        raise JpegError('jpeg oracle: code %d' % rc)
+    out = np.empty((bh.value, bw.value, 64), np.int16)
+    rc = _jpeg().jo_decode_coefficients(data, len(data), component, out.ctypes.data, out.size, bw, bh)
+    if rc:
+        raise JpegError('jpeg oracle: code %d' % rc)
+    return out

@@ -1,0 +1,50 @@
+"""The JPEG oracle (oracle/jpeg_oracle.c) against what cv2.imread returned in the build
+container for the reference's sample files and for synthetic streams."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from helpers import GOLDEN
+
+
+def load_streams(path):
+    d = np.load(path)
+    blob = d['blob'].tobytes()
+    off = d['offsets']
+    return [(str(d['names'][i]), blob[off[i]:off[i + 1]], tuple(int(v) for v in d['shapes'][i]),
+             str(d['sha256'][i]), int(d['set_no'][i])) for i in range(len(d['names']))]
+
+
+def test_oracle_matches_cv2_on_committed_streams():
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    assert len(streams) >= 50
+    for (name, data, shape, sha, _) in streams:
+        img = oracle.decode_jpeg(data)
+        assert img.shape == shape + (3,), name
+        assert hashlib.sha256(img.tobytes()).hexdigest() == sha, name
+
+
+def test_oracle_matches_cv2_on_every_sample_file():
+    path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    if not os.path.exists(path):
+        pytest.skip('full JPEG set not present (git-ignored; made by make_golden_jpeg.py)')
+    streams = load_streams(path)
+    assert len(streams) == 304
+    for (name, data, shape, sha, _) in streams[::3]:
+        assert hashlib.sha256(oracle.decode_jpeg(data).tobytes()).hexdigest() == sha, name
+
+
+def test_oracle_rejects_what_it_does_not_restate():
+    (name, data, _, _, _) = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))[0]
+    with pytest.raises(oracle.JpegError):
+        oracle.decode_jpeg(b'not a jpeg')
+    with pytest.raises(oracle.JpegError):
+        oracle.decode_jpeg(data[:200])                       # headers cut short
+    prog = bytearray(data)
+    i = prog.find(b'\xff\xc0')
+    prog[i + 1] = 0xC2                                       # claim progressive
+    with pytest.raises(oracle.JpegError):
+        oracle.decode_jpeg(bytes(prog))
