@@ -160,6 +160,29 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
                         size_t row_stride, size_t frame_stride, int use_rect,
                         int32_t *d_max_xy, float *d_max_val, float *d_result, void *stream);
 
+/* ---- ingest: cv2.imread of baseline JPEG streams on the GPU ------------------- */
+/* ImageFile.get_bgr_image's cv2.imread (_image.py:49) for n JPEG streams held in HOST memory:
+ * stream i is jpeg[offsets[i] .. offsets[i+1]).  The pixels are bit-identical to OpenCV's bundled
+ * libjpeg-turbo (ISLOW IDCT, fancy upsampling).  Supported: 8-bit baseline/extended sequential
+ * Huffman, one scan, YCbCr 4:4:4 / 4:2:2 / 4:2:0 or grey, no restart intervals; every stream of a
+ * call must decode to h x w pixels with the same subsampling.  Anything else: MELF_ERR_UNSUPPORTED /
+ * MELF_ERR_INVALID with a text in melf_last_error -- never a silently different image.
+ * d_bgr: device, frame f at d_bgr + f*frame_stride, rows row_stride apart.  Asynchronous on
+ * `stream` once the streams have been copied into the library's pinned staging buffer. */
+int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n, int h, int w,
+                     uint8_t *d_bgr, size_t row_stride, size_t frame_stride, void *stream);
+
+/* Header probe of one stream (host only): size, component count, luma sampling factors.
+ * Errors are reported through melf_last_error(NULL). */
+int melf_jpeg_info(const uint8_t *jpeg, size_t len, int *h, int *w, int *components, int *h_samp,
+                   int *v_samp);
+
+/* get_meter_values over JPEG files already read into memory (_api.py:22-33 without the file
+ * I/O): decode, crop to meter_rect, locate and read, in pipelined chunks on two streams.
+ * HOST streams in, HOST results out.  Synchronous. */
+int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n,
+                         melf_result *out);
+
 /* ---- offline calibration -------------------------------------------------- */
 /* get_average_meter_image (_calibration.py:63-66): every frame translated so that its matched
  * dials rect (d_match_xy, n*2 int32 as written by melf_match_template) lands on

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, 'csrc')
 OUT_DIR = os.environ.get('MELF_OUT_DIR') or os.path.join(HERE, '_lib')
 LIB = os.path.join(OUT_DIR, 'libmeterelf_b200.so')
 
-SOURCES = ['melf_api.cu', 'melf_match.cu', 'melf_match_tc.cu', 'melf_dials.cu', 'melf_convert.cu', 'melf_calib.cu', 'melf_host.cpp']
+SOURCES = ['melf_api.cu', 'melf_match.cu', 'melf_match_tc.cu', 'melf_dials.cu', 'melf_convert.cu', 'melf_calib.cu', 'melf_jpeg.cu', 'melf_host.cpp']
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
     '-fmad=false', '-Xcompiler', '-fPIC,-ffp-contract=off,-Wall', '-Xptxas', '-v',

@@ -76,7 +76,7 @@ _SYMBOLS = (
     'melf_create', 'melf_destroy', 'melf_last_error', 'melf_abi_version',
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
-    'melf_average_translated')
+    'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch')
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a')
 
@@ -125,6 +125,11 @@ def load_library() -> C.CDLL:
         lib.melf_average_translated.argtypes = [
             C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p,
             C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.melf_decode_jpeg.argtypes = [
+            C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
+            C.c_size_t, C.c_void_p]
+        lib.melf_jpeg_info.argtypes = [C.c_void_p, C.c_size_t] + [C.POINTER(C.c_int)] * 5
+        lib.melf_read_jpeg_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
         lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
@@ -248,6 +253,23 @@ class Engine:
                 frames.strides[0], out.ctypes.data))
         return out
 
+    # -- JPEG streams in (host), results out (host): SURVEY 8f-1 -------------------------
+    def read_jpeg_streams(self, streams: Sequence[bytes]) -> np.ndarray:
+        """``get_meter_values`` over JPEG files already read into memory; RESULT_DTYPE[n]."""
+        (blob, offsets) = pack_streams(streams)
+        out = np.zeros((len(streams),), RESULT_DTYPE)
+        if len(streams):
+            self._check(self.lib.melf_read_jpeg_batch(
+                self._ctx, blob.ctypes.data, offsets.ctypes.data, len(streams), out.ctypes.data))
+        return out
+
+    def decode_jpeg_device(self, blob: np.ndarray, offsets: np.ndarray, h: int, w: int, d_bgr: int,
+                           row_stride: int, frame_stride: int, stream: int = 0) -> None:
+        """``cv2.imread`` of len(offsets)-1 JPEG streams into device BGR frames."""
+        self._check(self.lib.melf_decode_jpeg(
+            self._ctx, blob.ctypes.data, offsets.ctypes.data, len(offsets) - 1, h, w, d_bgr,
+            row_stride, frame_stride, stream))
+
     # -- device frames in, device results out (raw pointers; async on `stream`) -------
     def read_device(self, d_bgr: int, n: int, h: int, w: int, row_stride: int,
                     frame_stride: int, d_out: int, stream: int = 0,
@@ -278,6 +300,26 @@ def convert_hls_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stri
                               lo_b, hi_b, d_mask or None, stream or None)
     if rc:
         raise EngineError(rc, (lib.melf_last_error(None) or b'').decode())
+
+
+def pack_streams(streams: Sequence[bytes]) -> Tuple[np.ndarray, np.ndarray]:
+    """Concatenates byte strings into (blob u8, offsets u64[n+1]) as the JPEG entry points take."""
+    sizes = np.array([len(s) for s in streams], np.uint64)
+    offsets = np.zeros(len(streams) + 1, np.uint64)
+    np.cumsum(sizes, out=offsets[1:])
+    blob = np.frombuffer(b''.join(bytes(s) for s in streams) or b'\0', np.uint8)
+    return (blob, offsets)
+
+
+def jpeg_info(data: bytes) -> Dict[str, int]:
+    """Header probe of one JPEG stream (no GPU needed)."""
+    lib = load_library()
+    data = bytes(data)
+    vals = [C.c_int() for _ in range(5)]
+    rc = lib.melf_jpeg_info(data, len(data), *[C.byref(v) for v in vals])
+    if rc:
+        raise EngineError(rc, (lib.melf_last_error(None) or b'').decode())
+    return dict(zip(('h', 'w', 'components', 'h_samp', 'v_samp'), (v.value for v in vals)))
 
 
 def average_translated_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stride: int,

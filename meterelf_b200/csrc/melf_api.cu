@@ -17,6 +17,8 @@ dim3 melf_match_plan(MelfMatchArgs &a, int n_frames);
 cudaError_t melf_launch_match(const MelfMatchArgs &args, dim3 grid, cudaStream_t stream);
 cudaError_t melf_launch_match_unpack(const u64 *key, int n, int res_w, int32_t *xy, float *val,
                                      cudaStream_t stream);
+#include "melf_jpeg.h"
+
 cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStream_t stream);
 bool melf_match_tc_supported(int tmpl_w, int tmpl_h);
 size_t melf_match_tc_toeplitz_bytes(int tmpl_h);
@@ -37,6 +39,8 @@ std::mutex g_err_mutex;
 std::string g_create_error;
 
 constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
+constexpr int kJpegChunkFrames = 4096; // streams per pipelined chunk in melf_read_jpeg_batch: the Huffman
+                                       // stage runs one lane per stream, so a chunk must be wide
 constexpr long long kTcMaxItems = 4096; // work items per prep + correlation launch pair (~400 MB scratch)
 
 }  // namespace
@@ -82,6 +86,14 @@ struct melf_ctx {
     melf_result *d_res[2] = {nullptr, nullptr};
     melf_result *h_res = nullptr;       // pinned, 2 * kChunkFrames
     u64 *d_chunk_keys[2] = {nullptr, nullptr};
+
+    // JPEG ingest (melf_jpeg.cu): [0] caller-stream path, [1], [2] pipeline streams of melf_read_jpeg_batch
+    MelfJpegState *jpeg[3] = {nullptr, nullptr, nullptr};
+    uint8_t *d_jchunk[2] = {nullptr, nullptr};
+    size_t jchunk_bytes = 0;
+    melf_result *d_jres[2] = {nullptr, nullptr};
+    melf_result *h_jres = nullptr;      // pinned, 2 * kJpegChunkFrames
+    u64 *d_jkeys[2] = {nullptr, nullptr};
 };
 
 namespace {
@@ -341,6 +353,9 @@ void free_ctx(melf_ctx *ctx)
         cudaFree(ctx->d_chunk[i]); cudaFree(ctx->d_res[i]); cudaFree(ctx->d_chunk_keys[i]);
     }
     if (ctx->h_res) cudaFreeHost(ctx->h_res);
+    for (int i = 0; i < 3; i++) melf_jpeg_state_free(ctx->jpeg[i]);
+    for (int i = 0; i < 2; i++) { cudaFree(ctx->d_jchunk[i]); cudaFree(ctx->d_jres[i]); cudaFree(ctx->d_jkeys[i]); }
+    if (ctx->h_jres) cudaFreeHost(ctx->h_jres);
     delete ctx;
 }
 
@@ -614,6 +629,104 @@ int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
             MELF_CUDA(ctx, cudaStreamSynchronize(ctx->streams[b]));
             std::memcpy(out + pending_f0[b], ctx->h_res + (size_t)b * kChunkFrames,
                         sizeof(melf_result) * pending[b]);
+        }
+    return MELF_OK;
+}
+
+// ---- JPEG ingest ----
+int melf_jpeg_info(const uint8_t *jpeg, size_t len, int *h, int *w, int *components, int *h_samp, int *v_samp)
+{
+    std::string err;
+    if (!jpeg) return fail(nullptr, MELF_ERR_INVALID, "null stream");
+    int rc = melf_jpeg_probe(jpeg, len, h, w, components, h_samp, v_samp, &err);
+    return rc ? fail(nullptr, rc, err) : MELF_OK;
+}
+
+int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n, int h, int w,
+                     uint8_t *d_bgr, size_t row_stride, size_t frame_stride, void *stream)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if (n < 0 || h < 1 || w < 1 || (n > 0 && (!jpeg || !offsets || !d_bgr)))
+        return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
+    if (n == 0) return MELF_OK;
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    MelfJpegBatch batch{jpeg, offsets, n};
+    std::string err;
+    uint64_t launches = 0;
+    int rc = melf_jpeg_decode_range(&ctx->jpeg[0], batch, 0, n, h, w, 0, 0, w, h, d_bgr, row_stride,
+                                    frame_stride, (cudaStream_t)stream, &err, &launches);
+    g_launches += launches;
+    return rc ? fail(ctx, rc, err) : MELF_OK;
+}
+
+int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n, melf_result *out)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if (n < 0 || (n > 0 && (!jpeg || !offsets || !out))) return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
+    if (n == 0) return MELF_OK;
+    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    int h = 0, w = 0;
+    std::string err;
+    int rc = melf_jpeg_probe(jpeg + offsets[0], (size_t)(offsets[1] - offsets[0]), &h, &w, nullptr, nullptr,
+                             nullptr, &err);
+    if (rc) return fail(ctx, rc, "stream 0: " + err);
+    MelfGeom geom;
+    rc = make_geom(ctx, h, w, true, &geom);
+    if (rc) return rc;
+    // only the meter_rect pixels are converted to BGR: compact device layout [frame][crop_h][pitch]
+    const size_t pitch = ((size_t)geom.crop_w * 3 + 15) & ~(size_t)15;
+    const size_t frame_bytes = pitch * geom.crop_h;
+    const int chunk_frames = n < kJpegChunkFrames ? n : kJpegChunkFrames;
+    const size_t need = frame_bytes * chunk_frames;
+    if (!ctx->streams[0])
+        for (int i = 0; i < 2; i++) MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking));
+    if (!ctx->h_jres) {
+        for (int i = 0; i < 2; i++) {
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_jres[i], sizeof(melf_result) * kJpegChunkFrames));
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_jkeys[i], sizeof(u64) * kJpegChunkFrames));
+        }
+        MELF_CUDA(ctx, cudaMallocHost(&ctx->h_jres, sizeof(melf_result) * kJpegChunkFrames * 2));
+    }
+    if (need > ctx->jchunk_bytes) {
+        for (int i = 0; i < 2; i++) {
+            if (ctx->d_jchunk[i]) cudaFree(ctx->d_jchunk[i]);
+            ctx->d_jchunk[i] = nullptr;
+        }
+        ctx->jchunk_bytes = 0;
+        for (int i = 0; i < 2; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_jchunk[i], need));
+        ctx->jchunk_bytes = need;
+    }
+    MelfGeom cg = geom;
+    cg.crop_x0 = 0; cg.crop_y0 = 0;
+    MelfJpegBatch batch{jpeg, offsets, n};
+    int pending[2] = {0, 0}, pending_f0[2] = {0, 0};
+    int chunk = 0;
+    for (int f0 = 0; f0 < n; f0 += kJpegChunkFrames, chunk++) {
+        const int b = chunk & 1;
+        const int nf = n - f0 < kJpegChunkFrames ? n - f0 : kJpegChunkFrames;
+        cudaStream_t st = ctx->streams[b];
+        if (pending[b]) {
+            MELF_CUDA(ctx, cudaStreamSynchronize(st));
+            std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
+            pending[b] = 0;
+        }
+        uint64_t launches = 0;
+        rc = melf_jpeg_decode_range(&ctx->jpeg[1 + b], batch, f0, nf, h, w, geom.crop_x0, geom.crop_y0,
+                                    geom.crop_w, geom.crop_h, ctx->d_jchunk[b], pitch, frame_bytes, st, &err,
+                                    &launches);
+        g_launches += launches;
+        if (rc) return fail(ctx, rc, err);
+        rc = run_path(ctx, ctx->d_jchunk[b], nf, geom.crop_h, geom.crop_w, pitch, frame_bytes, cg,
+                      ctx->d_jkeys[b], ctx->d_jres[b], nullptr, st, 1 + b);
+        if (rc) return rc;
+        MELF_CUDA(ctx, cudaMemcpyAsync(ctx->h_jres + (size_t)b * kJpegChunkFrames, ctx->d_jres[b],
+                                       sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
+        pending[b] = nf; pending_f0[b] = f0;
+    }
+    for (int b = 0; b < 2; b++)
+        if (pending[b]) {
+            MELF_CUDA(ctx, cudaStreamSynchronize(ctx->streams[b]));
+            std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
         }
     return MELF_OK;
 }

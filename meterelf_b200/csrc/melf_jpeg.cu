@@ -1,0 +1,774 @@
+// Ingest row: a batch of baseline JPEG streams -> BGR frames on the device,
+// bit-identical to what cv2.imread returns (reference call site meterelf/_image.py:49; the decoder
+// behind it is OpenCV's bundled libjpeg-turbo with libjpeg defaults: ISLOW IDCT, fancy
+// upsampling, BGR output -- restated on the CPU in oracle/jpeg_oracle.c).
+//
+// The host only walks the marker segments (a few hundred bytes per stream) and uploads the
+// compressed bytes; everything else runs on the GPU:
+//
+//   melf_jpeg_destuff_kernel   one CTA per stream: removes the FF00 byte stuffing of the entropy
+//                              segment and cuts it at the first marker (two passes: first marker,
+//                              then a block-wide scan compaction).
+//   melf_jpeg_huffman_kernel   sequential Huffman decoding, one lane per stream (G lanes of a
+//                              one-warp CTA active, so that a batch spreads over all SMs); 9-bit
+//                              look-ahead tables built in shared memory straight from the DHT bytes
+//                              of the uploaded stream; coefficients stored in zig-zag order.
+//   melf_jpeg_idct_kernel      one thread per 8x8 block: dequantisation with the DQT bytes of the
+//                              stream + the 13-bit integer LLM inverse DCT (jidctint.c arithmetic),
+//                              all in registers, samples written to per-component planes.
+//   melf_jpeg_color_kernel     triangle-filter ("fancy") chroma upsampling + YCbCr -> BGR for the
+//                              requested rectangle of every frame, 4 pixels per thread.
+//
+// All four are byte/integer kernels bounded by latency (Huffman) or HBM (the rest); no tensor work.
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "melf_jpeg.h"
+
+namespace {
+
+constexpr int kLook = 9;                 // look-ahead bits of the Huffman tables in shared memory
+constexpr int kLutEntries = 1 << kLook;
+
+struct JpegDesc {                        // one per stream (device copy)
+    uint64_t base;                       // offset of the stream in the blob
+    uint64_t clean_off;                  // offset of its de-stuffed entropy bytes in the clean buffer
+    uint32_t scan_off, scan_len;         // entropy-coded segment, relative to base
+    uint32_t huff_off[4];                // luma DC, luma AC, chroma DC, chroma AC: the 16 counts, then the symbols
+    uint32_t quant_off[3];               // 64 zig-zag entries per component ...
+    uint32_t quant16;                    // ... bit c set: 16-bit big-endian entries
+    uint32_t restart;                    // restart interval in MCUs (0: none)
+};
+
+struct JpegGeom {                        // shared by every stream of a batch
+    int w, h, ncomp, hs, vs;             // luma sampling factors (chroma is 1x1)
+    int mcus_x, mcus_y, nslots;          // blocks per MCU
+    uint32_t slot_info;                  // 4 bits per slot: comp | bx << 2 | by << 3
+    int blocks_w[3], blocks_h[3];        // MCU-padded block grid per component
+    int block_off[3];                    // first block of the component inside a stream's coefficient run
+    int blocks_per_image;
+    int plane_off[3];                    // byte offset of the component's sample plane inside a stream's planes
+    int plane_bytes;
+    int ds_w, ds_h;                      // downsampled_width / height of the chroma components
+};
+
+// ---------------------------------------------------------------------------------------------
+// host: marker walk (ITU-T T.81 Annex B).  Fills `d` and checks the geometry against `g`
+// (the first stream defines it).  Returns 0, or an error text.
+// ---------------------------------------------------------------------------------------------
+int rd16(const uint8_t *p) { return (p[0] << 8) | p[1]; }
+
+const char *check_huffman(const uint8_t *seg, int avail, int *used)
+{
+    if (avail < 17) return "truncated DHT";
+    int total = 0;
+    unsigned code = 0;
+    for (int len = 1; len <= 16; len++) {
+        total += seg[len];
+        code += seg[len];
+        if (code > (1u << len)) return "over-subscribed Huffman table";
+        code <<= 1;
+    }
+    if (total > 256 || 17 + total > avail) return "truncated DHT";
+    *used = 17 + total;
+    return nullptr;
+}
+
+const char *parse_stream(const uint8_t *data, size_t len, JpegDesc *d, JpegGeom *g, bool first)
+{
+    if (len < 4 || data[0] != 0xFF || data[1] != 0xD8) return "not a JPEG stream";
+    uint32_t dht[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}}, dqt[4] = {0, 0, 0, 0};
+    bool dqt16[4] = {false, false, false, false};
+    int w = 0, h = 0, ncomp = 0, chs[3] = {0, 0, 0}, cvs[3] = {0, 0, 0}, ctq[3] = {0, 0, 0}, cid[3] = {0, 0, 0};
+    bool sof = false;
+    size_t i = 2;
+    for (;;) {
+        if (i + 4 > len || data[i] != 0xFF) return "damaged JPEG headers";
+        while (i < len && data[i] == 0xFF) i++;
+        if (i >= len) return "damaged JPEG headers";
+        const int m = data[i++];
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7)) continue;
+        if (m == 0xD9 || i + 2 > len) return "damaged JPEG headers";
+        const int L = rd16(data + i);
+        if (L < 2 || i + (size_t)L > len) return "damaged JPEG headers";
+        const uint8_t *seg = data + i + 2;
+        const int n = L - 2;
+        if (m == 0xDB) {
+            int o = 0;
+            while (o < n) {
+                const int pq = seg[o] >> 4, tq = seg[o] & 15;
+                o++;
+                if (tq > 3 || pq > 1 || o + 64 * (pq + 1) > n) return "damaged DQT";
+                dqt[tq] = (uint32_t)(seg + o - data);
+                dqt16[tq] = pq != 0;
+                o += 64 * (pq + 1);
+            }
+        } else if (m == 0xC4) {
+            int o = 0;
+            while (o < n) {
+                const int tc = seg[o] >> 4, th = seg[o] & 15;
+                if (tc > 1 || th > 3) return "damaged DHT";
+                int used = 0;
+                const char *e = check_huffman(seg + o, n - o, &used);
+                if (e) return e;
+                dht[tc][th] = (uint32_t)(seg + o + 1 - data);
+                o += used;
+            }
+        } else if (m == 0xC0 || m == 0xC1) {
+            if (n < 6 || sof) return "damaged SOF";
+            if (seg[0] != 8) return "unsupported: sample precision is not 8 bits";
+            h = rd16(seg + 1);
+            w = rd16(seg + 3);
+            ncomp = seg[5];
+            if (ncomp != 1 && ncomp != 3) return "unsupported: not a 1- or 3-component JPEG";
+            if (n < 6 + 3 * ncomp) return "damaged SOF";
+            for (int c = 0; c < ncomp; c++) {
+                cid[c] = seg[6 + 3 * c];
+                chs[c] = seg[7 + 3 * c] >> 4;
+                cvs[c] = seg[7 + 3 * c] & 15;
+                ctq[c] = seg[8 + 3 * c];
+                if (ctq[c] > 3) return "damaged SOF";
+            }
+            sof = true;
+        } else if (m >= 0xC2 && m <= 0xCF && m != 0xC8 && m != 0xCC) {
+            return "unsupported: progressive, lossless or arithmetic-coded JPEG";
+        } else if (m == 0xDD) {
+            if (n < 2) return "damaged DRI";
+            d->restart = (uint32_t)rd16(seg);
+        } else if (m == 0xDA) {
+            if (!sof) return "SOS before SOF";
+            if (n < 1 || seg[0] != ncomp || n < 1 + 2 * ncomp + 3) return "unsupported: multi-scan JPEG";
+            int td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
+            for (int c = 0; c < ncomp; c++) {
+                if (seg[1 + 2 * c] != cid[c]) return "unsupported: scan component order";
+                td[c] = seg[2 + 2 * c] >> 4;
+                ta[c] = seg[2 + 2 * c] & 15;
+                if (td[c] > 3 || ta[c] > 3) return "damaged SOS";
+            }
+            if (ncomp == 3 && (td[1] != td[2] || ta[1] != ta[2]))
+                return "unsupported: the chroma components use different Huffman tables";
+            const int cc = ncomp == 3 ? 1 : 0;
+            d->huff_off[0] = dht[0][td[0]];
+            d->huff_off[1] = dht[1][ta[0]];
+            d->huff_off[2] = dht[0][td[cc]];
+            d->huff_off[3] = dht[1][ta[cc]];
+            for (int k = 0; k < 4; k++)
+                if (!d->huff_off[k]) return "missing Huffman table";
+            d->quant16 = 0;
+            for (int c = 0; c < 3; c++) {
+                const int cu = c < ncomp ? c : 0;
+                if (!dqt[ctq[cu]]) return "missing quantisation table";
+                d->quant_off[c] = dqt[ctq[cu]];
+                if (dqt16[ctq[cu]]) d->quant16 |= 1u << c;
+            }
+            d->scan_off = (uint32_t)(i + (size_t)L);
+            d->scan_len = (uint32_t)(len - (i + (size_t)L));
+            break;
+        }
+        i += (size_t)L;
+    }
+    int hs = 1, vs = 1;
+    if (ncomp == 3) {
+        hs = chs[0];
+        vs = cvs[0];
+        if (!((hs == 1 && vs == 1) || (hs == 2 && vs == 1) || (hs == 2 && vs == 2)) ||
+            chs[1] != 1 || cvs[1] != 1 || chs[2] != 1 || cvs[2] != 1)
+            return "unsupported: chroma subsampling other than 4:4:4, 4:2:2 or 4:2:0";
+    }
+    if (first) {
+        std::memset(g, 0, sizeof *g);
+        g->w = w; g->h = h; g->ncomp = ncomp; g->hs = hs; g->vs = vs;
+        g->mcus_x = (w + 8 * hs - 1) / (8 * hs);
+        g->mcus_y = (h + 8 * vs - 1) / (8 * vs);
+        int slot = 0;
+        for (int c = 0; c < ncomp; c++) {
+            const int ch = c ? 1 : hs, cv = c ? 1 : vs;
+            for (int by = 0; by < cv; by++)
+                for (int bx = 0; bx < ch; bx++, slot++) g->slot_info |= (uint32_t)(c | bx << 2 | by << 3) << (4 * slot);
+            g->blocks_w[c] = g->mcus_x * ch;
+            g->blocks_h[c] = g->mcus_y * cv;
+            g->block_off[c] = g->blocks_per_image;
+            g->blocks_per_image += g->blocks_w[c] * g->blocks_h[c];
+            g->plane_off[c] = g->plane_bytes;
+            g->plane_bytes += g->blocks_w[c] * g->blocks_h[c] * 64;
+        }
+        g->nslots = slot;
+        g->ds_w = (w + hs - 1) / hs;
+        g->ds_h = (h + vs - 1) / vs;
+    } else if (w != g->w || h != g->h || ncomp != g->ncomp || hs != g->hs || vs != g->vs) {
+        return "the streams of a batch must share size, component count and subsampling";
+    }
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 0: remove byte stuffing, cut at the first marker
+// ---------------------------------------------------------------------------------------------
+constexpr int DESTUFF_THREADS = 128;
+constexpr int DESTUFF_PER_THREAD = 16;
+
+__global__ void __launch_bounds__(DESTUFF_THREADS)
+melf_jpeg_destuff_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restrict__ desc,
+                         uint8_t *__restrict__ clean, uint32_t *__restrict__ clean_len)
+{
+    __shared__ uint32_t s_first;
+    __shared__ uint32_t s_warp[DESTUFF_THREADS / 32];
+    __shared__ uint32_t s_base;
+    const JpegDesc d = desc[blockIdx.x];
+    const uint8_t *src = blob + d.base + d.scan_off;
+    const uint32_t len = d.scan_len;
+    const int tid = threadIdx.x;
+    if (tid == 0) { s_first = len; s_base = 0; }
+    __syncthreads();
+    // pass 1: first 0xFF that is followed by neither 0x00 nor a restart marker code (the end of the data)
+    uint32_t first = len;
+    for (uint32_t j = tid; j < len; j += DESTUFF_THREADS) {
+        if (src[j] == 0xFF) {
+            const uint8_t nx = j + 1 < len ? src[j + 1] : 0xD9;
+            if (nx != 0x00 && (nx & 0xF8) != 0xD0) { first = j; break; }
+        }
+    }
+    if (first < len) atomicMin(&s_first, first);
+    __syncthreads();
+    const uint32_t end = s_first;
+    // pass 2: copy [0, end) without the zero that follows a data 0xFF and without the RSTn markers
+    // (whole bytes, so the decoder's byte alignment at a restart survives)
+    uint8_t *dst = clean + d.clean_off;
+    const uint32_t tile = DESTUFF_THREADS * DESTUFF_PER_THREAD;
+    for (uint32_t t0 = 0; t0 < end; t0 += tile) {
+        const uint32_t j0 = t0 + tid * DESTUFF_PER_THREAD;
+        uint8_t b[DESTUFF_PER_THREAD];
+        uint32_t keep = 0;
+        uint8_t prev = (j0 > 0 && j0 <= end) ? src[j0 - 1] : 0;
+#pragma unroll
+        for (int k = 0; k < DESTUFF_PER_THREAD; k++) {
+            const uint32_t j = j0 + k;
+            b[k] = j < end ? src[j] : 0;
+            const uint8_t nx = (b[k] == 0xFF && j + 1 < end) ? src[j + 1] : 0;
+            const bool drop = (prev == 0xFF && (b[k] == 0x00 || (b[k] & 0xF8) == 0xD0)) ||
+                              (b[k] == 0xFF && (nx & 0xF8) == 0xD0);
+            if (j < end && !drop) keep |= 1u << k;
+            prev = (prev == 0xFF && b[k] == 0x00) ? 0x01 : b[k];   // a stuffed zero ends the FF pair
+        }
+        const uint32_t cnt = __popc(keep);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((tid & 31) >= o) incl += v;
+        }
+        if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+        __syncthreads();
+        uint32_t before = s_base, total = 0;
+#pragma unroll
+        for (int wi = 0; wi < DESTUFF_THREADS / 32; wi++) {
+            if (wi < (tid >> 5)) before += s_warp[wi];
+            total += s_warp[wi];
+        }
+        uint32_t o = before + incl - cnt;
+#pragma unroll
+        for (int k = 0; k < DESTUFF_PER_THREAD; k++)
+            if (keep >> k & 1) dst[o++] = b[k];
+        __syncthreads();
+        if (tid == 0) s_base += total;
+        __syncthreads();
+    }
+    // zero padding: the decoder reads whole words and is fed zero bits after the data (jdhuff.c)
+    const uint32_t out_len = s_base;
+    for (uint32_t j = out_len + tid; j < ((out_len + 15) & ~15u) + 16; j += DESTUFF_THREADS) dst[j] = 0;
+    if (tid == 0) clean_len[blockIdx.x] = out_len;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 1: Huffman decoding (T.81 F.2.2; libjpeg jdhuff.c decode_mcu), one lane per stream
+// ---------------------------------------------------------------------------------------------
+struct HuffSmem {                         // per stream
+    uint16_t lut[4][kLutEntries];         // (code length << 8) | symbol for codes of <= kLook bits, else 0
+    int32_t maxcode[4][8];                // lengths kLook+1 .. 16: largest code of that length (-1: none) ...
+    int32_t valoff[4][8];                 // ... and symbol index - code of its first code
+};
+
+// Builds the tables of one stream with the whole warp.
+__device__ void build_tables(HuffSmem &S, const uint8_t *__restrict__ stream, const JpegDesc &d, int lane)
+{
+    for (int t = 0; t < 4; t++) {
+        const uint8_t *counts = stream + d.huff_off[t];
+        const uint8_t *symbols = counts + 16;
+        // canonical code assignment (T.81 Annex C), the same on every lane
+        int first[17], valptr[17], cnt[17];
+        int code = 0, k = 0;
+#pragma unroll
+        for (int l = 1; l <= 16; l++) {
+            cnt[l] = counts[l - 1];
+            first[l] = code;
+            valptr[l] = k;
+            code = (code + cnt[l]) << 1;
+            k += cnt[l];
+        }
+        for (int i = lane; i < kLutEntries; i += 32) {
+            uint16_t e = 0;
+#pragma unroll
+            for (int l = 1; l <= kLook; l++) {
+                const int c = i >> (kLook - l);
+                if (e == 0 && c >= first[l] && c - first[l] < cnt[l])
+                    e = (uint16_t)((l << 8) | symbols[valptr[l] + c - first[l]]);
+            }
+            S.lut[t][i] = e;
+        }
+        if (lane < 16 - kLook) {
+            int mc = -1, vo = 0;
+#pragma unroll
+            for (int l = kLook + 1; l <= 16; l++)
+                if (l - kLook - 1 == lane) {
+                    mc = cnt[l] ? first[l] + cnt[l] - 1 : -1;
+                    vo = valptr[l] - first[l];
+                }
+            S.maxcode[t][lane] = mc;
+            S.valoff[t][lane] = vo;
+        }
+    }
+}
+
+template <int G>
+__global__ void __launch_bounds__(32)
+melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
+                         const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ clean_len,
+                         int n, const JpegGeom g, int16_t *__restrict__ coef)
+{
+    extern __shared__ __align__(16) unsigned char huff_smem[];
+    HuffSmem *S = reinterpret_cast<HuffSmem *>(huff_smem);
+    const int lane = threadIdx.x;
+    const int img0 = blockIdx.x * G;
+    for (int gi = 0; gi < G && img0 + gi < n; gi++) {
+        const JpegDesc d = desc[img0 + gi];
+        build_tables(S[gi], blob + d.base, d, lane);
+    }
+    __syncwarp();
+    const int img = img0 + lane;
+    if (lane >= G || img >= n) return;
+    const HuffSmem &T = S[lane];
+    const JpegDesc d = desc[img];
+    const uint8_t *stream = blob + d.base;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + d.clean_off);
+    const int wmax = (int)((clean_len[img] + 3) >> 2);
+    int16_t *out = coef + (size_t)img * g.blocks_per_image * 64;
+
+    unsigned long long acc = 0;
+    int nbits = 0, wp = 0;
+    uint32_t nextw = wmax > 0 ? src[0] : 0;
+    int pred0 = 0, pred1 = 0, pred2 = 0;
+    int slot = 0, mx = 0, my = 0, k = 0, comp = 0, in_interval = 0;
+    int16_t *blk = out;
+    const int total_blocks = g.mcus_x * g.mcus_y * g.nslots;
+    int done = 0;
+    while (done < total_blocks) {
+        if (nbits <= 32) {
+            acc |= (unsigned long long)__byte_perm(nextw, 0, 0x0123) << (32 - nbits);
+            nbits += 32;
+            wp++;
+            nextw = wp < wmax ? src[wp] : 0;
+        }
+        const bool is_dc = k == 0;
+        const int t = (comp ? 2 : 0) + (is_dc ? 0 : 1);
+        const uint32_t e = T.lut[t][(uint32_t)(acc >> (64 - kLook))];
+        int len = (int)(e >> 8), sym = (int)(e & 255);
+        if (e == 0) {                                    // code longer than kLook bits (rare)
+            len = 17;
+            sym = 0;
+#pragma unroll
+            for (int l = kLook + 1; l <= 16; l++) {
+                const int c = (int)(acc >> (64 - l));
+                if (len == 17 && c <= T.maxcode[t][l - kLook - 1]) {
+                    len = l;
+                    sym = stream[d.huff_off[t] + 16 + ((c + T.valoff[t][l - kLook - 1]) & 255)];
+                }
+            }
+            if (len == 17) { len = 16; sym = 0; }        // invalid code: libjpeg warns and returns 0
+        }
+        const int s = sym & 15, r = sym >> 4;
+        const uint32_t bits = (uint32_t)(((acc << len) >> 1) >> (63 - s));
+        acc <<= (len + s);
+        nbits -= len + s;
+        const int v = (s && bits < (1u << (s - 1))) ? (int)bits - (1 << s) + 1 : (int)bits;   // EXTEND
+        if (is_dc) {
+            int p = comp == 0 ? pred0 : comp == 1 ? pred1 : pred2;
+            p += v;
+            if (comp == 0) pred0 = p; else if (comp == 1) pred1 = p; else pred2 = p;
+            blk[0] = (int16_t)p;
+            k = 1;
+        } else if (s) {
+            k += r;
+            if (k < 64) blk[k] = (int16_t)v;
+            k++;
+        } else {
+            k = r == 15 ? k + 16 : 64;
+        }
+        if (k >= 64) {                                   // next block of the MCU / next MCU
+            k = 0;
+            done++;
+            if (++slot == g.nslots) {
+                slot = 0;
+                if (++mx == g.mcus_x) { mx = 0; my++; }
+                if (d.restart && ++in_interval == (int)d.restart) {   // jdhuff.c process_restart
+                    in_interval = 0;
+                    const int drop = nbits & 7;                       // to the byte boundary
+                    acc <<= drop;
+                    nbits -= drop;
+                    pred0 = pred1 = pred2 = 0;
+                }
+            }
+            const uint32_t info = g.slot_info >> (4 * slot);
+            comp = info & 3;
+            const int bx = info >> 2 & 1, by = info >> 3 & 1;
+            const int ch = comp ? 1 : g.hs, cv = comp ? 1 : g.vs;
+            const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
+            const int boff = comp == 0 ? g.block_off[0] : comp == 1 ? g.block_off[1] : g.block_off[2];
+            blk = out + ((size_t)boff + (size_t)(my * cv + by) * bw + (mx * ch + bx)) * 64;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 2: dequantisation + inverse DCT (libjpeg jidctint.c jpeg_idct_islow), one thread per block
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
+
+// One 8-point pass of the Loeffler-Ligtenberg-Moschytz flow graph with libjpeg's 13-bit constants.
+__device__ __forceinline__ void idct8(int i0, int i1, int i2, int i3, int i4, int i5, int i6, int i7,
+                                      int shift, int (&o)[8])
+{
+    int z1 = (i2 + i6) * 4433;
+    int tmp2 = z1 + i6 * (-15137);
+    int tmp3 = z1 + i2 * 6270;
+    int tmp0 = (int)((unsigned)(i0 + i4) << 13);
+    int tmp1 = (int)((unsigned)(i0 - i4) << 13);
+    const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+    tmp0 = i7; tmp1 = i5; tmp2 = i3; tmp3 = i1;
+    z1 = tmp0 + tmp3;
+    int z2 = tmp1 + tmp2, z3 = tmp0 + tmp2, z4 = tmp1 + tmp3;
+    const int z5 = (z3 + z4) * 9633;
+    tmp0 *= 2446; tmp1 *= 16819; tmp2 *= 25172; tmp3 *= 12299;
+    z1 *= -7373; z2 *= -20995; z3 *= -16069; z4 *= -3196;
+    z3 += z5; z4 += z5;
+    tmp0 += z1 + z3; tmp1 += z2 + z4; tmp2 += z2 + z3; tmp3 += z1 + z4;
+    o[0] = descale(tmp10 + tmp3, shift); o[7] = descale(tmp10 - tmp3, shift);
+    o[1] = descale(tmp11 + tmp2, shift); o[6] = descale(tmp11 - tmp2, shift);
+    o[2] = descale(tmp12 + tmp1, shift); o[5] = descale(tmp12 - tmp1, shift);
+    o[3] = descale(tmp13 + tmp0, shift); o[4] = descale(tmp13 - tmp0, shift);
+}
+
+constexpr int IDCT_THREADS = 128;
+
+__global__ void __launch_bounds__(IDCT_THREADS)
+melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restrict__ desc,
+                      const int16_t *__restrict__ coef, const JpegGeom g, uint8_t *__restrict__ planes)
+{
+    constexpr uint8_t ZZ[64] = {
+        0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43,
+        9, 11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60,
+        21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};
+    const int img = blockIdx.y;
+    const int b = blockIdx.x * IDCT_THREADS + threadIdx.x;
+    if (b >= g.blocks_per_image) return;
+    const int comp = b >= g.block_off[2] && g.ncomp == 3 ? 2 : (b >= g.block_off[1] && g.ncomp == 3 ? 1 : 0);
+    const int local = b - (comp == 0 ? 0 : comp == 1 ? g.block_off[1] : g.block_off[2]);
+    const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
+    const int by = local / bw, bx = local - by * bw;
+    const JpegDesc d = desc[img];
+    const uint8_t *q = blob + d.base + (comp == 0 ? d.quant_off[0] : comp == 1 ? d.quant_off[1] : d.quant_off[2]);
+    const bool q16 = d.quant16 >> comp & 1;
+
+    // 64 coefficients (zig-zag order in memory) -> registers, dequantised
+    const uint4 *src = reinterpret_cast<const uint4 *>(coef + ((size_t)img * g.blocks_per_image + b) * 64);
+    int z[64];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const uint4 v = __ldg(src + j);
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            z[8 * j + 2 * k] = (int)(int16_t)(w4[k] & 0xFFFF);
+            z[8 * j + 2 * k + 1] = (int)(int16_t)(w4[k] >> 16);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 64; j++) {
+        const int qv = q16 ? (q[2 * j] << 8 | q[2 * j + 1]) : q[j];
+        z[j] *= qv;
+    }
+    // pass 1: columns (natural index = 8 * row + col)
+    int ws[64];
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        int o[8];
+        idct8(z[ZZ[c]], z[ZZ[8 + c]], z[ZZ[16 + c]], z[ZZ[24 + c]], z[ZZ[32 + c]], z[ZZ[40 + c]],
+              z[ZZ[48 + c]], z[ZZ[56 + c]], 13 - 2, o);
+#pragma unroll
+        for (int r = 0; r < 8; r++) ws[8 * r + c] = o[r];
+    }
+    // pass 2: rows, range limit (+128, clamp), 8 samples = one 8-byte store
+    const int stride = bw * 8;
+    uint8_t *dst = planes + (size_t)img * g.plane_bytes +
+                   (comp == 0 ? g.plane_off[0] : comp == 1 ? g.plane_off[1] : g.plane_off[2]) +
+                   (size_t)by * 8 * stride + bx * 8;
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        int o[8];
+        idct8(ws[8 * r], ws[8 * r + 1], ws[8 * r + 2], ws[8 * r + 3], ws[8 * r + 4], ws[8 * r + 5],
+              ws[8 * r + 6], ws[8 * r + 7], 13 + 2 + 3, o);
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            lo |= (uint32_t)min(max(o[c] + 128, 0), 255) << (8 * c);
+            hi |= (uint32_t)min(max(o[4 + c] + 128, 0), 255) << (8 * c);
+        }
+        *reinterpret_cast<uint2 *>(dst + (size_t)r * stride) = make_uint2(lo, hi);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel 3: chroma upsampling (libjpeg jdsample.c, edge rows per jdmainct.c) + YCbCr -> BGR
+// (jdcolor.c), 4 pixels of one row per thread, for the rectangle [x0, x0+cw) x [y0, y0+ch)
+// ---------------------------------------------------------------------------------------------
+struct ColorArgs {
+    const uint8_t *planes;
+    uint8_t *out;
+    size_t row_stride, frame_stride;
+    int x0, y0, cw, ch, n;
+};
+
+__device__ __forceinline__ int upsampled(const uint8_t *__restrict__ p, int stride, const JpegGeom &g,
+                                         int x, int y)
+{
+    if (g.hs == 1) return p[(size_t)y * stride + x];
+    const int cx = x >> 1, last = g.ds_w - 1;
+    if (g.ds_w <= 2) return p[(size_t)(g.vs == 2 ? y >> 1 : y) * stride + cx];   // jinit_upsampler: replicate
+    if (g.vs == 1) {                                                           // h2v1_fancy_upsample
+        const uint8_t *r = p + (size_t)y * stride;
+        const int v = r[cx];
+        if (x & 1) return cx == last ? v : (3 * v + r[cx + 1] + 2) >> 2;
+        return cx == 0 ? v : (3 * v + r[cx - 1] + 1) >> 2;
+    }
+    const int cy = y >> 1;                                                     // h2v2_fancy_upsample
+    const int oy = min(max((y & 1) ? cy + 1 : cy - 1, 0), g.ds_h - 1);
+    const uint8_t *r0 = p + (size_t)cy * stride, *r1 = p + (size_t)oy * stride;
+    const int cur = 3 * r0[cx] + r1[cx];
+    if (x & 1) {
+        if (cx == last) return (4 * cur + 7) >> 4;
+        return (3 * cur + 3 * r0[cx + 1] + r1[cx + 1] + 7) >> 4;
+    }
+    if (cx == 0) return (4 * cur + 8) >> 4;
+    return (3 * cur + 3 * r0[cx - 1] + r1[cx - 1] + 8) >> 4;
+}
+
+constexpr int COLOR_THREADS = 128;
+
+__global__ void __launch_bounds__(COLOR_THREADS)
+melf_jpeg_color_kernel(const ColorArgs a, const JpegGeom g)
+{
+    const int groups = (a.cw + 3) >> 2;
+    const int t = blockIdx.x * COLOR_THREADS + threadIdx.x;
+    const int y = a.y0 + blockIdx.y, img = blockIdx.z;
+    if (t >= groups) return;
+    const uint8_t *pl = a.planes + (size_t)img * g.plane_bytes;
+    const uint8_t *yp = pl + g.plane_off[0] + (size_t)y * (g.blocks_w[0] * 8);
+    const int cstride = g.blocks_w[1] * 8;
+    uint8_t *o = a.out + (size_t)img * a.frame_stride + (size_t)blockIdx.y * a.row_stride + (size_t)t * 12;
+    uint8_t px[12];
+    const int npx = min(4, a.cw - 4 * t);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = a.x0 + 4 * t + (k < npx ? k : 0);
+        const int yy = yp[x];
+        int b = yy, gg = yy, r = yy;
+        if (g.ncomp == 3) {
+            const int cb = upsampled(pl + g.plane_off[1], cstride, g, x, y) - 128;
+            const int cr = upsampled(pl + g.plane_off[2], cstride, g, x, y) - 128;
+            r = yy + ((91881 * cr + 32768) >> 16);                       // FIX(1.40200)
+            gg = yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16);         // FIX(0.34414), FIX(0.71414)
+            b = yy + ((116130 * cb + 32768) >> 16);                      // FIX(1.77200)
+        }
+        px[3 * k] = (uint8_t)min(max(b, 0), 255);
+        px[3 * k + 1] = (uint8_t)min(max(gg, 0), 255);
+        px[3 * k + 2] = (uint8_t)min(max(r, 0), 255);
+    }
+    if (npx == 4 && ((reinterpret_cast<uintptr_t>(o) & 3) == 0)) {
+        uint32_t *o32 = reinterpret_cast<uint32_t *>(o);
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+            o32[k] = px[4 * k] | px[4 * k + 1] << 8 | px[4 * k + 2] << 16 | (uint32_t)px[4 * k + 3] << 24;
+    } else {
+        for (int k = 0; k < 3 * npx; k++) o[k] = px[k];
+    }
+}
+
+template <typename T>
+cudaError_t grow(T **p, size_t *cap, size_t need)
+{
+    if (need <= *cap) return cudaSuccess;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    const size_t bytes = need + need / 8;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(p), bytes);
+    if (e == cudaSuccess) *cap = bytes;
+    return e;
+}
+
+}  // namespace
+
+struct MelfJpegState {
+    uint8_t *d_blob = nullptr;      size_t blob_cap = 0;
+    uint8_t *d_clean = nullptr;     size_t clean_cap = 0;
+    JpegDesc *d_desc = nullptr;     size_t desc_cap = 0;
+    uint32_t *d_clean_len = nullptr; size_t len_cap = 0;
+    int16_t *d_coef = nullptr;      size_t coef_cap = 0;
+    uint8_t *d_planes = nullptr;    size_t planes_cap = 0;
+    uint8_t *h_stage = nullptr;     size_t stage_cap = 0;     // pinned: descriptors + streams of one call
+    cudaEvent_t uploaded = nullptr;
+    bool upload_pending = false;
+};
+
+void melf_jpeg_state_free(MelfJpegState *s)
+{
+    if (!s) return;
+    cudaFree(s->d_blob); cudaFree(s->d_clean); cudaFree(s->d_desc); cudaFree(s->d_clean_len);
+    cudaFree(s->d_coef); cudaFree(s->d_planes);
+    if (s->h_stage) cudaFreeHost(s->h_stage);
+    if (s->uploaded) cudaEventDestroy(s->uploaded);
+    delete s;
+}
+
+int melf_jpeg_probe(const uint8_t *jpeg, size_t len, int *h, int *w, int *ncomp, int *hs, int *vs,
+                    std::string *err)
+{
+    JpegDesc d{};
+    JpegGeom g{};
+    const char *e = parse_stream(jpeg, len, &d, &g, true);
+    if (e) {
+        if (err) *err = e;
+        return std::strncmp(e, "unsupported", 11) == 0 ? 3 : 1;
+    }
+    if (h) *h = g.h;
+    if (w) *w = g.w;
+    if (ncomp) *ncomp = g.ncomp;
+    if (hs) *hs = g.hs;
+    if (vs) *vs = g.vs;
+    return 0;
+}
+
+#define JPEG_CUDA(call)                                                            \
+    do {                                                                           \
+        cudaError_t e_ = (call);                                                   \
+        if (e_ != cudaSuccess) {                                                   \
+            if (err) *err = std::string(#call) + ": " + cudaGetErrorString(e_);    \
+            return 2;                                                              \
+        }                                                                          \
+    } while (0)
+
+int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, int first, int count,
+                           int h, int w, int x0, int y0, int cw, int ch, uint8_t *d_out,
+                           size_t row_stride, size_t frame_stride, cudaStream_t stream,
+                           std::string *err, uint64_t *launches)
+{
+    if (count <= 0) return 0;
+    if (!*state) *state = new MelfJpegState();
+    MelfJpegState &S = **state;
+    if (!S.uploaded) JPEG_CUDA(cudaEventCreateWithFlags(&S.uploaded, cudaEventDisableTiming));
+
+    // ---- host: marker walk, descriptors, staging copy ----
+    const uint64_t blob0 = batch.offsets[first];
+    const size_t blob_bytes = (size_t)(batch.offsets[first + count] - blob0);
+    const size_t desc_bytes = ((size_t)count * sizeof(JpegDesc) + 255) & ~(size_t)255;
+    if (S.upload_pending) {             // the staging buffer is still the source of the previous upload
+        JPEG_CUDA(cudaEventSynchronize(S.uploaded));
+        S.upload_pending = false;
+    }
+    if (desc_bytes + blob_bytes + 16 > S.stage_cap) {
+        if (S.h_stage) cudaFreeHost(S.h_stage);
+        S.h_stage = nullptr;
+        S.stage_cap = 0;
+        const size_t bytes = (desc_bytes + blob_bytes + 16) * 5 / 4;
+        JPEG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&S.h_stage), bytes));
+        S.stage_cap = bytes;
+    }
+    JpegDesc *descs = reinterpret_cast<JpegDesc *>(S.h_stage);
+    JpegGeom g{};
+    size_t clean_bytes = 0;
+    for (int i = 0; i < count; i++) {
+        const uint64_t o0 = batch.offsets[first + i], o1 = batch.offsets[first + i + 1];
+        if (o1 < o0 || o1 - o0 > 0xFFFFFFF0ull) {
+            if (err) *err = "bad stream offsets";
+            return 1;
+        }
+        JpegDesc &d = descs[i];
+        std::memset(&d, 0, sizeof d);
+        const char *e = parse_stream(batch.jpeg + o0, (size_t)(o1 - o0), &d, &g, i == 0);
+        if (e) {
+            if (err) *err = "stream " + std::to_string(first + i) + ": " + e;
+            return std::strncmp(e, "unsupported", 11) == 0 ? 3 : 1;
+        }
+        d.base = o0 - blob0;
+        d.clean_off = clean_bytes;
+        clean_bytes += (((size_t)d.scan_len + 15) & ~(size_t)15) + 32;
+    }
+    if (g.w != w || g.h != h) {
+        if (err) *err = "the streams decode to " + std::to_string(g.w) + "x" + std::to_string(g.h) +
+                        " pixels, not the " + std::to_string(w) + "x" + std::to_string(h) + " asked for";
+        return 1;
+    }
+    if (x0 < 0 || y0 < 0 || cw < 1 || ch < 1 || x0 + cw > w || y0 + ch > h || row_stride < (size_t)cw * 3) {
+        if (err) *err = "bad output rectangle";
+        return 1;
+    }
+    std::memcpy(S.h_stage + desc_bytes, batch.jpeg + blob0, blob_bytes);
+
+    // ---- device buffers ----
+    const size_t coef_elems = (size_t)count * g.blocks_per_image * 64;
+    JPEG_CUDA(grow(&S.d_blob, &S.blob_cap, desc_bytes + blob_bytes + 16));
+    JPEG_CUDA(grow(&S.d_clean, &S.clean_cap, clean_bytes + 64));
+    JPEG_CUDA(grow(&S.d_clean_len, &S.len_cap, (size_t)count * 4));
+    JPEG_CUDA(grow(&S.d_coef, &S.coef_cap, coef_elems * 2));
+    JPEG_CUDA(grow(&S.d_planes, &S.planes_cap, (size_t)count * g.plane_bytes));
+    (void)S.d_desc; (void)S.desc_cap;
+
+    JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes + blob_bytes, cudaMemcpyHostToDevice, stream));
+    JPEG_CUDA(cudaEventRecord(S.uploaded, stream));
+    S.upload_pending = true;
+    const JpegDesc *d_desc = reinterpret_cast<const JpegDesc *>(S.d_blob);
+    const uint8_t *d_streams = S.d_blob + desc_bytes;
+    JPEG_CUDA(cudaMemsetAsync(S.d_coef, 0, coef_elems * 2, stream));
+
+    melf_jpeg_destuff_kernel<<<count, DESTUFF_THREADS, 0, stream>>>(d_streams, d_desc, S.d_clean, S.d_clean_len);
+    // lanes per warp: few enough that the batch still reaches every SM sub-partition
+    int G = 32;
+    while (G > 2 && count / G < 600) G >>= 1;
+    const int ctas = (count + G - 1) / G;
+    const size_t hsmem = sizeof(HuffSmem) * G;
+#define MELF_HUFF_LAUNCH(GG)                                                                              \
+    case GG:                                                                                              \
+        JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG>,                                      \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));         \
+        melf_jpeg_huffman_kernel<GG><<<ctas, 32, hsmem, stream>>>(d_streams, S.d_clean, d_desc,           \
+                                                                  S.d_clean_len, count, g, S.d_coef);     \
+        break;
+    switch (G) {
+        MELF_HUFF_LAUNCH(32)
+        MELF_HUFF_LAUNCH(16)
+        MELF_HUFF_LAUNCH(8)
+        MELF_HUFF_LAUNCH(4)
+        MELF_HUFF_LAUNCH(2)
+    }
+#undef MELF_HUFF_LAUNCH
+    dim3 igrid((g.blocks_per_image + IDCT_THREADS - 1) / IDCT_THREADS, count);
+    melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, S.d_planes);
+    ColorArgs ca{S.d_planes, d_out, row_stride, frame_stride, x0, y0, cw, ch, count};
+    dim3 cgrid(((cw + 3) / 4 + COLOR_THREADS - 1) / COLOR_THREADS, ch, count);
+    melf_jpeg_color_kernel<<<cgrid, COLOR_THREADS, 0, stream>>>(ca, g);
+    JPEG_CUDA(cudaGetLastError());
+    if (launches) *launches += 4;
+    return 0;
+}

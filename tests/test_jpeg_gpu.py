@@ -1,0 +1,125 @@
+"""Ingest row on the GPU: melf_decode_jpeg against the CPU oracle and against
+what cv2.imread returned in the build container; melf_read_jpeg_batch against the reference's
+golden readings.  Everything goes through the C-ABI."""
+import collections
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from helpers import GOLDEN, assert_results_equal, format_result_line, golden_set
+from test_jpeg_oracle import load_streams
+
+pytestmark = pytest.mark.gpu
+
+
+def decode_on_gpu(eng, streams, h, w):
+    import torch
+    from meterelf_b200 import _engine
+    (blob, offsets) = _engine.pack_streams(streams)
+    out = torch.zeros((len(streams), h, w, 3), dtype=torch.uint8, device='cuda:0')
+    eng.decode_jpeg_device(blob, offsets, h, w, out.data_ptr(), w * 3, h * w * 3,
+                           torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def batches(streams):
+    """Streams grouped into batches of one geometry (size + subsampling), as the entry point wants."""
+    from meterelf_b200 import _engine
+    groups = collections.OrderedDict()
+    for s in streams:
+        info = _engine.jpeg_info(s[1])
+        groups.setdefault(tuple(sorted(info.items())), []).append(s)
+    return list(groups.values())
+
+
+def test_committed_streams_decode_like_cv2_and_the_oracle():
+    eng = golden_set(1).engine()
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    n = 0
+    for group in batches(streams):
+        (h, w) = group[0][2]
+        got = decode_on_gpu(eng, [s[1] for s in group], h, w)
+        for (img, (name, data, shape, sha, _)) in zip(got, group):
+            want = oracle.decode_jpeg(data)
+            assert np.array_equal(img, want), (name, np.argwhere(img != want)[:4])
+            assert hashlib.sha256(img.tobytes()).hexdigest() == sha, name
+            n += 1
+    assert n == len(streams) >= 50
+
+
+def test_every_sample_file_decodes_like_cv2():
+    path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    if not os.path.exists(path):
+        pytest.skip('full JPEG set not present')
+    eng = golden_set(1).engine()
+    streams = load_streams(path)
+    assert len(streams) == 304
+    for group in batches(streams):
+        (h, w) = group[0][2]
+        got = decode_on_gpu(eng, [s[1] for s in group], h, w)
+        for (img, (name, _, _, sha, _)) in zip(got, group):
+            assert hashlib.sha256(img.tobytes()).hexdigest() == sha, name
+
+
+def test_decode_into_strided_frames_and_repeated_calls():
+    import torch
+    from meterelf_b200 import _engine
+    eng = golden_set(1).engine()
+    streams = [s for s in load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz')) if s[2] == (17, 33)]
+    group = batches(streams)[0]
+    (h, w) = (17, 33)
+    (blob, offsets) = _engine.pack_streams([s[1] for s in group])
+    (rs, fs) = (w * 3 + 13, (w * 3 + 13) * h + 7)
+    for _ in range(2):
+        buf = torch.full((len(group) * fs,), 0xA5, dtype=torch.uint8, device='cuda:0')
+        eng.decode_jpeg_device(blob, offsets, h, w, buf.data_ptr(), rs, fs)
+        torch.cuda.synchronize()
+        host = buf.cpu().numpy()
+        for (i, s) in enumerate(group):
+            frame = host[i * fs:i * fs + rs * h].reshape(h, rs)
+            assert np.array_equal(frame[:, :w * 3].reshape(h, w, 3), oracle.decode_jpeg(s[1])), s[0]
+            assert (frame[:, w * 3:] == 0xA5).all()          # nothing written outside the rows
+
+
+def test_unsupported_and_damaged_streams_fail_loudly():
+    from meterelf_b200 import _engine
+    eng = golden_set(1).engine()
+    (name, data, shape, _, _) = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))[0]
+    prog = bytearray(data)
+    prog[prog.find(b'\xff\xc0') + 1] = 0xC2
+    for bad in (bytes(prog), b'junk', data[:300]):
+        with pytest.raises(_engine.EngineError):
+            eng.read_jpeg_streams([data, bad])
+    with pytest.raises(_engine.EngineError):                 # size mismatch inside one batch
+        decode_on_gpu(eng, [data], shape[0] + 1, shape[1])
+
+
+@pytest.mark.parametrize('set_no', [1, 2])
+def test_readings_from_jpeg_bytes_match_the_golden_lines(set_no):
+    path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    streams = load_streams(path if os.path.exists(path) else os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    streams = [s for s in streams if s[4] == set_no]
+    gs = golden_set(set_no)
+    eng = gs.engine(cropped_input=False)
+    n_lines = 0
+    for group in batches(streams):
+        got = eng.read_jpeg_streams([s[1] for s in group])
+        # the same frames decoded by the oracle, cropped as _image.py:46-55 does, read by the oracle
+        (x0, y0, x1, y1) = gs.meter_rect
+        crops = np.stack([oracle.decode_jpeg(s[1])[y0:y1, x0:x1] for s in group[:12]])
+        want = oracle.read_batch(gs.oracle_params(), np.ascontiguousarray(crops), n_threads=4)
+        for (g, w, s) in zip(got, want, group):
+            assert_results_equal(g, w, len(gs.names), s[0])
+        for (g, s) in zip(got, group):
+            exp = gs.expected[s[0]]
+            line = format_result_line(g, gs.names)
+            if exp['status'] == 0:
+                assert line == exp['line'], s[0]
+                n_lines += 1
+            else:
+                assert line.split(' (match val')[0] == exp['line'].split(' (match val')[0], s[0]
+    assert n_lines >= 2
