@@ -120,7 +120,12 @@ int melf_dial_window(const melf_ctx *ctx, int dial, int32_t *win_x0, int32_t *wi
 #define MELF_PROF_MATCH_TC   1      /* melf_match_tc_kernel: tcgen05 correlation + arg-max    */
 #define MELF_PROF_DIALS      2      /* melf_dials_kernel                                      */
 #define MELF_PROF_MATCH_DP4A 3      /* melf_match_kernel: dp4a correlation (large templates)  */
-#define MELF_PROF_KINDS      4
+#define MELF_PROF_JPEG_UPLOAD  4    /* melf_decode_jpeg: H2D copy of the streams + coefficient clear */
+#define MELF_PROF_JPEG_DESTUFF 5    /* melf_jpeg_destuff_kernel                               */
+#define MELF_PROF_JPEG_HUFFMAN 6    /* melf_jpeg_huffman_kernel                               */
+#define MELF_PROF_JPEG_IDCT    7    /* melf_jpeg_idct_kernel                                  */
+#define MELF_PROF_JPEG_COLOR   8    /* melf_jpeg_color_kernel                                 */
+#define MELF_PROF_KINDS      9
 int melf_profile_enable(melf_ctx *ctx, int on);
 int melf_profile_read(melf_ctx *ctx, float *ms /*[MELF_PROF_KINDS]*/, int32_t *launches /*[MELF_PROF_KINDS]*/);
 

@@ -78,7 +78,8 @@ _SYMBOLS = (
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
     'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch')
 
-PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a')
+PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a', 'jpeg_upload', 'jpeg_destuff',
+                 'jpeg_huffman', 'jpeg_idct', 'jpeg_color')
 
 
 def load_library() -> C.CDLL:

@@ -39,8 +39,10 @@ std::mutex g_err_mutex;
 std::string g_create_error;
 
 constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
-constexpr int kJpegChunkFrames = 4096; // streams per pipelined chunk in melf_read_jpeg_batch: the Huffman
-                                       // stage runs one lane per stream, so a chunk must be wide
+constexpr int kJpegChunkFrames = 4096; // most streams per pipelined chunk in melf_read_jpeg_batch ...
+constexpr int kJpegSlots = 4;          // ... and chunks in flight: the Huffman stage runs one lane per stream
+                                       // at low occupancy, so several chunks' kernels share the GPU
+constexpr int kScratchSlots = 3 + kJpegSlots;   // [0] caller stream, [1], [2] melf_read_batch, then JPEG
 constexpr long long kTcMaxItems = 4096; // work items per prep + correlation launch pair (~400 MB scratch)
 
 }  // namespace
@@ -67,8 +69,8 @@ struct melf_ctx {
     bool profiling = false;
     struct Span { int kind; cudaEvent_t e0, e1; };
     std::vector<Span> spans;
-    uint8_t *d_tc_scratch[3] = {nullptr, nullptr, nullptr};   // [0]: caller-stream path, [1], [2]: pipeline streams
-    long long tc_scratch_items[3] = {0, 0, 0};
+    uint8_t *d_tc_scratch[kScratchSlots] = {};   // [0]: caller-stream path, [1], [2]: pipeline streams, ...
+    long long tc_scratch_items[kScratchSlots] = {};
     long long sum_t = 0, n_t = 0;
     int tw4p = 0, steps = 0;
     std::vector<int32_t> win_x0, win_y0;
@@ -76,8 +78,8 @@ struct melf_ctx {
     // scratch for the async path
     u64 *d_keys = nullptr;
     int keys_cap = 0;
-    MelfDialSlot *d_dial_slots[3] = {nullptr, nullptr, nullptr};   // per scratch slot, like d_tc_scratch
-    int dial_slots_cap[3] = {0, 0, 0};
+    MelfDialSlot *d_dial_slots[kScratchSlots] = {};   // per scratch slot, like d_tc_scratch
+    int dial_slots_cap[kScratchSlots] = {};
 
     // pipeline resources of melf_read_batch
     cudaStream_t streams[2] = {nullptr, nullptr};
@@ -87,13 +89,14 @@ struct melf_ctx {
     melf_result *h_res = nullptr;       // pinned, 2 * kChunkFrames
     u64 *d_chunk_keys[2] = {nullptr, nullptr};
 
-    // JPEG ingest (melf_jpeg.cu): [0] caller-stream path, [1], [2] pipeline streams of melf_read_jpeg_batch
-    MelfJpegState *jpeg[3] = {nullptr, nullptr, nullptr};
-    uint8_t *d_jchunk[2] = {nullptr, nullptr};
+    // JPEG ingest (melf_jpeg.cu): [0] caller-stream path, [1 ..] pipeline slots of melf_read_jpeg_batch
+    MelfJpegState *jpeg[1 + kJpegSlots] = {};
+    cudaStream_t jstreams[kJpegSlots] = {};
+    uint8_t *d_jchunk[kJpegSlots] = {};
     size_t jchunk_bytes = 0;
-    melf_result *d_jres[2] = {nullptr, nullptr};
-    melf_result *h_jres = nullptr;      // pinned, 2 * kJpegChunkFrames
-    u64 *d_jkeys[2] = {nullptr, nullptr};
+    melf_result *d_jres[kJpegSlots] = {};
+    melf_result *h_jres = nullptr;      // pinned, kJpegSlots * kJpegChunkFrames
+    u64 *d_jkeys[kJpegSlots] = {};
 };
 
 namespace {
@@ -338,6 +341,25 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
     return MELF_OK;
 }
 
+
+// event pairs for the five stages of one JPEG decode while profiling (NULL otherwise)
+struct JpegSpans {
+    cudaEvent_t ev[5][2];
+    bool on = false;
+    explicit JpegSpans(melf_ctx *ctx)
+    {
+        if (!ctx->profiling) return;
+        on = true;
+        for (auto &p : ev) { cudaEventCreate(&p[0]); cudaEventCreate(&p[1]); }
+    }
+    cudaEvent_t (*get())[2] { return on ? ev : nullptr; }
+    void commit(melf_ctx *ctx)
+    {
+        if (!on) return;
+        for (int k = 0; k < 5; k++) ctx->spans.push_back(melf_ctx::Span{MELF_PROF_JPEG_UPLOAD + k, ev[k][0], ev[k][1]});
+    }
+};
+
 void free_ctx(melf_ctx *ctx)
 {
     if (!ctx) return;
@@ -346,15 +368,18 @@ void free_ctx(melf_ctx *ctx)
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_keys);
-    for (int i = 0; i < 3; i++) cudaFree(ctx->d_dial_slots[i]);
-    for (int i = 0; i < 3; i++) cudaFree(ctx->d_tc_scratch[i]);
+    for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_dial_slots[i]);
+    for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_tc_scratch[i]);
     for (int i = 0; i < 2; i++) {
         if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
         cudaFree(ctx->d_chunk[i]); cudaFree(ctx->d_res[i]); cudaFree(ctx->d_chunk_keys[i]);
     }
     if (ctx->h_res) cudaFreeHost(ctx->h_res);
-    for (int i = 0; i < 3; i++) melf_jpeg_state_free(ctx->jpeg[i]);
-    for (int i = 0; i < 2; i++) { cudaFree(ctx->d_jchunk[i]); cudaFree(ctx->d_jres[i]); cudaFree(ctx->d_jkeys[i]); }
+    for (int i = 0; i < 1 + kJpegSlots; i++) melf_jpeg_state_free(ctx->jpeg[i]);
+    for (int i = 0; i < kJpegSlots; i++) {
+        if (ctx->jstreams[i]) cudaStreamDestroy(ctx->jstreams[i]);
+        cudaFree(ctx->d_jchunk[i]); cudaFree(ctx->d_jres[i]); cudaFree(ctx->d_jkeys[i]);
+    }
     if (ctx->h_jres) cudaFreeHost(ctx->h_jres);
     delete ctx;
 }
@@ -653,8 +678,10 @@ int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets
     MelfJpegBatch batch{jpeg, offsets, n};
     std::string err;
     uint64_t launches = 0;
+    JpegSpans spans(ctx);
     int rc = melf_jpeg_decode_range(&ctx->jpeg[0], batch, 0, n, h, w, 0, 0, w, h, d_bgr, row_stride,
-                                    frame_stride, (cudaStream_t)stream, &err, &launches);
+                                    frame_stride, (cudaStream_t)stream, &err, &launches, spans.get());
+    spans.commit(ctx);
     g_launches += launches;
     return rc ? fail(ctx, rc, err) : MELF_OK;
 }
@@ -674,58 +701,65 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
     rc = make_geom(ctx, h, w, true, &geom);
     if (rc) return rc;
     // only the meter_rect pixels are converted to BGR: compact device layout [frame][crop_h][pitch]
-    const size_t pitch = ((size_t)geom.crop_w * 3 + 15) & ~(size_t)15;
+    // (the rectangle starts at a column that is a multiple of 4, so that the colour kernel's
+    // 12-byte pixel groups are aligned stores; the path is told where the real crop begins)
+    const int jx0 = geom.crop_x0 & ~3, jw = geom.crop_w + (geom.crop_x0 - jx0);
+    const size_t pitch = ((size_t)jw * 3 + 15) & ~(size_t)15;
     const size_t frame_bytes = pitch * geom.crop_h;
-    const int chunk_frames = n < kJpegChunkFrames ? n : kJpegChunkFrames;
+    // chunk size: a quarter of the batch (so that all slots are busy), between 512 and kJpegChunkFrames
+    int chunk_frames = (n + kJpegSlots - 1) / kJpegSlots;
+    chunk_frames = (chunk_frames + 511) & ~511;
+    if (chunk_frames > kJpegChunkFrames) chunk_frames = kJpegChunkFrames;
     const size_t need = frame_bytes * chunk_frames;
-    if (!ctx->streams[0])
-        for (int i = 0; i < 2; i++) MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking));
     if (!ctx->h_jres) {
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < kJpegSlots; i++) {
+            MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->jstreams[i], cudaStreamNonBlocking));
             MELF_CUDA(ctx, cudaMalloc(&ctx->d_jres[i], sizeof(melf_result) * kJpegChunkFrames));
             MELF_CUDA(ctx, cudaMalloc(&ctx->d_jkeys[i], sizeof(u64) * kJpegChunkFrames));
         }
-        MELF_CUDA(ctx, cudaMallocHost(&ctx->h_jres, sizeof(melf_result) * kJpegChunkFrames * 2));
+        MELF_CUDA(ctx, cudaMallocHost(&ctx->h_jres, sizeof(melf_result) * kJpegChunkFrames * kJpegSlots));
     }
     if (need > ctx->jchunk_bytes) {
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < kJpegSlots; i++) {
             if (ctx->d_jchunk[i]) cudaFree(ctx->d_jchunk[i]);
             ctx->d_jchunk[i] = nullptr;
         }
         ctx->jchunk_bytes = 0;
-        for (int i = 0; i < 2; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_jchunk[i], need));
+        for (int i = 0; i < kJpegSlots; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_jchunk[i], need));
         ctx->jchunk_bytes = need;
     }
     MelfGeom cg = geom;
-    cg.crop_x0 = 0; cg.crop_y0 = 0;
+    cg.crop_x0 = geom.crop_x0 - jx0; cg.crop_y0 = 0;
     MelfJpegBatch batch{jpeg, offsets, n};
-    int pending[2] = {0, 0}, pending_f0[2] = {0, 0};
+    int pending[kJpegSlots] = {}, pending_f0[kJpegSlots] = {};
     int chunk = 0;
-    for (int f0 = 0; f0 < n; f0 += kJpegChunkFrames, chunk++) {
-        const int b = chunk & 1;
-        const int nf = n - f0 < kJpegChunkFrames ? n - f0 : kJpegChunkFrames;
-        cudaStream_t st = ctx->streams[b];
+    for (int f0 = 0; f0 < n; f0 += chunk_frames, chunk++) {
+        const int b = chunk % kJpegSlots;
+        const int nf = n - f0 < chunk_frames ? n - f0 : chunk_frames;
+        cudaStream_t st = ctx->jstreams[b];
         if (pending[b]) {
             MELF_CUDA(ctx, cudaStreamSynchronize(st));
             std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
             pending[b] = 0;
         }
         uint64_t launches = 0;
-        rc = melf_jpeg_decode_range(&ctx->jpeg[1 + b], batch, f0, nf, h, w, geom.crop_x0, geom.crop_y0,
-                                    geom.crop_w, geom.crop_h, ctx->d_jchunk[b], pitch, frame_bytes, st, &err,
-                                    &launches);
+        JpegSpans spans(ctx);
+        rc = melf_jpeg_decode_range(&ctx->jpeg[1 + b], batch, f0, nf, h, w, jx0, geom.crop_y0,
+                                    jw, geom.crop_h, ctx->d_jchunk[b], pitch, frame_bytes, st, &err,
+                                    &launches, spans.get());
+        spans.commit(ctx);
         g_launches += launches;
         if (rc) return fail(ctx, rc, err);
-        rc = run_path(ctx, ctx->d_jchunk[b], nf, geom.crop_h, geom.crop_w, pitch, frame_bytes, cg,
-                      ctx->d_jkeys[b], ctx->d_jres[b], nullptr, st, 1 + b);
+        rc = run_path(ctx, ctx->d_jchunk[b], nf, geom.crop_h, jw, pitch, frame_bytes, cg,
+                      ctx->d_jkeys[b], ctx->d_jres[b], nullptr, st, 3 + b);
         if (rc) return rc;
         MELF_CUDA(ctx, cudaMemcpyAsync(ctx->h_jres + (size_t)b * kJpegChunkFrames, ctx->d_jres[b],
                                        sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
         pending[b] = nf; pending_f0[b] = f0;
     }
-    for (int b = 0; b < 2; b++)
+    for (int b = 0; b < kJpegSlots; b++)
         if (pending[b]) {
-            MELF_CUDA(ctx, cudaStreamSynchronize(ctx->streams[b]));
+            MELF_CUDA(ctx, cudaStreamSynchronize(ctx->jstreams[b]));
             std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
         }
     return MELF_OK;

@@ -22,6 +22,7 @@
 // All four are byte/integer kernels bounded by latency (Huffman) or HBM (the rest); no tensor work.
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -287,15 +288,19 @@ melf_jpeg_destuff_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__res
 // ---------------------------------------------------------------------------------------------
 struct HuffSmem {                         // per stream
     uint16_t lut[4][kLutEntries];         // (code length << 8) | symbol for codes of <= kLook bits, else 0
-    int32_t maxcode[4][8];                // lengths kLook+1 .. 16: largest code of that length (-1: none) ...
-    int32_t valoff[4][8];                 // ... and symbol index - code of its first code
+    uint32_t limit[4][8];                 // lengths kLook+1 .. 16: first 16-bit window value past the codes of
+                                          // that length (canonical codes are contiguous, so monotone)
+    int32_t valoff[4][8];                 // ... and symbol index - code of the first code of that length
+    uint32_t symbols[4];                  // offset of the table's symbol bytes in the stream
 };
 
 // Builds the tables of one stream with the whole warp.
 __device__ void build_tables(HuffSmem &S, const uint8_t *__restrict__ stream, const JpegDesc &d, int lane)
 {
+#pragma unroll 1
     for (int t = 0; t < 4; t++) {
-        const uint8_t *counts = stream + d.huff_off[t];
+        const uint32_t hoff = t == 0 ? d.huff_off[0] : t == 1 ? d.huff_off[1] : t == 2 ? d.huff_off[2] : d.huff_off[3];
+        const uint8_t *counts = stream + hoff;
         const uint8_t *symbols = counts + 16;
         // canonical code assignment (T.81 Annex C), the same on every lane
         int first[17], valptr[17], cnt[17];
@@ -318,21 +323,29 @@ __device__ void build_tables(HuffSmem &S, const uint8_t *__restrict__ stream, co
             }
             S.lut[t][i] = e;
         }
-        if (lane < 16 - kLook) {
-            int mc = -1, vo = 0;
+        if (lane < 8) {
+            uint32_t lim = 0xFFFFFFFFu;
+            int vo = 0;
 #pragma unroll
             for (int l = kLook + 1; l <= 16; l++)
                 if (l - kLook - 1 == lane) {
-                    mc = cnt[l] ? first[l] + cnt[l] - 1 : -1;
+                    lim = (uint32_t)(first[l] + cnt[l]) << (16 - l);
                     vo = valptr[l] - first[l];
                 }
-            S.maxcode[t][lane] = mc;
+            S.limit[t][lane] = lim;
             S.valoff[t][lane] = vo;
         }
+        if (lane == 0) S.symbols[t] = hoff + 16;
     }
 }
 
-template <int G>
+// The loop body is written with selects instead of branches: the lanes of a warp decode different
+// streams and would otherwise serialise on every DC/AC/end-of-block/refill decision.  Coefficients
+// go out in DECODE order (block b of the scan at out + 64*b, zig-zag order inside the block), so
+// that the end of a block costs one pointer increment; the IDCT kernel undoes both orders.
+// SHARED: every stream of the launch carries the same four Huffman tables (the host compared the
+// DHT bytes), so one set of tables per CTA serves all lanes.
+template <int G, bool SHARED>
 __global__ void __launch_bounds__(32)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
                          const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ clean_len,
@@ -342,91 +355,80 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     HuffSmem *S = reinterpret_cast<HuffSmem *>(huff_smem);
     const int lane = threadIdx.x;
     const int img0 = blockIdx.x * G;
-    for (int gi = 0; gi < G && img0 + gi < n; gi++) {
+    for (int gi = 0; gi < (SHARED ? 1 : G) && img0 + gi < n; gi++) {
         const JpegDesc d = desc[img0 + gi];
         build_tables(S[gi], blob + d.base, d, lane);
     }
     __syncwarp();
     const int img = img0 + lane;
     if (lane >= G || img >= n) return;
-    const HuffSmem &T = S[lane];
-    const JpegDesc d = desc[img];
-    const uint8_t *stream = blob + d.base;
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + d.clean_off);
+    const HuffSmem &T = S[SHARED ? 0 : lane];
+    const uint64_t base = desc[img].base;
+    const int restart = (int)desc[img].restart;
+    const uint8_t *stream = blob + base;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[img].clean_off);
     const int wmax = (int)((clean_len[img] + 3) >> 2);
-    int16_t *out = coef + (size_t)img * g.blocks_per_image * 64;
+    int16_t *blk = coef + (size_t)img * g.blocks_per_image * 64;
 
     unsigned long long acc = 0;
     int nbits = 0, wp = 0;
     uint32_t nextw = wmax > 0 ? src[0] : 0;
     int pred0 = 0, pred1 = 0, pred2 = 0;
-    int slot = 0, mx = 0, my = 0, k = 0, comp = 0, in_interval = 0;
-    int16_t *blk = out;
-    const int total_blocks = g.mcus_x * g.mcus_y * g.nslots;
-    int done = 0;
-    while (done < total_blocks) {
-        if (nbits <= 32) {
-            acc |= (unsigned long long)__byte_perm(nextw, 0, 0x0123) << (32 - nbits);
-            nbits += 32;
-            wp++;
-            nextw = wp < wmax ? src[wp] : 0;
+    int slot = 0, k = 0, comp = 0, in_interval = 0;
+    const int nslots = g.nslots;
+    const uint32_t slot_info = g.slot_info;
+    int left = g.mcus_x * g.mcus_y * nslots;
+    while (left > 0) {
+        {   // refill: 32 more bits when at most 32 are left
+            const bool need = nbits <= 32;
+            const unsigned long long add = (unsigned long long)__byte_perm(nextw, 0, 0x0123) << ((32 - nbits) & 63);
+            acc |= need ? add : 0ull;
+            nbits += need ? 32 : 0;
+            wp += need ? 1 : 0;
+            if (need) nextw = wp < wmax ? src[wp] : 0;
         }
         const bool is_dc = k == 0;
         const int t = (comp ? 2 : 0) + (is_dc ? 0 : 1);
-        const uint32_t e = T.lut[t][(uint32_t)(acc >> (64 - kLook))];
+        const uint32_t win16 = (uint32_t)(acc >> 48);
+        const uint32_t e = T.lut[t][win16 >> (16 - kLook)];
         int len = (int)(e >> 8), sym = (int)(e & 255);
         if (e == 0) {                                    // code longer than kLook bits (rare)
-            len = 17;
-            sym = 0;
+            int l = kLook + 1;
 #pragma unroll
-            for (int l = kLook + 1; l <= 16; l++) {
-                const int c = (int)(acc >> (64 - l));
-                if (len == 17 && c <= T.maxcode[t][l - kLook - 1]) {
-                    len = l;
-                    sym = stream[d.huff_off[t] + 16 + ((c + T.valoff[t][l - kLook - 1]) & 255)];
-                }
-            }
-            if (len == 17) { len = 16; sym = 0; }        // invalid code: libjpeg warns and returns 0
+            for (int j = 0; j < 16 - kLook - 1; j++) l += win16 >= T.limit[t][j] ? 1 : 0;
+            const bool valid = win16 < T.limit[t][16 - kLook - 1];
+            const int idx = (int)(win16 >> (16 - l)) + T.valoff[t][l - kLook - 1];
+            sym = valid ? stream[T.symbols[t] + (idx & 255)] : 0;    // invalid code: libjpeg warns, returns 0
+            len = l;
         }
         const int s = sym & 15, r = sym >> 4;
         const uint32_t bits = (uint32_t)(((acc << len) >> 1) >> (63 - s));
         acc <<= (len + s);
         nbits -= len + s;
         const int v = (s && bits < (1u << (s - 1))) ? (int)bits - (1 << s) + 1 : (int)bits;   // EXTEND
-        if (is_dc) {
-            int p = comp == 0 ? pred0 : comp == 1 ? pred1 : pred2;
-            p += v;
-            if (comp == 0) pred0 = p; else if (comp == 1) pred1 = p; else pred2 = p;
-            blk[0] = (int16_t)p;
-            k = 1;
-        } else if (s) {
-            k += r;
-            if (k < 64) blk[k] = (int16_t)v;
-            k++;
-        } else {
-            k = r == 15 ? k + 16 : 64;
-        }
-        if (k >= 64) {                                   // next block of the MCU / next MCU
+        // DC: difference to the predictor of the component; AC: run r, value v; (0,0) end of block; (15,0) 16 zeros
+        pred0 += (is_dc && comp == 0) ? v : 0;
+        pred1 += (is_dc && comp == 1) ? v : 0;
+        pred2 += (is_dc && comp == 2) ? v : 0;
+        const int p = comp == 0 ? pred0 : comp == 1 ? pred1 : pred2;
+        const int pos = is_dc ? 0 : k + r;
+        if (is_dc || (s != 0 && pos < 64)) blk[pos] = (int16_t)(is_dc ? p : v);
+        k = (is_dc || s != 0) ? pos + 1 : (r == 15 ? k + 16 : 64);
+        const bool block_end = k >= 64;
+        if (block_end) {
             k = 0;
-            done++;
-            if (++slot == g.nslots) {
-                slot = 0;
-                if (++mx == g.mcus_x) { mx = 0; my++; }
-                if (d.restart && ++in_interval == (int)d.restart) {   // jdhuff.c process_restart
-                    in_interval = 0;
-                    const int drop = nbits & 7;                       // to the byte boundary
-                    acc <<= drop;
-                    nbits -= drop;
-                    pred0 = pred1 = pred2 = 0;
-                }
+            blk += 64;
+            left--;
+            const bool mcu_end = slot + 1 == nslots;
+            slot = mcu_end ? 0 : slot + 1;
+            comp = (int)(slot_info >> (4 * slot) & 3);
+            if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
+                in_interval = 0;
+                const int drop = nbits & 7;                           // to the byte boundary
+                acc <<= drop;
+                nbits -= drop;
+                pred0 = pred1 = pred2 = 0;
             }
-            const uint32_t info = g.slot_info >> (4 * slot);
-            comp = info & 3;
-            const int bx = info >> 2 & 1, by = info >> 3 & 1;
-            const int ch = comp ? 1 : g.hs, cv = comp ? 1 : g.vs;
-            const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
-            const int boff = comp == 0 ? g.block_off[0] : comp == 1 ? g.block_off[1] : g.block_off[2];
-            blk = out + ((size_t)boff + (size_t)(my * cv + by) * bw + (mx * ch + bx)) * 64;
         }
     }
 }
@@ -462,9 +464,12 @@ __device__ __forceinline__ void idct8(int i0, int i1, int i2, int i3, int i4, in
 
 constexpr int IDCT_THREADS = 128;
 
+struct BlockRect { int bx0[2], bx1[2], by0[2], by1[2]; };   // [0] luma, [1] chroma: blocks to transform
+
 __global__ void __launch_bounds__(IDCT_THREADS)
 melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restrict__ desc,
-                      const int16_t *__restrict__ coef, const JpegGeom g, uint8_t *__restrict__ planes)
+                      const int16_t *__restrict__ coef, const JpegGeom g, const BlockRect rect,
+                      uint8_t *__restrict__ planes)
 {
     constexpr uint8_t ZZ[64] = {
         0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43,
@@ -477,12 +482,20 @@ melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restri
     const int local = b - (comp == 0 ? 0 : comp == 1 ? g.block_off[1] : g.block_off[2]);
     const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
     const int by = local / bw, bx = local - by * bw;
+    {   // only the blocks the colour stage will read
+        const int rc = comp ? 1 : 0;
+        if (bx < rect.bx0[rc] || bx > rect.bx1[rc] || by < rect.by0[rc] || by > rect.by1[rc]) return;
+    }
     const JpegDesc d = desc[img];
     const uint8_t *q = blob + d.base + (comp == 0 ? d.quant_off[0] : comp == 1 ? d.quant_off[1] : d.quant_off[2]);
     const bool q16 = d.quant16 >> comp & 1;
 
     // 64 coefficients (zig-zag order in memory) -> registers, dequantised
-    const uint4 *src = reinterpret_cast<const uint4 *>(coef + ((size_t)img * g.blocks_per_image + b) * 64);
+    // the Huffman stage stores blocks in scan order: MCU-major, component slots inside an MCU
+    const int ch = comp ? 1 : g.hs, cv = comp ? 1 : g.vs;
+    const int slot0 = comp == 0 ? 0 : g.hs * g.vs + comp - 1;
+    const int scan_idx = ((by / cv) * g.mcus_x + bx / ch) * g.nslots + slot0 + (by % cv) * ch + bx % ch;
+    const uint4 *src = reinterpret_cast<const uint4 *>(coef + ((size_t)img * g.blocks_per_image + scan_idx) * 64);
     int z[64];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
@@ -566,42 +579,85 @@ __device__ __forceinline__ int upsampled(const uint8_t *__restrict__ p, int stri
 
 constexpr int COLOR_THREADS = 128;
 
+__device__ __forceinline__ void ycc_to_bgr(int yy, int cb, int cr, uint8_t *px)
+{
+    cb -= 128;
+    cr -= 128;
+    const int r = yy + ((91881 * cr + 32768) >> 16);                       // FIX(1.40200)
+    const int gg = yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16);         // FIX(0.34414), FIX(0.71414)
+    const int b = yy + ((116130 * cb + 32768) >> 16);                      // FIX(1.77200)
+    px[0] = (uint8_t)min(max(b, 0), 255);
+    px[1] = (uint8_t)min(max(gg, 0), 255);
+    px[2] = (uint8_t)min(max(r, 0), 255);
+}
+
+// h2v2 row pair -> the 4 upsampled samples of pixels 4T .. 4T+3 (chroma columns 2T, 2T+1 and their
+// neighbours 2T-1, 2T+2; the first and last column rules of h2v2_fancy_upsample at the edges)
+__device__ __forceinline__ void h2v2_four(const uint8_t *__restrict__ r0, const uint8_t *__restrict__ r1,
+                                          int c0, int last, int (&o)[4])
+{
+    const uint32_t a = *reinterpret_cast<const uint16_t *>(r0 + c0);       // c0 is even: aligned pair
+    const uint32_t b = *reinterpret_cast<const uint16_t *>(r1 + c0);
+    const int s0 = 3 * (int)(a & 255) + (int)(b & 255), s1 = 3 * (int)(a >> 8) + (int)(b >> 8);
+    const int sl = c0 > 0 ? 3 * r0[c0 - 1] + r1[c0 - 1] : 0;
+    const int sr = c0 + 2 <= last ? 3 * r0[c0 + 2] + r1[c0 + 2] : 0;
+    o[0] = c0 == 0 ? (4 * s0 + 8) >> 4 : (3 * s0 + sl + 8) >> 4;
+    o[1] = c0 == last ? (4 * s0 + 7) >> 4 : (3 * s0 + s1 + 7) >> 4;
+    o[2] = (3 * s1 + s0 + 8) >> 4;
+    o[3] = c0 + 1 == last ? (4 * s1 + 7) >> 4 : (3 * s1 + sr + 7) >> 4;
+}
+
 __global__ void __launch_bounds__(COLOR_THREADS)
 melf_jpeg_color_kernel(const ColorArgs a, const JpegGeom g)
 {
-    const int groups = (a.cw + 3) >> 2;
-    const int t = blockIdx.x * COLOR_THREADS + threadIdx.x;
+    // thread = 4 pixels of one row at an image column that is a multiple of 4
+    const int t0 = a.x0 >> 2;
+    const int T = t0 + blockIdx.x * COLOR_THREADS + threadIdx.x;
     const int y = a.y0 + blockIdx.y, img = blockIdx.z;
-    if (t >= groups) return;
+    const int X = 4 * T;
+    if (X >= a.x0 + a.cw) return;
     const uint8_t *pl = a.planes + (size_t)img * g.plane_bytes;
-    const uint8_t *yp = pl + g.plane_off[0] + (size_t)y * (g.blocks_w[0] * 8);
+    const int ystride = g.blocks_w[0] * 8;
+    const uint8_t *yp = pl + g.plane_off[0] + (size_t)y * ystride;
     const int cstride = g.blocks_w[1] * 8;
-    uint8_t *o = a.out + (size_t)img * a.frame_stride + (size_t)blockIdx.y * a.row_stride + (size_t)t * 12;
     uint8_t px[12];
-    const int npx = min(4, a.cw - 4 * t);
+    const uint32_t y4 = *reinterpret_cast<const uint32_t *>(yp + X);       // the plane is padded to whole blocks
+    if (g.ncomp == 3 && g.hs == 2 && g.vs == 2 && g.ds_w > 2 && X + 3 <= 2 * g.ds_w - 1) {
+        const int cy = y >> 1;
+        const int oy = min(max((y & 1) ? cy + 1 : cy - 1, 0), g.ds_h - 1);
+        int cb[4], cr[4];
+        const uint8_t *pb = pl + g.plane_off[1], *pr = pl + g.plane_off[2];
+        h2v2_four(pb + (size_t)cy * cstride, pb + (size_t)oy * cstride, X >> 1, g.ds_w - 1, cb);
+        h2v2_four(pr + (size_t)cy * cstride, pr + (size_t)oy * cstride, X >> 1, g.ds_w - 1, cr);
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int x = a.x0 + 4 * t + (k < npx ? k : 0);
-        const int yy = yp[x];
-        int b = yy, gg = yy, r = yy;
-        if (g.ncomp == 3) {
-            const int cb = upsampled(pl + g.plane_off[1], cstride, g, x, y) - 128;
-            const int cr = upsampled(pl + g.plane_off[2], cstride, g, x, y) - 128;
-            r = yy + ((91881 * cr + 32768) >> 16);                       // FIX(1.40200)
-            gg = yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16);         // FIX(0.34414), FIX(0.71414)
-            b = yy + ((116130 * cb + 32768) >> 16);                      // FIX(1.77200)
+        for (int k = 0; k < 4; k++) ycc_to_bgr((int)(y4 >> (8 * k) & 255), cb[k], cr[k], px + 3 * k);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = min(X + k, g.w - 1);
+            const int yy = yp[x];
+            if (g.ncomp == 3)
+                ycc_to_bgr(yy, upsampled(pl + g.plane_off[1], cstride, g, x, y),
+                           upsampled(pl + g.plane_off[2], cstride, g, x, y), px + 3 * k);
+            else
+                px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = (uint8_t)yy;
         }
-        px[3 * k] = (uint8_t)min(max(b, 0), 255);
-        px[3 * k + 1] = (uint8_t)min(max(gg, 0), 255);
-        px[3 * k + 2] = (uint8_t)min(max(r, 0), 255);
     }
-    if (npx == 4 && ((reinterpret_cast<uintptr_t>(o) & 3) == 0)) {
-        uint32_t *o32 = reinterpret_cast<uint32_t *>(o);
+    uint8_t *o = a.out + (size_t)img * a.frame_stride + (size_t)blockIdx.y * a.row_stride;
+    const int rel = X - a.x0;                       // column of the first pixel inside the rectangle
+    if (rel >= 0 && rel + 4 <= a.cw && ((reinterpret_cast<uintptr_t>(o + 3 * rel) & 3) == 0)) {
+        uint32_t *o32 = reinterpret_cast<uint32_t *>(o + 3 * rel);
 #pragma unroll
         for (int k = 0; k < 3; k++)
             o32[k] = px[4 * k] | px[4 * k + 1] << 8 | px[4 * k + 2] << 16 | (uint32_t)px[4 * k + 3] << 24;
     } else {
-        for (int k = 0; k < 3 * npx; k++) o[k] = px[k];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (rel + k >= 0 && rel + k < a.cw) {
+                o[3 * (rel + k)] = px[3 * k];
+                o[3 * (rel + k) + 1] = px[3 * k + 1];
+                o[3 * (rel + k) + 2] = px[3 * k + 2];
+            }
     }
 }
 
@@ -672,7 +728,7 @@ int melf_jpeg_probe(const uint8_t *jpeg, size_t len, int *h, int *w, int *ncomp,
 int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, int first, int count,
                            int h, int w, int x0, int y0, int cw, int ch, uint8_t *d_out,
                            size_t row_stride, size_t frame_stride, cudaStream_t stream,
-                           std::string *err, uint64_t *launches)
+                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2])
 {
     if (count <= 0) return 0;
     if (!*state) *state = new MelfJpegState();
@@ -687,17 +743,25 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         JPEG_CUDA(cudaEventSynchronize(S.uploaded));
         S.upload_pending = false;
     }
-    if (desc_bytes + blob_bytes + 16 > S.stage_cap) {
+    // a caller blob that is already page-locked is uploaded from where it lies; otherwise it is
+    // gathered into the pinned staging buffer behind the descriptors
+    cudaPointerAttributes pattr{};
+    const bool direct = cudaPointerGetAttributes(&pattr, batch.jpeg) == cudaSuccess &&
+                        pattr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    const size_t stage_need = desc_bytes + (direct ? 0 : blob_bytes) + 16;
+    if (stage_need > S.stage_cap) {
         if (S.h_stage) cudaFreeHost(S.h_stage);
         S.h_stage = nullptr;
         S.stage_cap = 0;
-        const size_t bytes = (desc_bytes + blob_bytes + 16) * 5 / 4;
+        const size_t bytes = stage_need * 5 / 4;
         JPEG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&S.h_stage), bytes));
         S.stage_cap = bytes;
     }
     JpegDesc *descs = reinterpret_cast<JpegDesc *>(S.h_stage);
     JpegGeom g{};
     size_t clean_bytes = 0;
+    bool shared_tables = true;
     for (int i = 0; i < count; i++) {
         const uint64_t o0 = batch.offsets[first + i], o1 = batch.offsets[first + i + 1];
         if (o1 < o0 || o1 - o0 > 0xFFFFFFF0ull) {
@@ -710,6 +774,15 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         if (e) {
             if (err) *err = "stream " + std::to_string(first + i) + ": " + e;
             return std::strncmp(e, "unsupported", 11) == 0 ? 3 : 1;
+        }
+        if (shared_tables && i > 0) {
+            const uint8_t *a = batch.jpeg + batch.offsets[first], *b = batch.jpeg + o0;
+            for (int t = 0; t < 4 && shared_tables; t++) {
+                const uint8_t *ta = a + descs[0].huff_off[t], *tb = b + d.huff_off[t];
+                int total = 0;
+                for (int k = 0; k < 16; k++) total += ta[k];
+                shared_tables = std::memcmp(ta, tb, 16 + (size_t)total) == 0;
+            }
         }
         d.base = o0 - blob0;
         d.clean_off = clean_bytes;
@@ -724,7 +797,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         if (err) *err = "bad output rectangle";
         return 1;
     }
-    std::memcpy(S.h_stage + desc_bytes, batch.jpeg + blob0, blob_bytes);
+    if (!direct) std::memcpy(S.h_stage + desc_bytes, batch.jpeg + blob0, blob_bytes);
 
     // ---- device buffers ----
     const size_t coef_elems = (size_t)count * g.blocks_per_image * 64;
@@ -735,25 +808,40 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     JPEG_CUDA(grow(&S.d_planes, &S.planes_cap, (size_t)count * g.plane_bytes));
     (void)S.d_desc; (void)S.desc_cap;
 
-    JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes + blob_bytes, cudaMemcpyHostToDevice, stream));
+    if (spans) cudaEventRecord(spans[0][0], stream);
+    if (direct) {
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes, cudaMemcpyHostToDevice, stream));
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob + desc_bytes, batch.jpeg + blob0, blob_bytes, cudaMemcpyHostToDevice, stream));
+    } else {
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes + blob_bytes, cudaMemcpyHostToDevice, stream));
+    }
     JPEG_CUDA(cudaEventRecord(S.uploaded, stream));
     S.upload_pending = true;
     const JpegDesc *d_desc = reinterpret_cast<const JpegDesc *>(S.d_blob);
     const uint8_t *d_streams = S.d_blob + desc_bytes;
     JPEG_CUDA(cudaMemsetAsync(S.d_coef, 0, coef_elems * 2, stream));
 
+    if (spans) { cudaEventRecord(spans[0][1], stream); cudaEventRecord(spans[1][0], stream); }
     melf_jpeg_destuff_kernel<<<count, DESTUFF_THREADS, 0, stream>>>(d_streams, d_desc, S.d_clean, S.d_clean_len);
+    if (spans) { cudaEventRecord(spans[1][1], stream); cudaEventRecord(spans[2][0], stream); }
     // lanes per warp: few enough that the batch still reaches every SM sub-partition
-    int G = 32;
-    while (G > 2 && count / G < 600) G >>= 1;
+    int G = 8;                                   // measured: profiles/r02_jpeg_*.json
+    while (G > 2 && count / G < 256) G >>= 1;
+    static const int forced = std::getenv("MELF_JPEG_LANES") ? std::atoi(std::getenv("MELF_JPEG_LANES")) : 0;
+    if (forced == 1 || forced == 2 || forced == 4 || forced == 8 || forced == 16 || forced == 32) G = forced;
     const int ctas = (count + G - 1) / G;
-    const size_t hsmem = sizeof(HuffSmem) * G;
+    const size_t hsmem = sizeof(HuffSmem) * (shared_tables ? 1 : G);
 #define MELF_HUFF_LAUNCH(GG)                                                                              \
     case GG:                                                                                              \
-        JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG>,                                      \
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));         \
-        melf_jpeg_huffman_kernel<GG><<<ctas, 32, hsmem, stream>>>(d_streams, S.d_clean, d_desc,           \
-                                                                  S.d_clean_len, count, g, S.d_coef);     \
+        if (shared_tables) {                                                                              \
+            melf_jpeg_huffman_kernel<GG, true><<<ctas, 32, hsmem, stream>>>(                              \
+                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, S.d_coef);                         \
+        } else {                                                                                          \
+            JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false>,                           \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
+            melf_jpeg_huffman_kernel<GG, false><<<ctas, 32, hsmem, stream>>>(                             \
+                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, S.d_coef);                         \
+        }                                                                                                 \
         break;
     switch (G) {
         MELF_HUFF_LAUNCH(32)
@@ -761,13 +849,26 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         MELF_HUFF_LAUNCH(8)
         MELF_HUFF_LAUNCH(4)
         MELF_HUFF_LAUNCH(2)
+        MELF_HUFF_LAUNCH(1)
     }
 #undef MELF_HUFF_LAUNCH
+    if (spans) { cudaEventRecord(spans[2][1], stream); cudaEventRecord(spans[3][0], stream); }
     dim3 igrid((g.blocks_per_image + IDCT_THREADS - 1) / IDCT_THREADS, count);
-    melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, S.d_planes);
+    BlockRect br;
+    br.bx0[0] = x0 >> 3; br.bx1[0] = (x0 + cw - 1) >> 3;
+    br.by0[0] = y0 >> 3; br.by1[0] = (y0 + ch - 1) >> 3;
+    {   // chroma samples under the rectangle plus the one-sample apron of the triangle filter
+        const int cx0 = x0 / g.hs - 1, cx1 = (x0 + cw - 1) / g.hs + 1, cy0 = y0 / g.vs - 1, cy1 = (y0 + ch - 1) / g.vs + 1;
+        br.bx0[1] = (cx0 < 0 ? 0 : cx0) >> 3; br.bx1[1] = cx1 >> 3;
+        br.by0[1] = (cy0 < 0 ? 0 : cy0) >> 3; br.by1[1] = cy1 >> 3;
+    }
+    melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, br, S.d_planes);
+    if (spans) { cudaEventRecord(spans[3][1], stream); cudaEventRecord(spans[4][0], stream); }
     ColorArgs ca{S.d_planes, d_out, row_stride, frame_stride, x0, y0, cw, ch, count};
-    dim3 cgrid(((cw + 3) / 4 + COLOR_THREADS - 1) / COLOR_THREADS, ch, count);
+    const int cgroups = ((x0 + cw + 3) >> 2) - (x0 >> 2);
+    dim3 cgrid((cgroups + COLOR_THREADS - 1) / COLOR_THREADS, ch, count);
     melf_jpeg_color_kernel<<<cgrid, COLOR_THREADS, 0, stream>>>(ca, g);
+    if (spans) cudaEventRecord(spans[4][1], stream);
     JPEG_CUDA(cudaGetLastError());
     if (launches) *launches += 4;
     return 0;

@@ -25,6 +25,7 @@ int melf_jpeg_probe(const uint8_t *jpeg, size_t len, int *h, int *w, int *ncomp,
 int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, int first, int count,
                            int h, int w, int x0, int y0, int cw, int ch, uint8_t *d_out,
                            size_t row_stride, size_t frame_stride, cudaStream_t stream,
-                           std::string *err, uint64_t *launches);
+                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2] = nullptr);
+// spans (optional): 5 event pairs recorded around upload + clear, destuff, Huffman, IDCT, colour.
 
 void melf_jpeg_state_free(MelfJpegState *state);
