@@ -1,8 +1,8 @@
 """``DEBUG`` environment switch (reference: ``_debug.py:1-14``).
 
-Only the text side of debug mode exists here: the CLI appends the meter_values dict and
-per-image errors are re-raised.  The reference's HighGUI windows (``cv2.imshow``) are
-unavailable on this box and are left out (out of scope).
+The CLI appends the meter_values dict and per-image errors are re-raised, as in the reference.
+The reference's HighGUI windows (``cv2.imshow``) cannot exist on this box; with
+``MELF_DEBUG_DIR=<dir>`` the same pictures are written as PNG files instead (``_overlay.py``).
 """
 import os
 

@@ -27,6 +27,8 @@ ST_ANGLE_UNDETERMINED = 3
 
 ERR_NAMES = {1: 'MELF_ERR_INVALID', 2: 'MELF_ERR_CUDA', 3: 'MELF_ERR_UNSUPPORTED',
              4: 'MELF_ERR_TOO_SMALL'}
+ERR_INVALID = 1
+ERR_UNSUPPORTED = 3
 ERR_TOO_SMALL = 4
 
 

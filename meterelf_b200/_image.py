@@ -1,8 +1,12 @@
 """Frame I/O and dial location (reference: ``_image.py:12-81``).
 
-JPEG decoding stays on the host with ``cv2.imread`` exactly as in the reference (so the
-decoded pixels are identical); everything after the decoded BGR frame runs on the GPU.
+Files that are baseline JPEGs the ingest kernels support (the pixels are
+bit-identical to ``cv2.imread``) are handed to the GPU as bytes (``read_stream`` +
+``gpu_ingest_geometry``); everything else -- PNG, progressive or EXIF-rotated JPEGs,
+injected ``bgr_image`` arrays -- is decoded with ``cv2.imread`` exactly as in the
+reference and uploaded as pixels.  ``MELF_INGEST=host`` forces the latter for every file.
 """
+import os
 from typing import Dict, Optional, Tuple
 
 import numpy
@@ -15,6 +19,59 @@ from .exceptions import DialsNotFoundError, ImageLoadingError
 def _imread(filename: str, grayscale: bool = False) -> Optional[Image]:
     import cv2
     return cv2.imread(filename, cv2.IMREAD_GRAYSCALE if grayscale else cv2.IMREAD_COLOR)
+
+
+def gpu_ingest_enabled() -> bool:
+    return os.getenv('MELF_INGEST', 'gpu').lower() != 'host'
+
+
+def read_stream(filename: str) -> Optional[bytes]:
+    """The file's bytes, or None where ``cv2.imread`` would return None for I/O reasons."""
+    try:
+        with open(filename, 'rb') as fp:
+            return fp.read()
+    except OSError:
+        return None
+
+
+def exif_orientation(data: bytes) -> int:
+    """EXIF orientation tag (0x0112) of a JPEG stream, 1 when absent.  ``cv2.imread``
+    rotates by it; the ingest kernels do not, so anything but 1 stays on the host."""
+    pos = 2
+    while pos + 4 <= len(data) and data[pos] == 0xFF:
+        marker = data[pos + 1]
+        if marker in (0xDA, 0xD9):
+            break
+        size = int.from_bytes(data[pos + 2:pos + 4], 'big')
+        seg = data[pos + 4:pos + 2 + size]
+        if marker == 0xE1 and seg[:6] == b'Exif\0\0' and len(seg) >= 14:
+            tiff = seg[6:]
+            order = 'little' if tiff[:2] == b'II' else 'big'
+            ifd = int.from_bytes(tiff[4:8], order)
+            if ifd + 2 > len(tiff):
+                return 1
+            for k in range(int.from_bytes(tiff[ifd:ifd + 2], order)):
+                entry = tiff[ifd + 2 + 12 * k:ifd + 14 + 12 * k]
+                if len(entry) == 12 and int.from_bytes(entry[:2], order) == 0x0112:
+                    return int.from_bytes(entry[8:10], order)
+            return 1
+        pos += 2 + size
+    return 1
+
+
+def gpu_ingest_geometry(data: bytes) -> Optional[Tuple[int, ...]]:
+    """(h, w, components, h_samp, v_samp) when ``melf_read_jpeg_batch`` can take the
+    stream as it is, else None (the file then goes through ``cv2.imread``)."""
+    from . import _engine
+    if data[:2] != b'\xff\xd8':
+        return None
+    try:
+        info = _engine.jpeg_info(data)
+    except _engine.EngineError:
+        return None
+    if exif_orientation(data) != 1:
+        return None
+    return (info['h'], info['w'], info['components'], info['h_samp'], info['v_samp'])
 
 
 class ImageFile:

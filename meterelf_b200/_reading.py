@@ -9,9 +9,11 @@ from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy
 
-from . import _engine
+from . import _engine, _overlay
 from ._dial_data import get_dial_data
-from ._image import ImageFile, get_dials_template, stack_frames
+from ._image import (
+    ImageFile, get_dials_template, gpu_ingest_enabled, gpu_ingest_geometry, read_stream,
+    stack_frames)
 from ._params import Params as _Params
 from .exceptions import (
     DialAngleDeterminingError, DialsNotFoundError, ImageProcessingError,
@@ -69,10 +71,41 @@ def result_to_python(record: Any, names: Sequence[str], filename: str,
 
 def read_image_files(params: _Params, imgfs: Sequence[ImageFile], device: int = 0,
                      ) -> List[Tuple[Dict[str, float], Optional[ImageProcessingError]]]:
-    """Decode on the host, group by frame shape, read each group in one GPU batch."""
+    """Baseline JPEG files go to the GPU as bytes, grouped by geometry
+    (``melf_read_jpeg_batch``); anything else is decoded on the host as in the reference,
+    grouped by frame shape and read in one GPU batch per group."""
     out: List[Any] = [None] * len(imgfs)
+    debug_dir = _overlay.overlay_dir()      # debug pictures need the decoded pixels on the host
     groups: Dict[Tuple[bool, Tuple[int, ...]], List[Tuple[int, numpy.ndarray]]] = {}
+    streams: Dict[Tuple[int, ...], List[Tuple[int, bytes]]] = {}
+    host_decode: List[int] = []
     for (index, imgf) in enumerate(imgfs):
+        data = None
+        if imgf.bgr_image is None and gpu_ingest_enabled() and debug_dir is None:
+            data = read_stream(imgf.filename)
+        geometry = gpu_ingest_geometry(data) if data else None
+        if geometry is not None:
+            streams.setdefault(geometry, []).append((index, data))
+        else:
+            host_decode.append(index)
+    for members in streams.values():
+        engine = get_engine(params, cropped_input=False, device=device)
+        try:
+            records = engine.read_jpeg_streams([data for (_i, data) in members])
+        except _engine.EngineError as error:
+            if error.code == _engine.ERR_TOO_SMALL:
+                raise ValueError(
+                    'image smaller than the dials template: ' + imgfs[members[0][0]].filename)
+            if error.code not in (_engine.ERR_INVALID, _engine.ERR_UNSUPPORTED):
+                raise
+            # a stream the header probe accepted but the decoder rejects (e.g. cut short):
+            # cv2.imread decides what the reference would have seen
+            host_decode.extend(index for (index, _d) in members)
+            continue
+        for ((index, _d), record) in zip(members, records):
+            out[index] = result_to_python(record, engine.names, imgfs[index].filename)
+    for index in sorted(host_decode):
+        imgf = imgfs[index]
         try:
             (frame, needs_crop) = imgf.load_frame()
         except ImageProcessingError as error:
@@ -91,6 +124,12 @@ def read_image_files(params: _Params, imgfs: Sequence[ImageFile], device: int = 
                 'image smaller than the dials template: ' + imgfs[members[0][0]].filename)
         for ((index, _frame), record) in zip(members, records):
             out[index] = result_to_python(record, engine.names, imgfs[index].filename)
+        if debug_dir is not None:
+            ((x0, y0), (x1, y1)) = params.meter_rect if needs_crop else ((0, 0), (None, None))
+            crops = stack_frames([frame[y0:y1, x0:x1] for (_i, frame) in members])
+            _overlay.write_overlays(
+                params, get_engine(params, cropped_input=True, device=device), crops,
+                [imgfs[index].filename for (index, _f) in members], debug_dir)
     return out
 
 

@@ -1,5 +1,6 @@
 // C ABI of the dial-reading path (include/meterelf_b200.h): context, batching, launches.
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -39,8 +40,8 @@ std::mutex g_err_mutex;
 std::string g_create_error;
 
 constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
-constexpr int kJpegChunkFrames = 4096; // most streams per pipelined chunk in melf_read_jpeg_batch ...
-constexpr int kJpegSlots = 4;          // ... and chunks in flight: the Huffman stage runs one lane per stream
+constexpr int kJpegChunkFrames = 8192; // most streams per pipelined chunk in melf_read_jpeg_batch ...
+constexpr int kJpegSlots = 8;          // ... and (at most) chunks in flight: the Huffman stage runs one lane per stream
                                        // at low occupancy, so several chunks' kernels share the GPU
 constexpr int kScratchSlots = 3 + kJpegSlots;   // [0] caller stream, [1], [2] melf_read_batch, then JPEG
 constexpr long long kTcMaxItems = 4096; // work items per prep + correlation launch pair (~400 MB scratch)
@@ -706,13 +707,25 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
     const int jx0 = geom.crop_x0 & ~3, jw = geom.crop_w + (geom.crop_x0 - jx0);
     const size_t pitch = ((size_t)jw * 3 + 15) & ~(size_t)15;
     const size_t frame_bytes = pitch * geom.crop_h;
-    // chunk size: a quarter of the batch (so that all slots are busy), between 512 and kJpegChunkFrames
-    int chunk_frames = (n + kJpegSlots - 1) / kJpegSlots;
+    // chunks in flight and streams per chunk (MELF_JPEG_SLOTS / MELF_JPEG_CHUNK override the defaults):
+    // the batch is cut so that every slot is busy, in multiples of 512 streams
+    static const int slots = [] {
+        const char *e = std::getenv("MELF_JPEG_SLOTS");
+        const int v = e ? std::atoi(e) : kJpegSlots;         // measured: profiles/r01_v11_jpeg_sweep.txt
+        return v < 1 ? 1 : v > kJpegSlots ? kJpegSlots : v;
+    }();
+    static const int chunk_cap = [] {
+        const char *e = std::getenv("MELF_JPEG_CHUNK");
+        const int v = e ? std::atoi(e) : kJpegChunkFrames;
+        return v < 512 ? 512 : v > kJpegChunkFrames ? kJpegChunkFrames : v;
+    }();
+    static const bool trace = std::getenv("MELF_JPEG_TRACE") != nullptr;
+    int chunk_frames = (n + slots - 1) / slots;
     chunk_frames = (chunk_frames + 511) & ~511;
-    if (chunk_frames > kJpegChunkFrames) chunk_frames = kJpegChunkFrames;
+    if (chunk_frames > chunk_cap) chunk_frames = chunk_cap;
     const size_t need = frame_bytes * chunk_frames;
     if (!ctx->h_jres) {
-        for (int i = 0; i < kJpegSlots; i++) {
+        for (int i = 0; i < slots; i++) {
             MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->jstreams[i], cudaStreamNonBlocking));
             MELF_CUDA(ctx, cudaMalloc(&ctx->d_jres[i], sizeof(melf_result) * kJpegChunkFrames));
             MELF_CUDA(ctx, cudaMalloc(&ctx->d_jkeys[i], sizeof(u64) * kJpegChunkFrames));
@@ -720,12 +733,12 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
         MELF_CUDA(ctx, cudaMallocHost(&ctx->h_jres, sizeof(melf_result) * kJpegChunkFrames * kJpegSlots));
     }
     if (need > ctx->jchunk_bytes) {
-        for (int i = 0; i < kJpegSlots; i++) {
+        for (int i = 0; i < slots; i++) {
             if (ctx->d_jchunk[i]) cudaFree(ctx->d_jchunk[i]);
             ctx->d_jchunk[i] = nullptr;
         }
         ctx->jchunk_bytes = 0;
-        for (int i = 0; i < kJpegSlots; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_jchunk[i], need));
+        for (int i = 0; i < slots; i++) MELF_CUDA(ctx, cudaMalloc(&ctx->d_jchunk[i], need));
         ctx->jchunk_bytes = need;
     }
     MelfGeom cg = geom;
@@ -733,21 +746,30 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
     MelfJpegBatch batch{jpeg, offsets, n};
     int pending[kJpegSlots] = {}, pending_f0[kJpegSlots] = {};
     int chunk = 0;
+    double host_ms = 0, wait_ms = 0;
+    const auto t_call = std::chrono::steady_clock::now();
+    auto ms_since = [](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count();
+    };
     for (int f0 = 0; f0 < n; f0 += chunk_frames, chunk++) {
-        const int b = chunk % kJpegSlots;
+        const int b = chunk % slots;
         const int nf = n - f0 < chunk_frames ? n - f0 : chunk_frames;
         cudaStream_t st = ctx->jstreams[b];
         if (pending[b]) {
+            const auto t0 = std::chrono::steady_clock::now();
             MELF_CUDA(ctx, cudaStreamSynchronize(st));
             std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
             pending[b] = 0;
+            wait_ms += ms_since(t0);
         }
         uint64_t launches = 0;
         JpegSpans spans(ctx);
+        const auto t_host = std::chrono::steady_clock::now();
         rc = melf_jpeg_decode_range(&ctx->jpeg[1 + b], batch, f0, nf, h, w, jx0, geom.crop_y0,
                                     jw, geom.crop_h, ctx->d_jchunk[b], pitch, frame_bytes, st, &err,
                                     &launches, spans.get());
         spans.commit(ctx);
+        host_ms += ms_since(t_host);
         g_launches += launches;
         if (rc) return fail(ctx, rc, err);
         rc = run_path(ctx, ctx->d_jchunk[b], nf, geom.crop_h, jw, pitch, frame_bytes, cg,
@@ -757,11 +779,16 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
                                        sizeof(melf_result) * nf, cudaMemcpyDeviceToHost, st));
         pending[b] = nf; pending_f0[b] = f0;
     }
-    for (int b = 0; b < kJpegSlots; b++)
+    const double issued_ms = ms_since(t_call);
+    for (int b = 0; b < slots; b++)
         if (pending[b]) {
             MELF_CUDA(ctx, cudaStreamSynchronize(ctx->jstreams[b]));
             std::memcpy(out + pending_f0[b], ctx->h_jres + (size_t)b * kJpegChunkFrames, sizeof(melf_result) * pending[b]);
         }
+    if (trace)
+        std::fprintf(stderr, "melf_read_jpeg_batch: n %d, %d chunks of %d in %d slots; header walk + launches %.2f ms, "
+                     "slot waits %.2f ms, all issued at %.2f ms, done at %.2f ms\n",
+                     n, chunk, chunk_frames, slots, host_ms, wait_ms, issued_ms, ms_since(t_call));
     return MELF_OK;
 }
 

@@ -56,6 +56,15 @@ struct JpegGeom {                        // shared by every stream of a batch
     int ds_w, ds_h;                      // downsampled_width / height of the chroma components
 };
 
+// The MCUs whose blocks the later stages read (the output rectangle plus the chroma apron).  The
+// Huffman stage keeps only their coefficients, densely, in decode order, stops after the last of them,
+// and sends every other block to one trash block at the end of the stream's run.
+struct McuRect {
+    int mx0, mx1, my0, my1;              // inclusive MCU range
+    int mw;                              // mx1 - mx0 + 1
+    int stride_blocks;                   // kept blocks per stream + 1 (the trash block)
+};
+
 // ---------------------------------------------------------------------------------------------
 // host: marker walk (ITU-T T.81 Annex B).  Fills `d` and checks the geometry against `g`
 // (the first stream defines it).  Returns 0, or an error text.
@@ -349,7 +358,7 @@ template <int G, bool SHARED>
 __global__ void __launch_bounds__(32)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
                          const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ clean_len,
-                         int n, const JpegGeom g, int16_t *__restrict__ coef)
+                         int n, const JpegGeom g, const McuRect R, int16_t *__restrict__ coef)
 {
     extern __shared__ __align__(16) unsigned char huff_smem[];
     HuffSmem *S = reinterpret_cast<HuffSmem *>(huff_smem);
@@ -368,16 +377,24 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     const uint8_t *stream = blob + base;
     const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[img].clean_off);
     const int wmax = (int)((clean_len[img] + 3) >> 2);
-    int16_t *blk = coef + (size_t)img * g.blocks_per_image * 64;
+    int16_t *kept = coef + (size_t)img * R.stride_blocks * 64;
+    int16_t *const trash = kept + (size_t)(R.stride_blocks - 1) * 64;
+    const int mcus_x = g.mcus_x;
+    int mcu_x = 0, mcu_y = 0;
+    bool keep = R.my0 == 0 && R.mx0 == 0;
+    int16_t *blk = keep ? kept : trash;
 
     unsigned long long acc = 0;
     int nbits = 0, wp = 0;
     uint32_t nextw = wmax > 0 ? src[0] : 0;
-    int pred0 = 0, pred1 = 0, pred2 = 0;
+    // DC predictors: (pred, pred1, pred2) belong to components (comp, comp + 1, comp + 2) mod 3 and rotate
+    // when the component changes at the end of a block, so the symbol loop touches only `pred`
+
+    int pred = 0, pred1 = 0, pred2 = 0;
     int slot = 0, k = 0, comp = 0, in_interval = 0;
     const int nslots = g.nslots;
     const uint32_t slot_info = g.slot_info;
-    int left = g.mcus_x * g.mcus_y * nslots;
+    int left = (R.my1 * mcus_x + R.mx1 + 1) * nslots;          // nothing after the last kept MCU is needed
     while (left > 0) {
         {   // refill: 32 more bits when at most 32 are left
             const bool need = nbits <= 32;
@@ -407,27 +424,40 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
         nbits -= len + s;
         const int v = (s && bits < (1u << (s - 1))) ? (int)bits - (1 << s) + 1 : (int)bits;   // EXTEND
         // DC: difference to the predictor of the component; AC: run r, value v; (0,0) end of block; (15,0) 16 zeros
-        pred0 += (is_dc && comp == 0) ? v : 0;
-        pred1 += (is_dc && comp == 1) ? v : 0;
-        pred2 += (is_dc && comp == 2) ? v : 0;
-        const int p = comp == 0 ? pred0 : comp == 1 ? pred1 : pred2;
+        pred += is_dc ? v : 0;
         const int pos = is_dc ? 0 : k + r;
-        if (is_dc || (s != 0 && pos < 64)) blk[pos] = (int16_t)(is_dc ? p : v);
+        if (is_dc || (s != 0 && pos < 64)) blk[pos] = (int16_t)(is_dc ? pred : v);
         k = (is_dc || s != 0) ? pos + 1 : (r == 15 ? k + 16 : 64);
         const bool block_end = k >= 64;
         if (block_end) {
             k = 0;
-            blk += 64;
+            kept += keep ? 64 : 0;
             left--;
             const bool mcu_end = slot + 1 == nslots;
             slot = mcu_end ? 0 : slot + 1;
-            comp = (int)(slot_info >> (4 * slot) & 3);
+            const int ncomp = (int)(slot_info >> (4 * slot) & 3);
+            if (ncomp != comp) {                                      // 0 -> 1 -> 2 -> 0 in scan order
+                // park the predictor of the component that ends, fetch the one that begins:
+                // (pred, pred1, pred2) hold components (comp, comp + 1, comp + 2) mod 3
+                const int t0 = pred;
+                pred = ncomp == (comp + 1) % 3 ? pred1 : pred2;
+                if (ncomp == (comp + 1) % 3) { pred1 = pred2; pred2 = t0; }
+                else { pred2 = pred1; pred1 = t0; }
+                comp = ncomp;
+            }
+            if (mcu_end) {
+                const bool row_end = mcu_x + 1 == mcus_x;
+                mcu_x = row_end ? 0 : mcu_x + 1;
+                mcu_y += row_end ? 1 : 0;
+                keep = mcu_y >= R.my0 && mcu_x >= R.mx0 && mcu_x <= R.mx1;
+            }
+            blk = keep ? kept : trash;
             if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
                 in_interval = 0;
                 const int drop = nbits & 7;                           // to the byte boundary
                 acc <<= drop;
                 nbits -= drop;
-                pred0 = pred1 = pred2 = 0;
+                pred = pred1 = pred2 = 0;
             }
         }
     }
@@ -469,7 +499,7 @@ struct BlockRect { int bx0[2], bx1[2], by0[2], by1[2]; };   // [0] luma, [1] chr
 __global__ void __launch_bounds__(IDCT_THREADS)
 melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restrict__ desc,
                       const int16_t *__restrict__ coef, const JpegGeom g, const BlockRect rect,
-                      uint8_t *__restrict__ planes)
+                      const McuRect R, uint8_t *__restrict__ planes)
 {
     constexpr uint8_t ZZ[64] = {
         0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43,
@@ -494,8 +524,8 @@ melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restri
     // the Huffman stage stores blocks in scan order: MCU-major, component slots inside an MCU
     const int ch = comp ? 1 : g.hs, cv = comp ? 1 : g.vs;
     const int slot0 = comp == 0 ? 0 : g.hs * g.vs + comp - 1;
-    const int scan_idx = ((by / cv) * g.mcus_x + bx / ch) * g.nslots + slot0 + (by % cv) * ch + bx % ch;
-    const uint4 *src = reinterpret_cast<const uint4 *>(coef + ((size_t)img * g.blocks_per_image + scan_idx) * 64);
+    const int scan_idx = ((by / cv - R.my0) * R.mw + (bx / ch - R.mx0)) * g.nslots + slot0 + (by % cv) * ch + bx % ch;
+    const uint4 *src = reinterpret_cast<const uint4 *>(coef + ((size_t)img * R.stride_blocks + scan_idx) * 64);
     int z[64];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
@@ -799,8 +829,34 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     }
     if (!direct) std::memcpy(S.h_stage + desc_bytes, batch.jpeg + blob0, blob_bytes);
 
+    // ---- blocks under the output rectangle, and the MCUs that hold them ----
+    BlockRect br;
+    br.bx0[0] = x0 >> 3; br.bx1[0] = (x0 + cw - 1) >> 3;
+    br.by0[0] = y0 >> 3; br.by1[0] = (y0 + ch - 1) >> 3;
+    {   // chroma samples under the rectangle plus the one-sample apron of the triangle filter
+        const int cx0 = x0 / g.hs - 1, cx1 = (x0 + cw - 1) / g.hs + 1, cy0 = y0 / g.vs - 1, cy1 = (y0 + ch - 1) / g.vs + 1;
+        br.bx0[1] = (cx0 < 0 ? 0 : cx0) >> 3; br.bx1[1] = cx1 >> 3;
+        br.by0[1] = (cy0 < 0 ? 0 : cy0) >> 3; br.by1[1] = cy1 >> 3;
+        if (br.bx1[1] > g.blocks_w[g.ncomp == 3 ? 1 : 0] - 1) br.bx1[1] = g.blocks_w[g.ncomp == 3 ? 1 : 0] - 1;
+        if (br.by1[1] > g.blocks_h[g.ncomp == 3 ? 1 : 0] - 1) br.by1[1] = g.blocks_h[g.ncomp == 3 ? 1 : 0] - 1;
+    }
+    McuRect mr;
+    {
+        const bool chroma = g.ncomp == 3;
+        mr.mx0 = br.bx0[0] / g.hs; mr.mx1 = br.bx1[0] / g.hs;
+        mr.my0 = br.by0[0] / g.vs; mr.my1 = br.by1[0] / g.vs;
+        if (chroma) {
+            if (br.bx0[1] < mr.mx0) mr.mx0 = br.bx0[1];
+            if (br.bx1[1] > mr.mx1) mr.mx1 = br.bx1[1];
+            if (br.by0[1] < mr.my0) mr.my0 = br.by0[1];
+            if (br.by1[1] > mr.my1) mr.my1 = br.by1[1];
+        }
+        mr.mw = mr.mx1 - mr.mx0 + 1;
+        mr.stride_blocks = mr.mw * (mr.my1 - mr.my0 + 1) * g.nslots + 1;
+    }
+
     // ---- device buffers ----
-    const size_t coef_elems = (size_t)count * g.blocks_per_image * 64;
+    const size_t coef_elems = (size_t)count * mr.stride_blocks * 64;
     JPEG_CUDA(grow(&S.d_blob, &S.blob_cap, desc_bytes + blob_bytes + 16));
     JPEG_CUDA(grow(&S.d_clean, &S.clean_cap, clean_bytes + 64));
     JPEG_CUDA(grow(&S.d_clean_len, &S.len_cap, (size_t)count * 4));
@@ -825,7 +881,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     melf_jpeg_destuff_kernel<<<count, DESTUFF_THREADS, 0, stream>>>(d_streams, d_desc, S.d_clean, S.d_clean_len);
     if (spans) { cudaEventRecord(spans[1][1], stream); cudaEventRecord(spans[2][0], stream); }
     // lanes per warp: few enough that the batch still reaches every SM sub-partition
-    int G = 8;                                   // measured: profiles/r02_jpeg_*.json
+    int G = 16;                                  // measured: profiles/r01_v11_jpeg_sweep.txt
     while (G > 2 && count / G < 256) G >>= 1;
     static const int forced = std::getenv("MELF_JPEG_LANES") ? std::atoi(std::getenv("MELF_JPEG_LANES")) : 0;
     if (forced == 1 || forced == 2 || forced == 4 || forced == 8 || forced == 16 || forced == 32) G = forced;
@@ -835,12 +891,12 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     case GG:                                                                                              \
         if (shared_tables) {                                                                              \
             melf_jpeg_huffman_kernel<GG, true><<<ctas, 32, hsmem, stream>>>(                              \
-                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, S.d_coef);                         \
+                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, mr, S.d_coef);                     \
         } else {                                                                                          \
             JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false>,                           \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
             melf_jpeg_huffman_kernel<GG, false><<<ctas, 32, hsmem, stream>>>(                             \
-                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, S.d_coef);                         \
+                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, mr, S.d_coef);                     \
         }                                                                                                 \
         break;
     switch (G) {
@@ -854,15 +910,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
 #undef MELF_HUFF_LAUNCH
     if (spans) { cudaEventRecord(spans[2][1], stream); cudaEventRecord(spans[3][0], stream); }
     dim3 igrid((g.blocks_per_image + IDCT_THREADS - 1) / IDCT_THREADS, count);
-    BlockRect br;
-    br.bx0[0] = x0 >> 3; br.bx1[0] = (x0 + cw - 1) >> 3;
-    br.by0[0] = y0 >> 3; br.by1[0] = (y0 + ch - 1) >> 3;
-    {   // chroma samples under the rectangle plus the one-sample apron of the triangle filter
-        const int cx0 = x0 / g.hs - 1, cx1 = (x0 + cw - 1) / g.hs + 1, cy0 = y0 / g.vs - 1, cy1 = (y0 + ch - 1) / g.vs + 1;
-        br.bx0[1] = (cx0 < 0 ? 0 : cx0) >> 3; br.bx1[1] = cx1 >> 3;
-        br.by0[1] = (cy0 < 0 ? 0 : cy0) >> 3; br.by1[1] = cy1 >> 3;
-    }
-    melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, br, S.d_planes);
+    melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, br, mr, S.d_planes);
     if (spans) { cudaEventRecord(spans[3][1], stream); cudaEventRecord(spans[4][0], stream); }
     ColorArgs ca{S.d_planes, d_out, row_stride, frame_stride, x0, y0, cw, ch, count};
     const int cgroups = ((x0 + cw + 3) >> 2) - (x0 >> 2);

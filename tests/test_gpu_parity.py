@@ -16,7 +16,7 @@ import pytest
 
 import oracle
 from helpers import (
-    assert_results_equal, format_result_line, golden_set, synthetic_blob_frames,
+    GOLDEN, assert_results_equal, format_result_line, golden_set, synthetic_blob_frames,
     window_words)
 
 pytestmark = pytest.mark.gpu
@@ -312,6 +312,119 @@ def test_python_api_image_file_and_errors(tmp_path):
                                 [str(tmp_path / 'a.png'), str(tmp_path / 'missing.png')]))
     assert '{:07.3f}'.format(out[0].value) == '253.623' and out[0].error is None
     assert out[1].value is None and out[1].error.get_message() == 'Unable to load image'
+
+
+def write_params_yml(gs, tmp_path, image_glob='*.jpg'):
+    """params.yml + dials template for a golden set, as the reference's sample directories hold."""
+    import cv2
+    import yaml
+    cv2.imwrite(str(tmp_path / 'dials.png'), gs.template)
+    nd = len(gs.names)
+    needle_data = [dict(
+        name=gs.names[i], color_range=dict(zip('hls', gs.dials[i]['color_range'])),
+        dist_from_center=int(gs.dist_from_center[i]), circle_thickness=int(gs.circle_thickness[i]),
+        angle_of_zero=gs.dials[i]['angle_of_zero'], center=list(gs.dials[i]['center']),
+        diameter=int(gs.diameters[i]), negative_momentum=gs.dials[i]['negative_momentum'])
+        for i in range(nd)]
+    (x0, y0, x1, y1) = gs.meter_rect
+    doc = dict(image_glob=image_glob, meter_rect=dict(top_left=[x0, y0], bottom_right=[x1, y1]),
+               dials_template='dials.png', dials_template_match_threshold=int(gs.match_threshold),
+               dials_template_size=[gs.tmpl_w, gs.tmpl_h], hue_shift=gs.hue_shift,
+               needle_color=dict(h=125, l=80, s=130), needle_color_range=dict(h=9, l=45, s=35),
+               needle_data=needle_data)
+    (tmp_path / 'params.yml').write_text(yaml.safe_dump(doc))
+    return str(tmp_path / 'params.yml')
+
+
+@pytest.mark.parametrize('set_no', [1, 2])
+def test_cli_on_jpeg_files_prints_the_golden_lines(set_no, tmp_path, capsys, monkeypatch):
+    """``python -m meterelf PARAMS FILES`` (_main.py:8-22) on the sample JPEGs themselves: the files
+    are decoded by the ingest kernels (default) and, in a second pass, by cv2.imread on the host
+    (MELF_INGEST=host); both must print the reference's golden stdout lines."""
+    from test_jpeg_oracle import load_streams
+    from meterelf_b200 import _engine, _main
+    path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    streams = load_streams(path if os.path.exists(path) else os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    streams = [s for s in streams if s[4] == set_no]
+    gs = golden_set(set_no)
+    params_file = write_params_yml(gs, tmp_path)
+    files = []
+    for s in streams:
+        files.append(str(tmp_path / s[0]))
+        with open(files[-1], 'wb') as fp:
+            fp.write(s[1])
+    files.append(str(tmp_path / 'missing.jpg'))
+
+    def run():
+        _main.main(['meterelf', params_file] + files)
+        return capsys.readouterr().out.splitlines()
+
+    def check(lines):
+        assert len(lines) == len(files)
+        n_exact = 0
+        for (line, fn, s) in zip(lines, files, streams):
+            exp = gs.expected[s[0]]
+            assert line.startswith(fn + ': ')
+            text = line[len(fn) + 2:]
+            if exp['status'] == 0:
+                assert text == exp['line'], s[0]
+                n_exact += 1
+            else:       # cv2's float32 DFT rounds the match value differently (DESIGN.md section 2)
+                assert text.split(' (match val')[0] == exp['line'].split(' (match val')[0], s[0]
+        assert lines[-1] == files[-1] + ': UNKNOWN Unable to load image'
+        return n_exact
+
+    before = _engine.launch_count()
+    gpu_lines = run()
+    assert check(gpu_lines) >= 2
+    assert _engine.launch_count() > before
+    monkeypatch.setenv('MELF_INGEST', 'host')
+    try:
+        import cv2  # noqa: F401
+    except ImportError:
+        return
+    assert run() == gpu_lines
+
+
+def test_debug_overlays_are_written_as_png_files(tmp_path, monkeypatch):
+    """DEBUG + MELF_DEBUG_DIR leaves the reference's debug pictures (_reading.py:43-78,
+    112-114) as PNG files; what they show is checked against the taps of the GPU path."""
+    import cv2
+    from meterelf_b200 import _debug, _overlay, _params, _reading, get_meter_values
+    gs = golden_set(1)
+    params_file = write_params_yml(gs, tmp_path, image_glob='*.png')
+    sub = gs.subset()
+    names = [str(s) for s in sub['names']]
+    crop = sub['crops'][names.index('20180814215230-01-e136.jpg')]
+    (x0, y0, x1, y1) = gs.meter_rect
+    frame = np.zeros((640, 480, 3), np.uint8)
+    frame[y0:y1, x0:x1] = crop
+    cv2.imwrite(str(tmp_path / 'a.png'), frame)
+    out_dir = tmp_path / 'debug'
+    monkeypatch.setattr(_debug, 'DEBUG', {'1'})
+    monkeypatch.setenv('MELF_DEBUG_DIR', str(out_dir))
+    (data,) = list(get_meter_values(params_file, [str(tmp_path / 'a.png')]))
+    assert '{:07.3f}'.format(data.value) == '253.623'
+    files = sorted(os.listdir(out_dir))
+    assert files == sorted(['a.png.png'] + ['a.png.dial-%s.png' % n for n in gs.names])
+    final = cv2.imread(str(out_dir / 'a.png.png'))
+    assert final.shape == (2 * gs.tmpl_h, 2 * gs.tmpl_w, 3)
+    small = final[::2, ::2]
+    assert np.array_equal(small, final[1::2, 1::2])
+    # the painted pixel counts are the tap counts of the same frame
+    params = _params.load(params_file)
+    eng = _reading.get_engine(params, cropped_input=True)
+    (records, taps) = _overlay.read_with_taps(eng, crop[None])
+    assert int(records[0]['status']) == 0
+    kept = int((small == np.array(_overlay.BGR_RING_KEPT, np.uint8)).all(axis=2).sum())
+    assert kept == int(taps['counts'][0, :, 1].sum()) > 0
+    assert (small == np.array(_overlay.BGR_NEEDLE, np.uint8)).all(axis=2).sum() > 100
+    (mx, my) = (int(records[0]['match_x']), int(records[0]['match_y']))
+    untouched = (small == crop[my:my + gs.tmpl_h, mx:mx + gs.tmpl_w]).all(axis=2)
+    assert untouched.mean() > 0.8                        # the background is the decoded crop itself
+    last = cv2.imread(str(out_dir / ('a.png.dial-%s.png' % gs.names[-1])))
+    assert last.shape == (4 * gs.tmpl_h, 4 * gs.tmpl_w, 3)
+    assert (last == np.array(_overlay.BGR_MAGENTA, np.uint8)).all(axis=2).sum() >= 20
 
 
 @pytest.mark.parametrize('hue_shift,lo,hi', [

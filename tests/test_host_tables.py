@@ -124,3 +124,66 @@ def kernel_model_angle(x, y):
     if y == 0:
         return 0.25 if x > 0 else 0.75
     return (-(math.atan(x / y) / (2 * math.pi)) + (0.5 if y > 0 else 0.0)) % 1.0
+
+
+def test_jpeg_ingest_header_helpers():
+    """Which files the API hands to the ingest kernels as bytes (meterelf_b200/_image.py)."""
+    import os
+    import struct
+    from helpers import GOLDEN
+    from test_jpeg_oracle import load_streams
+    from meterelf_b200 import _image
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    (name, data, shape, _sha, _set) = streams[0]
+    geometry = _image.gpu_ingest_geometry(data)
+    assert geometry is not None and geometry[:3] == (shape[0], shape[1], 3)
+    assert _image.exif_orientation(data) == 1
+    assert _image.gpu_ingest_geometry(b'\x89PNG\r\n\x1a\n' + b'\0' * 64) is None
+    assert _image.gpu_ingest_geometry(data[:100]) is None            # headers cut short
+
+    def with_exif(orientation, order):
+        fmt = '<' if order == b'II' else '>'
+        tiff = order + struct.pack(fmt + 'HI', 42, 8) + struct.pack(fmt + 'H', 1) + \
+            struct.pack(fmt + 'HHIHH', 0x0112, 3, 1, orientation, 0) + struct.pack(fmt + 'I', 0)
+        seg = b'Exif\0\0' + tiff
+        return data[:2] + b'\xff\xe1' + struct.pack('>H', len(seg) + 2) + seg + data[2:]
+
+    for order in (b'II', b'MM'):
+        assert _image.exif_orientation(with_exif(6, order)) == 6
+        assert _image.gpu_ingest_geometry(with_exif(6, order)) is None     # cv2.imread would rotate
+        assert _image.gpu_ingest_geometry(with_exif(1, order)) == geometry
+
+
+def test_debug_overlay_helpers(monkeypatch):
+    """PNG writer, tap-window unpacking and the on/off switch of meterelf_b200/_overlay.py."""
+    import struct
+    import zlib
+    from meterelf_b200 import _debug, _overlay
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, size=(13, 21, 3), dtype=np.uint8)
+    png = _overlay.encode_png(img)
+    assert png[:8] == b'\x89PNG\r\n\x1a\n'
+    (w, h, depth, ctype) = struct.unpack('>IIBB', png[16:26])
+    assert (w, h, depth, ctype) == (21, 13, 8, 2)
+    idat_len = struct.unpack('>I', png[33:37])[0]
+    raw = np.frombuffer(zlib.decompress(png[41:41 + idat_len]), np.uint8).reshape(13, 1 + 63)
+    assert not raw[:, 0].any() and np.array_equal(raw[:, 1:].reshape(13, 21, 3), img[:, :, ::-1])
+    try:
+        import cv2
+        assert np.array_equal(cv2.imdecode(np.frombuffer(png, np.uint8), cv2.IMREAD_COLOR), img)
+    except ImportError:
+        pass
+    big = _overlay.scale_image(img, 4)
+    assert big.shape == (52, 84, 3) and np.array_equal(big[::4, ::4], img) and np.array_equal(big[3::4, 3::4], img)
+    words = np.zeros(64, np.uint64)
+    words[0] = (1 << 3) | (1 << 63)
+    words[63] = 1
+    mask = _overlay.window_to_mask(words, -2, 5, (70, 80))
+    assert mask[5, 1] and mask[5, 61] and mask.sum() == 2          # (68, -2) falls outside of the image
+    monkeypatch.setenv('MELF_DEBUG_DIR', '/tmp/x')
+    monkeypatch.setattr(_debug, 'DEBUG', set())
+    assert _overlay.overlay_dir() is None
+    monkeypatch.setattr(_debug, 'DEBUG', {'1'})
+    assert _overlay.overlay_dir() == '/tmp/x'
+    monkeypatch.delenv('MELF_DEBUG_DIR')
+    assert _overlay.overlay_dir() is None

@@ -39,6 +39,7 @@ def main():
     ap.add_argument('--streams', type=int, default=4096)
     ap.add_argument('--reps', type=int, default=5)
     ap.add_argument('--json', default='')
+    ap.add_argument('--skip-decode', action='store_true', help='only the e2e leg (large batches)')
     args = ap.parse_args()
     from meterelf_b200 import _engine
     full = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
@@ -54,42 +55,46 @@ def main():
     eng = gs.engine(cropped_input=False)
     peaks = bench.load_peaks()
 
-    out = torch.zeros((n, h, w, 3), dtype=torch.uint8, device='cuda:0')
-    st = torch.cuda.current_stream()
+    rep = {'workload': '%d streams %dx%d 4:2:0, %.1f KB avg' % (n, w, h, int(offsets[-1]) / n / 1024)}
+    if not args.skip_decode:
+        out = torch.zeros((n, h, w, 3), dtype=torch.uint8, device='cuda:0')
+        st = torch.cuda.current_stream()
 
-    def decode():
-        eng.decode_jpeg_device(blob_p, offsets, h, w, out.data_ptr(), w * 3, h * w * 3, st.cuda_stream)
-    for _ in range(2):
-        decode()
-    torch.cuda.synchronize()
-    for i in (0, 1, len(base) - 1):
-        assert np.array_equal(out[i].cpu().numpy(), oracle.decode_jpeg(data[i])), i
-    eng.profile_enable(True)
-    t0 = time.perf_counter()
-    for _ in range(args.reps):
-        decode()
-    torch.cuda.synchronize()
-    wall = (time.perf_counter() - t0) / args.reps
-    prof = eng.profile_read()
-    eng.profile_enable(False)
-    stages = {k: v[0] / max(1, v[1]) for (k, v) in prof.items() if k.startswith('jpeg_')}
-    blocks = (w // 8) * (h // 8) * 3 // 2
-    jpeg_bytes = int(offsets[-1])
-    algo = {                                             # algorithmic bytes per batch, per stage
-        'jpeg_upload': jpeg_bytes + n * blocks * 128,    # H2D + coefficient clear
-        'jpeg_destuff': 2 * jpeg_bytes,
-        'jpeg_huffman': jpeg_bytes,                      # latency-bound: bytes are not the limit
-        'jpeg_idct': n * blocks * (128 + 64),
-        'jpeg_color': n * (blocks * 64 + h * w * 3),
-    }
-    dev_ms = sum(stages.values())
-    rep = {'workload': '%d streams %dx%d 4:2:0, %.1f KB avg' % (n, w, h, jpeg_bytes / n / 1024),
-           'decode': {'wall_ms_per_batch': wall * 1e3, 'device_ms_per_batch': dev_ms,
-                      'frames_per_s_device': n / (dev_ms / 1e3), 'frames_per_s_wall': n / wall,
-                      'stages_ms': stages,
-                      'stages_gbs': {k: algo[k] / (stages[k] / 1e3) / 1e9 for k in stages if stages[k] > 0},
-                      'hbm_peak_gbs': peaks['hbm_gbs'], 'peak_source': peaks['source']}}
-    print(json.dumps(rep['decode'], indent=1))
+        def decode():
+            eng.decode_jpeg_device(blob_p, offsets, h, w, out.data_ptr(), w * 3, h * w * 3, st.cuda_stream)
+        for _ in range(2):
+            decode()
+        torch.cuda.synchronize()
+        for i in (0, 1, len(base) - 1):
+            assert np.array_equal(out[i].cpu().numpy(), oracle.decode_jpeg(data[i])), i
+        eng.profile_enable(True)
+        t0 = time.perf_counter()
+        for _ in range(args.reps):
+            decode()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / args.reps
+        prof = eng.profile_read()
+        eng.profile_enable(False)
+        stages = {k: v[0] / max(1, v[1]) for (k, v) in prof.items() if k.startswith('jpeg_')}
+        blocks = (w // 8) * (h // 8) * 3 // 2
+        jpeg_bytes = int(offsets[-1])
+        algo = {                                             # algorithmic bytes per batch, per stage
+            'jpeg_upload': jpeg_bytes + n * blocks * 128,    # H2D + coefficient clear
+            'jpeg_destuff': 2 * jpeg_bytes,
+            'jpeg_huffman': jpeg_bytes,                      # latency-bound: bytes are not the limit
+            'jpeg_idct': n * blocks * (128 + 64),
+            'jpeg_color': n * (blocks * 64 + h * w * 3),
+        }
+        dev_ms = sum(stages.values())
+        rep.update({
+               'decode': {'wall_ms_per_batch': wall * 1e3, 'device_ms_per_batch': dev_ms,
+                          'frames_per_s_device': n / (dev_ms / 1e3), 'frames_per_s_wall': n / wall,
+                          'stages_ms': stages,
+                          'stages_gbs': {k: algo[k] / (stages[k] / 1e3) / 1e9 for k in stages if stages[k] > 0},
+                          'hbm_peak_gbs': peaks['hbm_gbs'], 'peak_source': peaks['source']}})
+        print(json.dumps(rep['decode'], indent=1))
+        del out
+        torch.cuda.empty_cache()
 
     # end to end: host JPEG bytes -> host readings
     res = eng.read_jpeg_streams(data[:64])               # warm-up + check
@@ -108,6 +113,12 @@ def main():
     for _ in range(args.reps):
         eng._check(lib.melf_read_jpeg_batch(eng._ctx, blob_p.ctypes.data, offsets.ctypes.data, n, results.ctypes.data))
     e2e = (time.perf_counter() - t0) / args.reps
+    jpeg_bytes = int(offsets[-1])
+    eng.profile_enable(True)
+    eng._check(lib.melf_read_jpeg_batch(eng._ctx, blob_p.ctypes.data, offsets.ctypes.data, n, results.ctypes.data))
+    prof = eng.profile_read()
+    eng.profile_enable(False)
+    rep['e2e_stages_ms'] = {k: v[0] for (k, v) in prof.items() if v[1]}       # summed over the chunks of one call
     rep['e2e'] = {'ms_per_batch': e2e * 1e3, 'frames_per_s': n / e2e, 'h2d_bytes_per_batch': jpeg_bytes,
                   'd2h_bytes_per_batch': int(results.nbytes),
                   'frames_read_ok': int((results['status'] == 0).sum())}
