@@ -25,6 +25,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "melf_jpeg.h"
@@ -234,11 +235,31 @@ melf_jpeg_destuff_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__res
     if (tid == 0) { s_first = len; s_base = 0; }
     __syncthreads();
     // pass 1: first 0xFF that is followed by neither 0x00 nor a restart marker code (the end of the data)
+    // (16 aligned bytes per load; the bytes in front of the segment and behind it belong to the blob
+    // allocation -- headers in front, 16 bytes of slack behind -- and are masked out by the index test;
+    // only the ~6 % of vectors that hold a 0xFF byte are looked at byte by byte)
     uint32_t first = len;
-    for (uint32_t j = tid; j < len; j += DESTUFF_THREADS) {
-        if (src[j] == 0xFF) {
-            const uint8_t nx = j + 1 < len ? src[j + 1] : 0xD9;
-            if (nx != 0x00 && (nx & 0xF8) != 0xD0) { first = j; break; }
+    {
+        const uint32_t a0 = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15);
+        const uint4 *vsrc = reinterpret_cast<const uint4 *>(src - a0);
+        const uint32_t nvec = (a0 + len + 15) >> 4;
+        for (uint32_t v = tid; v < nvec && first == len; v += DESTUFF_THREADS) {
+            const uint4 q = __ldg(vsrc + v);
+            const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+            uint32_t any = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t inv = ~w4[k];                          // a 0xFF byte becomes a zero byte
+                any |= (inv - 0x01010101u) & ~inv & 0x80808080u;
+            }
+            if (any == 0) continue;
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const int64_t j = (int64_t)v * 16 + k - a0;
+                if (j < 0 || j >= (int64_t)len || (w4[k >> 2] >> (8 * (k & 3)) & 255) != 0xFF) continue;
+                const uint8_t nx = j + 1 < (int64_t)len ? src[j + 1] : 0xD9;
+                if (nx != 0x00 && (nx & 0xF8) != 0xD0) { first = (uint32_t)j; break; }
+            }
         }
     }
     if (first < len) atomicMin(&s_first, first);
@@ -506,16 +527,22 @@ melf_jpeg_idct_kernel(const uint8_t *__restrict__ blob, const JpegDesc *__restri
         9, 11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60,
         21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};
     const int img = blockIdx.y;
-    const int b = blockIdx.x * IDCT_THREADS + threadIdx.x;
-    if (b >= g.blocks_per_image) return;
-    const int comp = b >= g.block_off[2] && g.ncomp == 3 ? 2 : (b >= g.block_off[1] && g.ncomp == 3 ? 1 : 0);
-    const int local = b - (comp == 0 ? 0 : comp == 1 ? g.block_off[1] : g.block_off[2]);
-    const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
-    const int by = local / bw, bx = local - by * bw;
-    {   // only the blocks the colour stage will read
-        const int rc = comp ? 1 : 0;
-        if (bx < rect.bx0[rc] || bx > rect.bx1[rc] || by < rect.by0[rc] || by > rect.by1[rc]) return;
+    // thread = one block of the ones the colour stage will read: the luma rectangle first, then the
+    // chroma rectangle of each chroma component
+    int t = blockIdx.x * IDCT_THREADS + threadIdx.x;
+    const int rw0 = rect.bx1[0] - rect.bx0[0] + 1, n0 = rw0 * (rect.by1[0] - rect.by0[0] + 1);
+    const int rw1 = rect.bx1[1] - rect.bx0[1] + 1, n1 = rw1 * (rect.by1[1] - rect.by0[1] + 1);
+    if (t >= n0 + (g.ncomp == 3 ? 2 * n1 : 0)) return;
+    int comp = 0;
+    if (t >= n0) {
+        t -= n0;
+        comp = 1 + (t >= n1 ? 1 : 0);
+        t -= t >= n1 ? n1 : 0;
     }
+    const int rc = comp ? 1 : 0;
+    const int rw = comp ? rw1 : rw0;
+    const int by = rect.by0[rc] + t / rw, bx = rect.bx0[rc] + t % rw;
+    const int bw = comp == 0 ? g.blocks_w[0] : g.blocks_w[1];
     const JpegDesc d = desc[img];
     const uint8_t *q = blob + d.base + (comp == 0 ? d.quant_off[0] : comp == 1 ? d.quant_off[1] : d.quant_off[2]);
     const bool q16 = d.quant16 >> comp & 1;
@@ -642,7 +669,7 @@ melf_jpeg_color_kernel(const ColorArgs a, const JpegGeom g)
 {
     // thread = 4 pixels of one row at an image column that is a multiple of 4
     const int t0 = a.x0 >> 2;
-    const int T = t0 + blockIdx.x * COLOR_THREADS + threadIdx.x;
+    const int T = t0 + blockIdx.x * blockDim.x + threadIdx.x;
     const int y = a.y0 + blockIdx.y, img = blockIdx.z;
     const int X = 4 * T;
     if (X >= a.x0 + a.cw) return;
@@ -792,31 +819,70 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     JpegGeom g{};
     size_t clean_bytes = 0;
     bool shared_tables = true;
-    for (int i = 0; i < count; i++) {
-        const uint64_t o0 = batch.offsets[first + i], o1 = batch.offsets[first + i + 1];
-        if (o1 < o0 || o1 - o0 > 0xFFFFFFF0ull) {
-            if (err) *err = "bad stream offsets";
-            return 1;
-        }
-        JpegDesc &d = descs[i];
-        std::memset(&d, 0, sizeof d);
-        const char *e = parse_stream(batch.jpeg + o0, (size_t)(o1 - o0), &d, &g, i == 0);
-        if (e) {
-            if (err) *err = "stream " + std::to_string(first + i) + ": " + e;
-            return std::strncmp(e, "unsupported", 11) == 0 ? 3 : 1;
-        }
-        if (shared_tables && i > 0) {
-            const uint8_t *a = batch.jpeg + batch.offsets[first], *b = batch.jpeg + o0;
-            for (int t = 0; t < 4 && shared_tables; t++) {
-                const uint8_t *ta = a + descs[0].huff_off[t], *tb = b + d.huff_off[t];
-                int total = 0;
-                for (int k = 0; k < 16; k++) total += ta[k];
-                shared_tables = std::memcmp(ta, tb, 16 + (size_t)total) == 0;
+    // marker walk of streams [i0, i1): descriptors, DHT comparison against stream 0 (whose descriptor and the
+    // geometry `g` exist by then); reports the first stream that fails
+    struct WalkResult { int bad = -1; int code = 0; std::string text; bool shared = true; };
+    auto walk = [&](int i0, int i1, WalkResult *r) {
+        for (int i = i0; i < i1; i++) {
+            const uint64_t o0 = batch.offsets[first + i], o1 = batch.offsets[first + i + 1];
+            const char *e = nullptr;
+            JpegDesc &d = descs[i];
+            if (o1 < o0 || o1 - o0 > 0xFFFFFFF0ull) {
+                e = "bad stream offsets";
+            } else {
+                std::memset(&d, 0, sizeof d);
+                e = parse_stream(batch.jpeg + o0, (size_t)(o1 - o0), &d, &g, i == 0);
             }
+            if (e) {
+                r->bad = i;
+                r->code = std::strncmp(e, "unsupported", 11) == 0 ? 3 : 1;
+                r->text = e;
+                return;
+            }
+            if (r->shared && i > 0) {
+                const uint8_t *a = batch.jpeg + batch.offsets[first], *b = batch.jpeg + o0;
+                for (int t = 0; t < 4 && r->shared; t++) {
+                    const uint8_t *ta = a + descs[0].huff_off[t], *tb = b + d.huff_off[t];
+                    int total = 0;
+                    for (int k = 0; k < 16; k++) total += ta[k];
+                    r->shared = std::memcmp(ta, tb, 16 + (size_t)total) == 0;
+                }
+            }
+            d.base = o0 - blob0;
         }
-        d.base = o0 - blob0;
-        d.clean_off = clean_bytes;
-        clean_bytes += (((size_t)d.scan_len + 15) & ~(size_t)15) + 32;
+    };
+    // stream 0 first (it defines the geometry), the rest on a few host threads when the chunk is large
+    static const int walk_threads = [] {
+        const char *e = std::getenv("MELF_JPEG_HOST_THREADS");
+        int v = e ? std::atoi(e) : (int)std::thread::hardware_concurrency() / 2;
+        return v < 1 ? 1 : v > 8 ? 8 : v;
+    }();
+    const int nt = count >= 2048 ? walk_threads : 1;
+    std::vector<WalkResult> results((size_t)nt + 1);
+    walk(0, 1, &results[0]);
+    if (results[0].bad < 0) {
+        if (nt == 1) {
+            walk(1, count, &results[1]);
+        } else {
+            std::vector<std::thread> pool;
+            const int per = (count - 1 + nt - 1) / nt;
+            for (int t = 0; t < nt; t++) {
+                const int i0 = 1 + t * per, i1 = i0 + per < count ? i0 + per : count;
+                if (i0 < i1) pool.emplace_back(walk, i0, i1, &results[(size_t)t + 1]);
+            }
+            for (std::thread &th : pool) th.join();
+        }
+    }
+    for (const WalkResult &r : results) {                 // ranges are in stream order: the first failure wins
+        if (r.bad >= 0) {
+            if (err) *err = r.text == "bad stream offsets" ? r.text : "stream " + std::to_string(first + r.bad) + ": " + r.text;
+            return r.code;
+        }
+        shared_tables = shared_tables && r.shared;
+    }
+    for (int i = 0; i < count; i++) {
+        descs[i].clean_off = clean_bytes;
+        clean_bytes += (((size_t)descs[i].scan_len + 15) & ~(size_t)15) + 32;
     }
     if (g.w != w || g.h != h) {
         if (err) *err = "the streams decode to " + std::to_string(g.w) + "x" + std::to_string(g.h) +
@@ -909,13 +975,17 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     }
 #undef MELF_HUFF_LAUNCH
     if (spans) { cudaEventRecord(spans[2][1], stream); cudaEventRecord(spans[3][0], stream); }
-    dim3 igrid((g.blocks_per_image + IDCT_THREADS - 1) / IDCT_THREADS, count);
+    const int idct_blocks = (br.bx1[0] - br.bx0[0] + 1) * (br.by1[0] - br.by0[0] + 1) +
+                            (g.ncomp == 3 ? 2 * (br.bx1[1] - br.bx0[1] + 1) * (br.by1[1] - br.by0[1] + 1) : 0);
+    dim3 igrid((idct_blocks + IDCT_THREADS - 1) / IDCT_THREADS, count);
     melf_jpeg_idct_kernel<<<igrid, IDCT_THREADS, 0, stream>>>(d_streams, d_desc, S.d_coef, g, br, mr, S.d_planes);
     if (spans) { cudaEventRecord(spans[3][1], stream); cudaEventRecord(spans[4][0], stream); }
     ColorArgs ca{S.d_planes, d_out, row_stride, frame_stride, x0, y0, cw, ch, count};
     const int cgroups = ((x0 + cw + 3) >> 2) - (x0 >> 2);
-    dim3 cgrid((cgroups + COLOR_THREADS - 1) / COLOR_THREADS, ch, count);
-    melf_jpeg_color_kernel<<<cgrid, COLOR_THREADS, 0, stream>>>(ca, g);
+    // narrow rectangles: 64-thread CTAs, so that no warp is launched just to return
+    const int cthreads = cgroups <= 64 ? 64 : COLOR_THREADS;
+    dim3 cgrid((cgroups + cthreads - 1) / cthreads, ch, count);
+    melf_jpeg_color_kernel<<<cgrid, cthreads, 0, stream>>>(ca, g);
     if (spans) cudaEventRecord(spans[4][1], stream);
     JPEG_CUDA(cudaGetLastError());
     if (launches) *launches += 4;
