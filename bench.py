@@ -155,6 +155,28 @@ def cpu_arm(gs, frames_host, n_threads):
     return (res, dt)
 
 
+_RESULT_FD = None
+
+
+def protect_stdout():
+    """stdout carries exactly one JSON line: keep the real stdout aside and point fd 1 at stderr,
+    so that nothing a library prints there (NCCL's version banner, C-level printf) can precede it."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    text = (json.dumps(line) + '\n').encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(text.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, text)
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (oracle port; the reference itself is
     Python + OpenCV and cannot travel to the GPU box) on all host cores, same workload."""
@@ -183,7 +205,7 @@ def run_reference(args):
                          'sample': '%d frames per step' % sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def load_traffic():
@@ -403,7 +425,7 @@ def run_ours(args):
                          'mismatches_vs_gpu': mism},
         'check': {'frames_read_ok': n_ok, 'frames': n},
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -421,6 +443,7 @@ def main():
     ap.add_argument('--e2e-frames', type=int, default=4096)
     ap.add_argument('--cpu-frames', type=int, default=8192, help='CPU baseline sample (frames)')
     args = ap.parse_args()
+    protect_stdout()
     set_frame_size(args.size)
     if not args.frames:
         world = int(os.environ.get('WORLD_SIZE', '1'))

@@ -375,6 +375,13 @@ __device__ void build_tables(HuffSmem &S, const uint8_t *__restrict__ stream, co
 // that the end of a block costs one pointer increment; the IDCT kernel undoes both orders.
 // SHARED: every stream of the launch carries the same four Huffman tables (the host compared the
 // DHT bytes), so one set of tables per CTA serves all lanes.
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+{
+    uint16_t v;
+    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+}
+
 template <int G, bool SHARED>
 __global__ void __launch_bounds__(32)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
@@ -393,6 +400,9 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     const int img = img0 + lane;
     if (lane >= G || img >= n) return;
     const HuffSmem &T = S[SHARED ? 0 : lane];
+    // the look-ahead tables are read through a shared-window address computed once (a generic pointer
+    // makes the compiler rebuild the window base in every iteration, on the critical path of the lookup)
+    const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(&T.lut[0][0]);
     const uint64_t base = desc[img].base;
     const int restart = (int)desc[img].restart;
     const uint8_t *stream = blob + base;
@@ -405,30 +415,33 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     bool keep = R.my0 == 0 && R.mx0 == 0;
     int16_t *blk = keep ? kept : trash;
 
-    unsigned long long acc = 0;
-    int nbits = 0, wp = 0;
-    uint32_t nextw = wmax > 0 ? src[0] : 0;
+    // bit reader: w0 = the 32 bits being consumed (first bit of the stream in the MSB), w1 = the 32 bits
+    // after them, bp = bits of w0 already used (< 32 once refilled), nextw = the word after w1 (as loaded).
+    // A code (<= 16 bits) and its extra bits (<= 15) always fit the 32-bit window funnel-shifted out of w0:w1.
+    uint32_t w0 = __byte_perm(wmax > 0 ? src[0] : 0, 0, 0x0123), w1 = __byte_perm(wmax > 1 ? src[1] : 0, 0, 0x0123);
+    int wp = 2, bp = 0;
+    uint32_t nextw = wp < wmax ? src[wp] : 0;
     // DC predictors: (pred, pred1, pred2) belong to components (comp, comp + 1, comp + 2) mod 3 and rotate
     // when the component changes at the end of a block, so the symbol loop touches only `pred`
-
     int pred = 0, pred1 = 0, pred2 = 0;
     int slot = 0, k = 0, comp = 0, in_interval = 0;
     const int nslots = g.nslots;
     const uint32_t slot_info = g.slot_info;
     int left = (R.my1 * mcus_x + R.mx1 + 1) * nslots;          // nothing after the last kept MCU is needed
     while (left > 0) {
-        {   // refill: 32 more bits when at most 32 are left
-            const bool need = nbits <= 32;
-            const unsigned long long add = (unsigned long long)__byte_perm(nextw, 0, 0x0123) << ((32 - nbits) & 63);
-            acc |= need ? add : 0ull;
-            nbits += need ? 32 : 0;
+        {   // refill: w0 is used up
+            const bool need = bp >= 32;
+            bp -= need ? 32 : 0;
+            w0 = need ? w1 : w0;
+            w1 = need ? __byte_perm(nextw, 0, 0x0123) : w1;
             wp += need ? 1 : 0;
             if (need) nextw = wp < wmax ? src[wp] : 0;
         }
         const bool is_dc = k == 0;
         const int t = (comp ? 2 : 0) + (is_dc ? 0 : 1);
-        const uint32_t win16 = (uint32_t)(acc >> 48);
-        const uint32_t e = T.lut[t][win16 >> (16 - kLook)];
+        const uint32_t win = __funnelshift_l(w1, w0, bp);
+        const uint32_t win16 = win >> 16;
+        const uint32_t e = lds_u16(lut_base + (uint32_t)t * (kLutEntries * 2) + ((win >> (32 - kLook)) << 1));
         int len = (int)(e >> 8), sym = (int)(e & 255);
         if (e == 0) {                                    // code longer than kLook bits (rare)
             int l = kLook + 1;
@@ -440,9 +453,8 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             len = l;
         }
         const int s = sym & 15, r = sym >> 4;
-        const uint32_t bits = (uint32_t)(((acc << len) >> 1) >> (63 - s));
-        acc <<= (len + s);
-        nbits -= len + s;
+        const uint32_t bits = ((win << len) >> 1) >> (31 - s);
+        bp += len + s;
         const int v = (s && bits < (1u << (s - 1))) ? (int)bits - (1 << s) + 1 : (int)bits;   // EXTEND
         // DC: difference to the predictor of the component; AC: run r, value v; (0,0) end of block; (15,0) 16 zeros
         pred += is_dc ? v : 0;
@@ -457,13 +469,11 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             const bool mcu_end = slot + 1 == nslots;
             slot = mcu_end ? 0 : slot + 1;
             const int ncomp = (int)(slot_info >> (4 * slot) & 3);
-            if (ncomp != comp) {                                      // 0 -> 1 -> 2 -> 0 in scan order
-                // park the predictor of the component that ends, fetch the one that begins:
-                // (pred, pred1, pred2) hold components (comp, comp + 1, comp + 2) mod 3
+            if (ncomp != comp) {
+                // the scan interleaves the components 0 -> 1 -> 2 -> 0 (parse_stream checks the order):
+                // park the predictor of the component that ends, fetch the one that begins
                 const int t0 = pred;
-                pred = ncomp == (comp + 1) % 3 ? pred1 : pred2;
-                if (ncomp == (comp + 1) % 3) { pred1 = pred2; pred2 = t0; }
-                else { pred2 = pred1; pred1 = t0; }
+                pred = pred1; pred1 = pred2; pred2 = t0;
                 comp = ncomp;
             }
             if (mcu_end) {
@@ -475,9 +485,14 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             blk = keep ? kept : trash;
             if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
                 in_interval = 0;
-                const int drop = nbits & 7;                           // to the byte boundary
-                acc <<= drop;
-                nbits -= drop;
+                bp = (bp + 7) & ~7;                                   // to the byte boundary
+                if (bp >= 64) {                                       // (the loop's refill covers bp < 64)
+                    bp -= 32;
+                    w0 = w1;
+                    w1 = __byte_perm(nextw, 0, 0x0123);
+                    wp++;
+                    nextw = wp < wmax ? src[wp] : 0;
+                }
                 pred = pred1 = pred2 = 0;
             }
         }
