@@ -100,6 +100,64 @@ def valid_crops(gs):
     return sub['crops'][keep]
 
 
+class NvmlSampler:
+    """SM clock, power and throttle reasons polled in-process through NVML every ~2 ms, so that a
+    timed region of a few tens of milliseconds still gets a useful number of samples (nvidia-smi
+    cannot loop faster than a few samples per second)."""
+
+    REASONS = (('hw_slowdown', 0x8), ('hw_thermal_slowdown', 0x40), ('sw_thermal_slowdown', 0x20),
+               ('sw_power_cap', 0x4))
+
+    def __init__(self, gpu_index):
+        import threading
+        import pynvml
+        self.nv = pynvml
+        pynvml.nvmlInit()
+        self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        self.rows = []
+        self.done = threading.Event()
+        self.thread = threading.Thread(target=self._poll, daemon=True)
+        self.thread.start()
+
+    def _poll(self):
+        nv = self.nv
+        while not self.done.is_set():
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                power = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((sm, power, mask))
+            except Exception:
+                pass
+            self.done.wait(0.002)
+
+    def stop(self):
+        self.done.set()
+        self.thread.join(timeout=2)
+        out = {'sm_mhz': None, 'sm_max_mhz': self.smax, 'reasons': [], 'samples': len(self.rows),
+               'sampler': 'nvml, 2 ms period'}
+        if self.rows:
+            pmax = max(r[1] for r in self.rows)
+            busy = [r[0] for r in self.rows if r[1] >= 0.5 * pmax] or [r[0] for r in self.rows]
+            mask = 0
+            for r in self.rows:
+                mask |= r[2]
+            out.update(sm_mhz=float(np.median(busy)), power_w_max=pmax,
+                       reasons=sorted(name for (name, bit) in self.REASONS if mask & bit))
+        return out
+
+
+def start_clock_sampler(gpu_index):
+    try:
+        return NvmlSampler(gpu_index)
+    except Exception:
+        return ClockSampler(gpu_index)
+
+
 class ClockSampler:
     def __init__(self, gpu_index):
         self.tmp = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
@@ -218,6 +276,48 @@ def load_traffic():
     return {}
 
 
+def ingest_leg(torch, eng, gs, n_streams, reps=3):
+    """SURVEY 8f-1, reported beside the headline: the reference's real input is JPEG files, so this
+    leg times melf_read_jpeg_batch -- host JPEG bytes in (page-locked), host readings out, decode
+    bit-identical to cv2.imread on the GPU -- over the portrait sample files of set 1 repeated to
+    n_streams, and checks every reading against the reference's golden line."""
+    from helpers import GOLDEN, format_result_line
+    from test_jpeg_oracle import load_streams
+    from meterelf_b200 import _engine
+    full = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    streams = load_streams(full if os.path.exists(full) else os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    base = [s for s in streams if s[4] == 1 and s[2] == (640, 480)]
+    data = [base[i % len(base)][1] for i in range(n_streams)]
+    (blob, offsets) = _engine.pack_streams(data)
+    blob_p = torch.from_numpy(blob.copy()).pin_memory().numpy()
+    results = np.zeros((n_streams,), _engine.RESULT_DTYPE)
+
+    def call():
+        eng._check(eng.lib.melf_read_jpeg_batch(eng._ctx, blob_p.ctypes.data, offsets.ctypes.data,
+                                                n_streams, results.ctypes.data))
+    for _ in range(2):
+        call()
+    launches0 = _engine.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        call()
+    dt = (time.perf_counter() - t0) / reps
+    launches = (_engine.launch_count() - launches0) // reps
+    bad = 0
+    for i in range(len(base)):
+        exp = gs.expected[base[i][0]]
+        got = format_result_line(results[i], gs.names)
+        bad += (got != exp['line']) if exp['status'] == 0 else (got.split(' (match val')[0] != exp['line'].split(' (match val')[0])
+    return {'metric': 'meter readings/sec from JPEG bytes (480x640 4:2:0 files, %.1f KB avg)' % (int(offsets[-1]) / n_streams / 1024),
+            'value': n_streams / dt, 'unit': UNIT, 'streams_per_step': n_streams, 'steps': reps,
+            'ms_per_step': dt * 1e3, 'h2d_bytes_per_step': int(offsets[-1]),
+            'd2h_bytes_per_step': int(results.nbytes), 'gpu_launches_per_step': int(launches),
+            'golden_lines_checked': len(base), 'golden_line_mismatches': int(bad),
+            'note': 'melf_read_jpeg_batch: header walk on the host, Huffman / IDCT / upsampling / colour on the '
+                    'GPU (bit-identical to cv2.imread), then the same locate and dial kernels; GPU-bound '
+                    '(Huffman stage), see DESIGN.md section 8'}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -260,7 +360,7 @@ def run_ours(args):
     for _ in range(warmup):
         step()
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = start_clock_sampler(local) if rank == 0 else None
     launches0 = _engine.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
@@ -425,6 +525,8 @@ def run_ours(args):
                          'mismatches_vs_gpu': mism},
         'check': {'frames_read_ok': n_ok, 'frames': n},
     }
+    if world == 1 and args.ingest_streams > 0 and (FRAME_H, FRAME_W) == (640, 480):
+        line['ingest'] = ingest_leg(torch, eng, gs, args.ingest_streams)
     emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -442,6 +544,8 @@ def main():
                     '32768 / n_gpus for 1280x720)')
     ap.add_argument('--e2e-frames', type=int, default=4096)
     ap.add_argument('--cpu-frames', type=int, default=8192, help='CPU baseline sample (frames)')
+    ap.add_argument('--ingest-streams', type=int, default=32768,
+                    help='JPEG streams per step of the ingest leg (N=1 only; 0 = skip)')
     args = ap.parse_args()
     protect_stdout()
     set_frame_size(args.size)

@@ -65,6 +65,10 @@ def gpu_ingest_geometry(data: bytes) -> Optional[Tuple[int, ...]]:
     from . import _engine
     if data[:2] != b'\xff\xd8':
         return None
+    if b'\xff\xd9' not in data[-64:]:
+        # no end-of-image marker: a file cut short.  libjpeg zero-fills what is missing in its own
+        # way (jdhuff.c insufficient_data); let cv2.imread decide what the reference sees
+        return None
     try:
         info = _engine.jpeg_info(data)
     except _engine.EngineError:

@@ -386,6 +386,47 @@ def test_cli_on_jpeg_files_prints_the_golden_lines(set_no, tmp_path, capsys, mon
     assert run() == gpu_lines
 
 
+def test_api_sends_unsupported_files_through_cv2(tmp_path):
+    """Files the ingest kernels do not take (progressive JPEG, EXIF-rotated JPEG, a JPEG cut short, PNG)
+    go through cv2.imread like in the reference; supported ones in the same call still go to the GPU as
+    bytes.  Expected readings: the oracle on what cv2.imread returns for each file."""
+    import struct
+    import cv2
+    from meterelf_b200 import _image, get_meter_values
+    gs = golden_set(1)
+    params_file = write_params_yml(gs, tmp_path)
+    sub = gs.subset()
+    names = [str(s) for s in sub['names']]
+    crop = sub['crops'][names.index('20180814215230-01-e136.jpg')]
+    (x0, y0, x1, y1) = gs.meter_rect
+    frame = np.full((640, 480, 3), 90, np.uint8)
+    frame[y0:y1, x0:x1] = crop
+    files = {k: str(tmp_path / k) for k in ('base.jpg', 'prog.jpg', 'exif.jpg', 'cut.jpg', 'loss.png')}
+    cv2.imwrite(files['base.jpg'], frame, [cv2.IMWRITE_JPEG_QUALITY, 95])
+    cv2.imwrite(files['prog.jpg'], frame, [cv2.IMWRITE_JPEG_QUALITY, 95, cv2.IMWRITE_JPEG_PROGRESSIVE, 1])
+    cv2.imwrite(files['loss.png'], frame)
+    base = open(files['base.jpg'], 'rb').read()
+    tiff = b'II' + struct.pack('<HI', 42, 8) + struct.pack('<H', 1) + \
+        struct.pack('<HHIHH', 0x0112, 3, 1, 3, 0) + struct.pack('<I', 0)          # orientation 3: upside down
+    seg = b'Exif\0\0' + tiff
+    open(files['exif.jpg'], 'wb').write(base[:2] + b'\xff\xe1' + struct.pack('>H', len(seg) + 2) + seg + base[2:])
+    open(files['cut.jpg'], 'wb').write(base[:len(base) * 9 // 10])
+    routes = {k: _image.gpu_ingest_geometry(open(v, 'rb').read()) is not None for (k, v) in files.items()}
+    assert routes == {'base.jpg': True, 'prog.jpg': False, 'exif.jpg': False, 'cut.jpg': False, 'loss.png': False}
+    order = list(files)
+    got = list(get_meter_values(params_file, [files[k] for k in order]))
+    for (k, data) in zip(order, got):
+        img = cv2.imread(files[k])
+        want = oracle.read_batch(gs.oracle_params(), np.ascontiguousarray(img[y0:y1, x0:x1])[None], n_threads=1)[0]
+        line = format_result_line(want, gs.names)
+        if int(want['status']) == 0:
+            assert data.error is None and data.value == float(want['value']), k
+        else:
+            assert data.value is None and ('UNKNOWN ' + data.error.get_message()).split(' (match val')[0] == \
+                line.split(' (match val')[0], k
+    assert got[0].value is not None and got[1].value is not None and got[4].value is not None
+
+
 def test_debug_overlays_are_written_as_png_files(tmp_path, monkeypatch):
     """DEBUG + MELF_DEBUG_DIR leaves the reference's debug pictures (_reading.py:43-78,
     112-114) as PNG files; what they show is checked against the taps of the GPU path."""

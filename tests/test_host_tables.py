@@ -140,6 +140,8 @@ def test_jpeg_ingest_header_helpers():
     assert _image.exif_orientation(data) == 1
     assert _image.gpu_ingest_geometry(b'\x89PNG\r\n\x1a\n' + b'\0' * 64) is None
     assert _image.gpu_ingest_geometry(data[:100]) is None            # headers cut short
+    assert _image.gpu_ingest_geometry(data[:len(data) // 2]) is None  # entropy data cut short: no EOI
+    assert _image.gpu_ingest_geometry(data + b'\0' * 20) == geometry  # padding after EOI is fine
 
     def with_exif(orientation, order):
         fmt = '<' if order == b'II' else '>'
