@@ -10,7 +10,7 @@
 //                              segment and cuts it at the first marker (two passes: first marker,
 //                              then a block-wide scan compaction).
 //   melf_jpeg_huffman_kernel   sequential Huffman decoding, one lane per stream (G lanes of a
-//                              one-warp CTA active, so that a batch spreads over all SMs); 9-bit
+//                              one-warp CTA active, so that a batch spreads over all SMs); 10-bit
 //                              look-ahead tables built in shared memory straight from the DHT bytes
 //                              of the uploaded stream; coefficients stored in zig-zag order.
 //   melf_jpeg_idct_kernel      one thread per 8x8 block: dequantisation with the DQT bytes of the
@@ -32,7 +32,10 @@
 
 namespace {
 
-constexpr int kLook = 9;                 // look-ahead bits of the Huffman tables in shared memory
+#ifndef MELF_JPEG_LOOK
+#define MELF_JPEG_LOOK 10
+#endif
+constexpr int kLook = MELF_JPEG_LOOK;    // look-ahead bits of the Huffman tables in shared memory
 constexpr int kLutEntries = 1 << kLook;
 
 struct JpegDesc {                        // one per stream (device copy)
@@ -321,7 +324,9 @@ struct HuffSmem {                         // per stream
     uint32_t limit[4][8];                 // lengths kLook+1 .. 16: first 16-bit window value past the codes of
                                           // that length (canonical codes are contiguous, so monotone)
     int32_t valoff[4][8];                 // ... and symbol index - code of the first code of that length
-    uint32_t symbols[4];                  // offset of the table's symbol bytes in the stream
+    uint8_t vals[4][256];                 // the table's symbol bytes (codes longer than kLook bits look them up
+                                          // here: with 16 streams per warp some lane does so in most iterations,
+                                          // and a global load there was the kernel's top stall, ncu long_scoreboard)
 };
 
 // Builds the tables of one stream with the whole warp.
@@ -365,7 +370,7 @@ __device__ void build_tables(HuffSmem &S, const uint8_t *__restrict__ stream, co
             S.limit[t][lane] = lim;
             S.valoff[t][lane] = vo;
         }
-        if (lane == 0) S.symbols[t] = hoff + 16;
+        for (int i = lane; i < 256; i += 32) S.vals[t][i] = i < k ? symbols[i] : 0;
     }
 }
 
@@ -403,16 +408,18 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     // the look-ahead tables are read through a shared-window address computed once (a generic pointer
     // makes the compiler rebuild the window base in every iteration, on the critical path of the lookup)
     const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(&T.lut[0][0]);
-    const uint64_t base = desc[img].base;
     const int restart = (int)desc[img].restart;
-    const uint8_t *stream = blob + base;
     const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[img].clean_off);
     const int wmax = (int)((clean_len[img] + 3) >> 2);
     int16_t *kept = coef + (size_t)img * R.stride_blocks * 64;
     int16_t *const trash = kept + (size_t)(R.stride_blocks - 1) * 64;
+    // kept / skipped MCUs alternate in runs along the scan: my0 * mcus_x + mx0 skipped ones first, then
+    // mw kept and mcus_x - mw skipped ones per MCU row; `run` counts the current run down
     const int mcus_x = g.mcus_x;
-    int mcu_x = 0, mcu_y = 0;
-    bool keep = R.my0 == 0 && R.mx0 == 0;
+    const int run_keep = R.mw == mcus_x ? 0x7fffffff : R.mw, run_skip = mcus_x - R.mw;
+    int run = R.my0 * mcus_x + R.mx0;
+    bool keep = run == 0;
+    run = keep ? run_keep : run;
     int16_t *blk = keep ? kept : trash;
 
     // bit reader: w0 = the 32 bits being consumed (first bit of the stream in the MSB), w1 = the 32 bits
@@ -449,7 +456,7 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             for (int j = 0; j < 16 - kLook - 1; j++) l += win16 >= T.limit[t][j] ? 1 : 0;
             const bool valid = win16 < T.limit[t][16 - kLook - 1];
             const int idx = (int)(win16 >> (16 - l)) + T.valoff[t][l - kLook - 1];
-            sym = valid ? stream[T.symbols[t] + (idx & 255)] : 0;    // invalid code: libjpeg warns, returns 0
+            sym = valid ? T.vals[t][idx & 255] : 0;                  // invalid code: libjpeg warns, returns 0
             len = l;
         }
         const int s = sym & 15, r = sym >> 4;
@@ -476,11 +483,9 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                 pred = pred1; pred1 = pred2; pred2 = t0;
                 comp = ncomp;
             }
-            if (mcu_end) {
-                const bool row_end = mcu_x + 1 == mcus_x;
-                mcu_x = row_end ? 0 : mcu_x + 1;
-                mcu_y += row_end ? 1 : 0;
-                keep = mcu_y >= R.my0 && mcu_x >= R.mx0 && mcu_x <= R.mx1;
+            if (mcu_end && --run == 0) {
+                keep = !keep;
+                run = keep ? run_keep : run_skip;
             }
             blk = keep ? kept : trash;
             if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
