@@ -57,7 +57,9 @@ def read_frames_sharded(read_fn: Callable[[np.ndarray], np.ndarray], frames: np.
                         dst: Optional[int] = 0) -> Optional[np.ndarray]:
     """Every rank passes the same ``frames`` (n, h, w, 3) array (or at least its own slice of
     it); rank k reads frames [k*n/G, (k+1)*n/G) with ``read_fn`` (``Engine.read_frames`` of
-    the rank's GPU) and the records are gathered in frame order."""
+    the rank's GPU) and the records are gathered in frame order.  ``frames`` may be any
+    sliceable sequence: a list of JPEG byte strings with ``Engine.read_jpeg_streams`` as
+    ``read_fn`` shards the ingest path the same way."""
     import torch.distributed as dist
     n = len(frames)
     if dist.is_available() and dist.is_initialized():

@@ -80,3 +80,50 @@ def test_two_rank_gloo_shard_and_gather(tmp_path, n_frames):
             assert np.array_equal(got[k], want[k]), k
         assert got['dial_pos'].tobytes() == np.asarray(want['dial_pos']).tobytes()
         assert got['value'].tobytes() == np.asarray(want['value']).tobytes()
+
+
+def _stream_worker(rank, world, port, n_streams, out_dir):
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import oracle
+    from helpers import GOLDEN, golden_set
+    from test_jpeg_oracle import load_streams
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        gs = golden_set(1)
+        streams = [s[1] for s in load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+                   if s[4] == 1 and s[2] == (640, 480)][:n_streams]
+        (x0, y0, x1, y1) = gs.meter_rect
+
+        def read_fn(part):          # stand-in for Engine.read_jpeg_streams: decode + read with the oracle
+            out = np.zeros((len(part),), _engine.RESULT_DTYPE)
+            if len(part):
+                crops = np.stack([oracle.decode_jpeg(d)[y0:y1, x0:x1] for d in part])
+                res = oracle.read_batch(gs.oracle_params(), np.ascontiguousarray(crops), n_threads=1)
+                for k in out.dtype.names:
+                    out[k] = res[k]
+            return out
+        got = _sharding.read_frames_sharded(read_fn, streams, dst=None)
+        np.save(os.path.join(out_dir, 'srank%d.npy' % rank), got)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_shards_jpeg_streams(tmp_path):
+    """The ingest path shards like the frame path: a list of JPEG byte strings split by index."""
+    import torch.multiprocessing as mp
+    from helpers import GOLDEN, format_result_line, golden_set
+    from test_jpeg_oracle import load_streams
+    (world, n) = (2, 3)          # the committed subset holds three portrait files of set 1
+    mp.spawn(_stream_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    gs = golden_set(1)
+    names = [s[0] for s in load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+             if s[4] == 1 and s[2] == (640, 480)][:n]
+    a = np.load(os.path.join(str(tmp_path), 'srank0.npy'))
+    b = np.load(os.path.join(str(tmp_path), 'srank1.npy'))
+    assert a.tobytes() == b.tobytes() and len(a) == n
+    for (rec, name) in zip(a, names):
+        exp = gs.expected[name]
+        if exp['status'] == 0:
+            assert format_result_line(rec, gs.names) == exp['line'], name
