@@ -172,10 +172,11 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
  * Huffman, one scan, YCbCr 4:4:4 / 4:2:2 / 4:2:0 or grey, no restart intervals; every stream of a
  * call must decode to h x w pixels with the same subsampling.  Anything else: MELF_ERR_UNSUPPORTED /
  * MELF_ERR_INVALID with a text in melf_last_error -- never a silently different image.
- * One caveat: a stream whose entropy data ends early (file cut short, no EOI marker) is decoded with
- * zero bits after its end, MCU after MCU, whereas libjpeg stops decoding at the MCU that runs dry and
- * leaves the rest grey; callers that may see such files check for the EOI marker first (the Python
- * layer does, and sends those files through cv2.imread).
+ * A stream whose entropy data ends early (file cut short) is decoded like libjpeg decodes it
+ * (jdhuff.c insufficient_data): the MCU in which the data runs dry is finished on zero bits, the MCUs
+ * after it stay mid-grey.  What is NOT restated is libjpeg's resynchronisation on the fake EOI marker
+ * that its file source appends when such a stream also uses restart intervals; the Python layer
+ * therefore sends every file without an EOI marker through cv2.imread.
  * d_bgr: device, frame f at d_bgr + f*frame_stride, rows row_stride apart.  Asynchronous on
  * `stream` once the streams have been copied into the library's pinned staging buffer. */
 int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n, int h, int w,

@@ -179,6 +179,7 @@ const char *parse_stream(const uint8_t *data, size_t len, JpegDesc *d, JpegGeom 
                 if (dqt16[ctq[cu]]) d->quant16 |= 1u << c;
             }
             d->scan_off = (uint32_t)(i + (size_t)L);
+            if (len - (i + (size_t)L) > 0x0FFFFFFFu) return "unsupported: entropy-coded segment larger than 256 MB";
             d->scan_len = (uint32_t)(len - (i + (size_t)L));
             break;
         }
@@ -411,6 +412,7 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     const int restart = (int)desc[img].restart;
     const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[img].clean_off);
     const int wmax = (int)((clean_len[img] + 3) >> 2);
+    const uint32_t avail_bits = clean_len[img] * 8u;           // parse_stream caps a scan at 256 MB
     int16_t *kept = coef + (size_t)img * R.stride_blocks * 64;
     int16_t *const trash = kept + (size_t)(R.stride_blocks - 1) * 64;
     // kept / skipped MCUs alternate in runs along the scan: my0 * mcus_x + mx0 skipped ones first, then
@@ -487,8 +489,12 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                 keep = !keep;
                 run = keep ? run_keep : run_skip;
             }
-            blk = keep ? kept : trash;
+            // jdhuff.c insufficient_data: a symbol of this MCU needed bits past the end of the data (a stream
+            // cut short).  libjpeg finishes that MCU on zero bits, as was just done, and leaves the following
+            // MCUs untouched -- all zero, mid-grey after the IDCT -- until a restart re-arms the decoder.
+            bool dry = mcu_end && (uint32_t)(wp - 2) * 32u + (uint32_t)bp > avail_bits;
             if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
+                dry = false;
                 in_interval = 0;
                 bp = (bp + 7) & ~7;                                   // to the byte boundary
                 if (bp >= 64) {                                       // (the loop's refill covers bp < 64)
@@ -500,6 +506,20 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                 }
                 pred = pred1 = pred2 = 0;
             }
+            while (dry && left > 0) {                                 // skip one MCU (rare: damaged streams only)
+                kept += keep ? nslots * 64 : 0;
+                left -= nslots;
+                if (--run == 0) {
+                    keep = !keep;
+                    run = keep ? run_keep : run_skip;
+                }
+                if (restart && ++in_interval == restart) {
+                    in_interval = 0;
+                    dry = false;
+                    pred = pred1 = pred2 = 0;
+                }
+            }
+            blk = keep ? kept : trash;
         }
     }
 }

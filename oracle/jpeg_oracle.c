@@ -16,6 +16,10 @@
  *     libjpeg jdsample.c / jdmainct.c (context rows above the first / below the last real row
  *     are copies of that row; first/last column special cases),
  *   - the 16-bit fixed point YCbCr -> RGB tables of libjpeg jdcolor.c.
+ *   - files cut short: jdhuff.c insufficient_data (the MCU in which the data runs dry is finished on zero
+ *     bits, the following MCUs stay all zero until a restart marker re-arms the decoder); pinned against
+ *     cv2.imread on 89 truncated files (tests/golden/make_golden_jpeg_truncated.py).  Not restated:
+ *     jpeg_resync_to_restart on the fake EOI of libjpeg's file source (truncated streams WITH restarts).
  * Pinned against cv2.imread on all 304 sample JPEGs of the reference (tests/golden/
  * make_golden_jpeg.py, run in the build container) -- see tests/test_jpeg_oracle.py.
  *
@@ -66,6 +70,8 @@ typedef struct {
     uint64_t acc;
     int bits;
     int hit_marker;
+    int real;          /* how many of `bits` are data; the rest is the zero padding after the data */
+    int insufficient;  /* jdhuff.c insufficient_data: a symbol needed more bits than the data holds */
 } BitReader;
 
 static void br_fill(BitReader *br) {
@@ -86,6 +92,7 @@ static void br_fill(BitReader *br) {
         } else {
             br->hit_marker = 1;
         }
+        if (!br->hit_marker) br->real = br->bits + 8;      /* data bytes always sit in front of the padding */
         br->acc |= (uint64_t)c << (56 - br->bits);
         br->bits += 8;
     }
@@ -99,6 +106,12 @@ static inline unsigned br_peek16(BitReader *br) {
 static inline void br_skip(BitReader *br, int n) {
     br->acc <<= n;
     br->bits -= n;
+    if (n > br->real) {                 /* jpeg_fill_bit_buffer: nbits > bits_left and no more bytes */
+        br->insufficient = 1;
+        br->real = 0;
+    } else {
+        br->real -= n;
+    }
 }
 
 static inline int br_get(BitReader *br, int n) {
@@ -258,22 +271,26 @@ static int decode_scan(Decoder *d) {
         k->coef = (int16_t *)calloc((size_t)k->blocks_w * k->blocks_h * 64, sizeof(int16_t));
         if (!k->coef) return JO_ERR_SPACE;
     }
-    BitReader br = {d->scan, d->scan + d->scan_len, 0, 0, 0};
+    BitReader br = {d->scan, d->scan + d->scan_len, 0, 0, 0, 0, 0};
     int pred[3] = {0, 0, 0};
     int todo = d->restart_interval;
     for (int my = 0; my < d->mcus_y; my++) {
         for (int mx = 0; mx < d->mcus_x; mx++) {
             if (d->restart_interval && todo == 0) {        /* process_restart */
-                br.acc = 0; br.bits = 0;                   /* discard the partial byte */
+                br.acc = 0; br.bits = 0; br.real = 0;      /* discard the partial byte */
                 if (br.hit_marker || (br.p + 1 < br.end && br.p[0] == 0xFF)) {
                     while (br.p + 1 < br.end && !(br.p[0] == 0xFF && br.p[1] >= 0xD0 && br.p[1] <= 0xD7)) br.p++;
                     if (br.p + 1 < br.end) br.p += 2;
                     br.hit_marker = 0;
+                    br.insufficient = 0;                   /* process_restart: a found marker re-arms decoding */
                 }
                 pred[0] = pred[1] = pred[2] = 0;
                 todo = d->restart_interval;
             }
-            for (int c = 0; c < d->ncomp; c++) {
+            /* decode_mcu: once the data has run dry the remaining MCUs are left as they are (all zero:
+             * mid-grey after the IDCT); the MCU in which it happened is finished on zero bits */
+            const int dry = br.insufficient;
+            for (int c = 0; c < d->ncomp && !dry; c++) {
                 Component *k = &d->comp[c];
                 const HuffTable *dct = d->dc[k->td], *act = d->ac[k->ta];
                 for (int by = 0; by < k->vs; by++) {

@@ -98,6 +98,38 @@ def test_unsupported_and_damaged_streams_fail_loudly():
         decode_on_gpu(eng, [data], shape[0] + 1, shape[1])
 
 
+def test_streams_cut_short_decode_like_libjpeg():
+    """Truncated entropy data (jdhuff.c insufficient_data) through melf_decode_jpeg: equal to the oracle
+    for every committed stream, restart intervals included, and to cv2.imread's vectors where they exist."""
+    import json
+    eng = golden_set(1).engine()
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    with open(os.path.join(GOLDEN, 'jpeg_truncated.json')) as fp:
+        vectors = {(c['name'], c['keep']): c['sha256'] for c in json.load(fp)}
+    (n, n_vec) = (0, 0)
+    for frac in (0.35, 0.5, 0.77, 0.93, 0.999):
+        cut = []
+        for s in streams:
+            part = s[1][:int(len(s[1]) * frac)]
+            try:
+                oracle.decode_jpeg(part)
+            except oracle.JpegError:              # cut inside the headers
+                continue
+            cut.append((s[0], part, s[2], None, s[4]))
+        for group in batches(cut):
+            (h, w) = group[0][2]
+            got = decode_on_gpu(eng, [s[1] for s in group], h, w)
+            for (img, s) in zip(got, group):
+                want = oracle.decode_jpeg(s[1])
+                assert np.array_equal(img, want), (s[0], frac, np.argwhere(img != want)[:3])
+                sha = vectors.get((s[0], len(s[1])))
+                if sha:
+                    assert hashlib.sha256(img.tobytes()).hexdigest() == sha, (s[0], frac)
+                    n_vec += 1
+                n += 1
+    assert n >= 150 and n_vec >= 60
+
+
 @pytest.mark.parametrize('set_no', [1, 2])
 def test_readings_from_jpeg_bytes_match_the_golden_lines(set_no):
     path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')

@@ -48,3 +48,16 @@ def test_oracle_rejects_what_it_does_not_restate():
     prog[i + 1] = 0xC2                                       # claim progressive
     with pytest.raises(oracle.JpegError):
         oracle.decode_jpeg(bytes(prog))
+
+
+def test_oracle_matches_cv2_on_files_cut_short():
+    """jdhuff.c insufficient_data: the MCU in which the data runs dry is finished on zero bits, the
+    rest stays mid-grey.  Vectors: cv2.imread on truncated files (make_golden_jpeg_truncated.py)."""
+    import json
+    streams = {s[0]: s[1] for s in load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))}
+    with open(os.path.join(GOLDEN, 'jpeg_truncated.json')) as fp:
+        cases = json.load(fp)
+    assert len(cases) >= 80
+    for case in cases:
+        img = oracle.decode_jpeg(streams[case['name']][:case['keep']])
+        assert hashlib.sha256(img.tobytes()).hexdigest() == case['sha256'], (case['name'], case['keep'])
