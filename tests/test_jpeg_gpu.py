@@ -130,6 +130,29 @@ def test_streams_cut_short_decode_like_libjpeg():
     assert n >= 150 and n_vec >= 60
 
 
+def test_readings_from_streams_cut_short_match_the_oracle():
+    """melf_read_jpeg_batch on truncated streams: the rectangle-only decode (kept / skipped MCU runs, early
+    stop) has to leave the same grey MCUs behind as the full decode, so the readings -- or the errors --
+    are the oracle's on the oracle's decode of the same bytes."""
+    gs = golden_set(1)
+    eng = gs.engine(cropped_input=False)
+    streams = [s for s in load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz')) if s[4] == 1 and s[2] == (640, 480)]
+    assert streams
+    (x0, y0, x1, y1) = gs.meter_rect
+    cut = []
+    for s in streams:
+        for frac in (0.3, 0.45, 0.55, 0.62, 0.7, 0.999):
+            cut.append(s[1][:int(len(s[1]) * frac)])
+    got = eng.read_jpeg_streams(cut)
+    crops = np.stack([oracle.decode_jpeg(d)[y0:y1, x0:x1] for d in cut])
+    want = oracle.read_batch(gs.oracle_params(), np.ascontiguousarray(crops), n_threads=4)
+    statuses = set()
+    for (i, (g, w)) in enumerate(zip(got, want)):
+        assert_results_equal(g, w, len(gs.names), i)
+        statuses.add(int(w['status']))
+    assert len(statuses) >= 2           # some cuts lose the dials, the late ones do not
+
+
 @pytest.mark.parametrize('set_no', [1, 2])
 def test_readings_from_jpeg_bytes_match_the_golden_lines(set_no):
     path = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
