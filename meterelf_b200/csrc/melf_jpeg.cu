@@ -485,38 +485,40 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                 pred = pred1; pred1 = pred2; pred2 = t0;
                 comp = ncomp;
             }
-            if (mcu_end && --run == 0) {
-                keep = !keep;
-                run = keep ? run_keep : run_skip;
-            }
-            // jdhuff.c insufficient_data: a symbol of this MCU needed bits past the end of the data (a stream
-            // cut short).  libjpeg finishes that MCU on zero bits, as was just done, and leaves the following
-            // MCUs untouched -- all zero, mid-grey after the IDCT -- until a restart re-arms the decoder.
-            bool dry = mcu_end && (uint32_t)(wp - 2) * 32u + (uint32_t)bp > avail_bits;
-            if (restart && mcu_end && ++in_interval == restart) {     // jdhuff.c process_restart
-                dry = false;
-                in_interval = 0;
-                bp = (bp + 7) & ~7;                                   // to the byte boundary
-                if (bp >= 64) {                                       // (the loop's refill covers bp < 64)
-                    bp -= 32;
-                    w0 = w1;
-                    w1 = __byte_perm(nextw, 0, 0x0123);
-                    wp++;
-                    nextw = wp < wmax ? src[wp] : 0;
-                }
-                pred = pred1 = pred2 = 0;
-            }
-            while (dry && left > 0) {                                 // skip one MCU (rare: damaged streams only)
-                kept += keep ? nslots * 64 : 0;
-                left -= nslots;
+            if (mcu_end) {                                            // one MCU in every nslots blocks
                 if (--run == 0) {
                     keep = !keep;
                     run = keep ? run_keep : run_skip;
                 }
-                if (restart && ++in_interval == restart) {
-                    in_interval = 0;
+                // jdhuff.c insufficient_data: a symbol of this MCU needed bits past the end of the data (a
+                // stream cut short).  libjpeg finishes that MCU on zero bits, as was just done, and leaves the
+                // following MCUs untouched -- all zero, mid-grey after the IDCT -- until a restart re-arms it.
+                bool dry = (uint32_t)(wp - 2) * 32u + (uint32_t)bp > avail_bits;
+                if (restart && ++in_interval == restart) {            // jdhuff.c process_restart
                     dry = false;
+                    in_interval = 0;
+                    bp = (bp + 7) & ~7;                               // to the byte boundary
+                    if (bp >= 64) {                                   // (the loop's refill covers bp < 64)
+                        bp -= 32;
+                        w0 = w1;
+                        w1 = __byte_perm(nextw, 0, 0x0123);
+                        wp++;
+                        nextw = wp < wmax ? src[wp] : 0;
+                    }
                     pred = pred1 = pred2 = 0;
+                }
+                while (dry && left > 0) {                             // skip one MCU (rare: damaged streams only)
+                    kept += keep ? nslots * 64 : 0;
+                    left -= nslots;
+                    if (--run == 0) {
+                        keep = !keep;
+                        run = keep ? run_keep : run_skip;
+                    }
+                    if (restart && ++in_interval == restart) {
+                        in_interval = 0;
+                        dry = false;
+                        pred = pred1 = pred2 = 0;
+                    }
                 }
             }
             blk = keep ? kept : trash;
