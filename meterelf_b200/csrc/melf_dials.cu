@@ -355,7 +355,7 @@ melf_dials_kernel(const MelfDialsArgs A)
 
     if (tl) tl[3] = clock64();
     // ---- components: largest filled area wins, first discovered wins ties -------------
-    u64 rem_a = era & D.disc_nb[2 * lane], rem_b = erb & D.disc_nb[2 * lane + 1];
+    u64 rem_a = era & D.disc[2 * lane], rem_b = erb & D.disc[2 * lane + 1];
     u64 best_a = 0, best_b = 0;
     int best_area2 = -1, ncomp = 0;
     for (int guard = 0; guard < 4096; ++guard) {

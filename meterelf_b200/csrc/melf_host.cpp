@@ -125,11 +125,7 @@ int melf_host_build_dial(const melf_params *P, int d, MelfDialDev *out,
             const int x = out->win_x0 + c;
             if (x < 0 || x >= tw) continue;
             const size_t i = (size_t)y * tw + x;
-            const bool frame = (x == 0 || y == 0 || x == tw - 1 || y == th - 1);
-            if (D.mask[i]) {
-                out->disc[r] |= 1ull << c;
-                if (!frame) out->disc_nb[r] |= 1ull << c;
-            }
+            if (D.mask[i]) out->disc[r] |= 1ull << c;
             if (D.circle_mask[i]) {
                 out->ring[r] |= 1ull << c;
                 const double dx = (double)x - D.center_x, dy = (double)y - D.center_y;
@@ -183,7 +179,7 @@ int melf_host_build_dial(const melf_params *P, int d, MelfDialDev *out,
 // ---- host-only debug export (tests/test_host_tables.py; needs no GPU) ----------------
 extern "C" int melf_host_dial_tables(const melf_params *P, int d,
                                      int32_t *geom /*[6]: win_x0,win_y0,win_w,win_h,patch_x,patch_y*/,
-                                     uint64_t *words /*[2 + 3*64]: colvalid,rowvalid,disc,disc_nb,ring*/,
+                                     uint64_t *words /*[2 + 2*64]: colvalid,rowvalid,disc,ring*/,
                                      double *terms /*[128]: termx, termy*/,
                                      int32_t *n_ring, uint16_t *ring_pos, double *ring_angle,
                                      double *ring_sqd, int32_t ring_cap)
@@ -200,8 +196,7 @@ extern "C" int melf_host_dial_tables(const melf_params *P, int d,
     geom[4] = dev.patch_x; geom[5] = dev.patch_y;
     words[0] = dev.colvalid; words[1] = dev.rowvalid;
     std::memcpy(words + 2, dev.disc, sizeof dev.disc);
-    std::memcpy(words + 2 + 64, dev.disc_nb, sizeof dev.disc_nb);
-    std::memcpy(words + 2 + 128, dev.ring, sizeof dev.ring);
+    std::memcpy(words + 2 + 64, dev.ring, sizeof dev.ring);
     std::memcpy(terms, dev.termx, sizeof dev.termx);
     std::memcpy(terms + 64, dev.termy, sizeof dev.termy);
     *n_ring = dev.n_ring;

@@ -20,9 +20,7 @@ struct MelfDialDev {
     double aoz_turns;            // angle_of_zero / 360.0 (_reading.py:95)
     uint64_t colvalid;           // bit c: column win_x0+c lies inside the dials rect
     uint64_t rowvalid;           // bit r: row win_y0+r lies inside the dials rect
-    uint64_t disc[64];           // DialData.mask
-    uint64_t disc_nb[64];        // DialData.mask minus the 1-px frame of the dials rect
-                                 // (findContours never reports frame pixels)
+    uint64_t disc[64];           // DialData.mask (frame pixels of the rect included: findContours pads)
     uint64_t ring[64];           // DialData.circle_mask
     double termx[64];            // sgn(dx)*dx^2 for dx = (win_x0+c) - center_x (_reading.py:36)
     double termy[64];            // same for rows (_reading.py:37)

@@ -98,6 +98,8 @@ const char *parse_stream(const uint8_t *data, size_t len, JpegDesc *d, JpegGeom 
     bool dqt16[4] = {false, false, false, false};
     int w = 0, h = 0, ncomp = 0, chs[3] = {0, 0, 0}, cvs[3] = {0, 0, 0}, ctq[3] = {0, 0, 0}, cid[3] = {0, 0, 0};
     bool sof = false;
+    bool saw_jfif = false, saw_adobe = false;       // libjpeg jdmarker.c examine_app0 / examine_app14
+    int adobe_transform = 0;
     size_t i = 2;
     for (;;) {
         if (i + 4 > len || data[i] != 0xFF) return "damaged JPEG headers";
@@ -152,6 +154,10 @@ const char *parse_stream(const uint8_t *data, size_t len, JpegDesc *d, JpegGeom 
         } else if (m == 0xDD) {
             if (n < 2) return "damaged DRI";
             d->restart = (uint32_t)rd16(seg);
+        } else if (m == 0xE0) {
+            if (n >= 14 && !std::memcmp(seg, "JFIF\0", 5)) saw_jfif = true;
+        } else if (m == 0xEE) {
+            if (n >= 12 && !std::memcmp(seg, "Adobe", 5)) { saw_adobe = true; adobe_transform = seg[11]; }
         } else if (m == 0xDA) {
             if (!sof) return "SOS before SOF";
             if (n < 1 || seg[0] != ncomp || n < 1 + 2 * ncomp + 3) return "unsupported: multi-scan JPEG";
@@ -187,6 +193,12 @@ const char *parse_stream(const uint8_t *data, size_t len, JpegDesc *d, JpegGeom 
     }
     int hs = 1, vs = 1;
     if (ncomp == 3) {
+        // libjpeg jdapimin.c default_decompress_parms: JFIF means YCbCr; else an Adobe marker decides
+        // (transform 0 = RGB); else the ids 'R','G','B' mean RGB.  The kernels convert YCbCr only, so
+        // RGB files go back to the caller (the Python layer hands them to cv2.imread).
+        const bool rgb = saw_jfif ? false : saw_adobe ? adobe_transform == 0
+                                                      : (cid[0] == 82 && cid[1] == 71 && cid[2] == 66);
+        if (rgb) return "unsupported: RGB colour space (Adobe transform 0 or component ids R, G, B)";
         hs = chs[0];
         vs = cvs[0];
         if (!((hs == 1 && vs == 1) || (hs == 2 && vs == 1) || (hs == 2 && vs == 2)) ||

@@ -26,6 +26,9 @@
  * Supported: SOF0/SOF1 8-bit Huffman, one scan; 3 components with luma sampling 1x1, 2x1 or 2x2
  * and 1x1 chroma, or 1 component (grey, replicated into B, G, R); restart intervals.
  * Everything else returns a negative code (the product returns an error for the same inputs).
+ * 3-component files that libjpeg reads as RGB (Adobe APP14 transform 0 without JFIF, or component
+ * ids 'R','G','B') are decoded without the YCbCr conversion here; the product sends those files
+ * through cv2.imread (melf_jpeg_info: "unsupported: RGB colour space").
  */
 #include <stdint.h>
 #include <stdlib.h>
@@ -56,6 +59,7 @@ typedef struct {
 
 typedef struct {
     int w, h, ncomp, max_h, max_v, mcus_x, mcus_y, restart_interval;
+    int rgb;                         /* libjpeg chose JCS_RGB: no YCbCr conversion (default_decompress_parms) */
     uint16_t quant[4][64];           /* natural order */
     int quant_present[4];
     HuffTable *dc[4], *ac[4];
@@ -162,6 +166,7 @@ static int parse_headers(Decoder *d, const uint8_t *data, size_t len) {
     if (len < 4 || data[0] != 0xFF || data[1] != 0xD8) return JO_ERR_FORMAT;
     size_t i = 2;
     int seen_sof = 0;
+    int saw_jfif = 0, saw_adobe = 0, adobe_transform = 0;
     for (;;) {
         if (i + 4 > len) return JO_ERR_FORMAT;
         if (data[i] != 0xFF) return JO_ERR_FORMAT;
@@ -225,6 +230,10 @@ static int parse_headers(Decoder *d, const uint8_t *data, size_t len) {
         } else if (m == 0xDD) {                            /* DRI */
             if (n < 2) return JO_ERR_FORMAT;
             d->restart_interval = rd16(seg);
+        } else if (m == 0xE0) {                            /* APP0: jdmarker.c examine_app0 */
+            if (n >= 14 && !memcmp(seg, "JFIF\0", 5)) saw_jfif = 1;
+        } else if (m == 0xEE) {                            /* APP14: jdmarker.c examine_app14 */
+            if (n >= 12 && !memcmp(seg, "Adobe", 5)) { saw_adobe = 1; adobe_transform = seg[11]; }
         } else if (m == 0xDA) {                            /* SOS */
             if (!seen_sof) return JO_ERR_FORMAT;
             if (n < 1 || seg[0] != d->ncomp || n < 1 + 2 * d->ncomp + 3) return JO_ERR_UNSUPPORTED;
@@ -239,6 +248,14 @@ static int parse_headers(Decoder *d, const uint8_t *data, size_t len) {
             break;
         }
         i += (size_t)L;
+    }
+    /* colour space of a 3-component file (libjpeg jdapimin.c default_decompress_parms): JFIF means
+     * YCbCr; else an Adobe marker decides (transform 0 = RGB); else the component ids 'R','G','B'
+     * mean RGB and anything else YCbCr */
+    if (d->ncomp == 3) {
+        if (saw_jfif) d->rgb = 0;
+        else if (saw_adobe) d->rgb = adobe_transform == 0;
+        else d->rgb = d->comp[0].id == 82 && d->comp[1].id == 71 && d->comp[2].id == 66;
     }
     /* geometry (libjpeg jdinput.c initial_setup / per_scan_setup) */
     if (d->ncomp == 1) {
@@ -461,6 +478,12 @@ int jo_decode_bgr(const uint8_t *data, size_t len, uint8_t *out, size_t out_cap,
             uint8_t *o = out + ((size_t)y * d.w + x) * 3;
             int yy = d.comp[0].plane[(size_t)y * d.comp[0].blocks_w * 8 + x];
             if (d.ncomp == 1) { o[0] = o[1] = o[2] = (uint8_t)yy; continue; }
+            if (d.rgb) {                                   /* jdcolor.c rgb_rgb_convert: components are R, G, B */
+                o[2] = (uint8_t)yy;
+                o[1] = (uint8_t)upsampled(&d, &d.comp[1], x, y);
+                o[0] = (uint8_t)upsampled(&d, &d.comp[2], x, y);
+                continue;
+            }
             int cb = upsampled(&d, &d.comp[1], x, y) - 128, cr = upsampled(&d, &d.comp[2], x, y) - 128;
             int r = yy + (int)((FIX(1.40200) * cr + ONE_HALF) >> SCALEBITS);
             int g = yy + (int)((-FIX(0.34414) * cb + ONE_HALF - FIX(0.71414) * cr) >> SCALEBITS);

@@ -83,7 +83,8 @@ def main():
         full += streams
         stride = max(1, len(streams) // SUBSET_PER_SET)
         subset += streams[::stride][:SUBSET_PER_SET]
-    src = cv2.imread(os.path.join(REF, 'sample-images1', '20180814021309-01-e01.jpg'))
+    # (not 20180814021309-01-e01.jpg: that frame is flat grey, its q75 streams were all-DC)
+    src = cv2.imread(os.path.join(REF, 'sample-images1', '20180814215230-01-e136.jpg'))
     subset += synthetic(src)
     np.savez_compressed(os.path.join(HERE, 'jpeg_subset.npz'), **pack(subset))
     os.makedirs(os.path.join(HERE, '_full'), exist_ok=True)

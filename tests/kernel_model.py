@@ -125,7 +125,7 @@ def read_dial(T, m0, neg_mom, aoz_turns):
         dn = pe[r + 1] if r < 63 else M64
         ero[r] = (up & pe[r] & dn) & V if rv(r) else 0
 
-    remaining = [ero[r] & T['disc_nb'][r] for r in range(64)]
+    remaining = [ero[r] & T['disc'][r] for r in range(64)]
     best, best_a2, ncomp = None, -1, 0
     while any(remaining):
         r0 = next(r for r in range(64) if remaining[r])

@@ -16,8 +16,8 @@ import pytest
 
 import oracle
 from helpers import (
-    GOLDEN, assert_results_equal, format_result_line, golden_set, synthetic_blob_frames,
-    window_words)
+    GOLDEN, SYNTHETIC_CASES, assert_results_equal, check_against_reference_record, format_result_line,
+    golden_set, synthetic_batch, synthetic_expected, window_words)
 
 pytestmark = pytest.mark.gpu
 
@@ -127,25 +127,70 @@ def test_device_resident_async_and_taps():
 # ---------------------------------------------------------------------------------------
 # branches the sample images never reach: synthetic blob frames, permissive threshold
 # ---------------------------------------------------------------------------------------
-@pytest.mark.parametrize('set_no,seed', [(2, 0), (2, 1), (1, 2)])
-def test_synthetic_blob_frames_all_branches(set_no, seed):
-    gs = golden_set(set_no)
-    rng = np.random.default_rng(seed)
+@pytest.mark.parametrize('case', [c[0] for c in SYNTHETIC_CASES])
+def test_synthetic_blob_frames_all_branches(case):
+    """Statuses 2 and 3, the area <= 100 branch, the tie-breaks and (set 3) discs cut by the
+    rect's frame: the GPU records against the oracle's AND against what the unmodified reference
+    computed on the same frames (tests/golden/synthetic_expected.json; near-tie rule for the
+    few frames where cv2's float32 DFT picks another arg-max, helpers.check_against_reference_record)."""
+    exp = synthetic_expected()[case]
+    gs = golden_set(exp['set'])
     (x0, y0, x1, y1) = gs.meter_rect
-    (h, w) = (y1 - y0, x1 - x0)
-    n = 160 if set_no == 2 else 48
-    frames = synthetic_blob_frames(rng, n, h, w)
-    # a few degenerate ones: flat colour (every TM value 0 -> match at (0,0), all in range)
-    frames[0] = 128
-    frames[1, :, :] = (40, 60, 200)
+    frames = synthetic_batch(exp['seed'], exp['n'], y1 - y0, x1 - x0)
     thr = -1e30
     got = gs.engine(cropped_input=True, threshold=thr).read_frames(frames)
-    want = oracle.read_batch(gs.oracle_params(threshold=thr), frames, n_threads=8)
+    O = gs.oracle_params(threshold=thr)
+    want = oracle.read_batch(O, frames, n_threads=8)
     seen = set()
     for (i, (g, wnt)) in enumerate(zip(got, want)):
         assert_results_equal(g, wnt, len(gs.names), 'frame %d' % i)
+        check_against_reference_record(gs, O, frames[i], g, None, exp['frames'][i], (case, i))
         seen.add(int(wnt['status']))
-    assert {0, 2, 3} & seen, seen        # the generator must reach the error branches
+    assert seen == {0, 2, 3}, seen        # the generator must reach the error branches
+
+
+def test_dial_taps_with_discs_cut_by_the_rect_frame():
+    """Set 3: needle masks, point counts and contour areas of components lying on the frame of
+    the dials rect (cv2.findContours pads the image) -- GPU taps against the oracle's,
+    which tests/test_oracle_golden.py pins to the reference on these very frames."""
+    torch = _torch()
+    from meterelf_b200 import _engine
+    gs = golden_set(3)
+    (x0, y0, x1, y1) = gs.meter_rect
+    frames = synthetic_batch(6, 64, y1 - y0, x1 - x0)
+    (n, h, w) = frames.shape[:3]
+    nd = len(gs.names)
+    eng = gs.engine(cropped_input=True, threshold=-1e30)
+    d_in = _dev(frames)
+    d_out = torch.zeros((n, _engine.RESULT_DTYPE.itemsize), dtype=torch.uint8, device='cuda')
+    t_words = [torch.zeros((n, nd, 64), dtype=torch.int64, device='cuda') for _ in range(3)]
+    t_col = torch.zeros((n, nd, 3), dtype=torch.int32, device='cuda')
+    t_cnt = torch.zeros((n, nd, 4), dtype=torch.int32, device='cuda')
+    t_mom = torch.zeros((n, nd, 3), dtype=torch.float64, device='cuda')
+    taps = _engine.CTaps(*(t.data_ptr() for t in t_words), t_col.data_ptr(), t_cnt.data_ptr(), t_mom.data_ptr())
+    eng.read_device(d_in.data_ptr(), n, h, w, w * 3, h * w * 3, d_out.data_ptr(),
+                    torch.cuda.current_stream().cuda_stream, taps)
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n)
+    nm = t_words[2].cpu().numpy().view(np.uint64)
+    de = t_words[1].cpu().numpy().view(np.uint64)
+    cnt = t_cnt.cpu().numpy()
+    O = gs.oracle_params(threshold=-1e30)
+    on_frame = 0
+    for i in range(n):
+        (res, ot) = oracle.read_frame(O, frames[i], want_taps=True)
+        assert_results_equal(got[i], res, nd, i)
+        last = nd if int(res['status']) != 2 else int(res['failed_dial'])
+        for d in range(last):
+            (wx, wy) = eng.dial_window(d)
+            disc = window_words(gs.dials[d]['mask'], wx, wy)
+            for (mine, theirs) in ((de, ot.mask_de), (nm, ot.needle_mask)):
+                assert np.array_equal(mine[i, d] & disc, window_words(theirs[d], wx, wy) & disc), (i, d)
+            assert cnt[i, d, 0] == ot.n_needle_points[d]
+            assert cnt[i, d, 2] == int(round(2 * ot.contour_area[d])), (i, d)
+            m = (ot.needle_mask[d] > 0) & (gs.dials[d]['mask'] > 0)
+            on_frame += int(m[0].any() or m[-1].any() or m[:, 0].any() or m[:, -1].any())
+    assert on_frame >= 20, on_frame       # the case must really put needle pixels on the frame
 
 
 def test_threshold_is_strict_less_than():

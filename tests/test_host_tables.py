@@ -86,7 +86,7 @@ def test_dial_tables_match_masks(set_no):
     (cp, keep) = gs.cparams()
     for d in range(len(gs.names)):
         geom = (C.c_int32 * 6)()
-        words = (C.c_uint64 * (2 + 3 * 64))()
+        words = (C.c_uint64 * (2 + 2 * 64))()
         terms = (C.c_double * 128)()
         n_ring = C.c_int32()
         cap = 4096
@@ -101,7 +101,7 @@ def test_dial_tables_match_masks(set_no):
         (cx, cy) = gs.dials[d]['center']
         assert (px, py) == (int(cx) - 2, int(cy) - 2)
         disc = np.array(list(words)[2:66], np.uint64)
-        ringw = np.array(list(words)[130:194], np.uint64)
+        ringw = np.array(list(words)[66:130], np.uint64)
         n_disc = sum(bin(int(w)).count('1') for w in disc)
         assert n_disc == int(np.count_nonzero(mask))
         assert sum(bin(int(w)).count('1') for w in ringw) == int(np.count_nonzero(ring))

@@ -178,3 +178,49 @@ def test_readings_from_jpeg_bytes_match_the_golden_lines(set_no):
             else:
                 assert line.split(' (match val')[0] == exp['line'].split(' (match val')[0], s[0]
     assert n_lines >= 2
+
+
+def test_colour_space_variants_ycbcr_on_the_gpu_rgb_back_to_the_host(tmp_path):
+    """streams libjpeg reads as YCbCr (JFIF, Adobe transform 1/2, any ids but R,G,B)
+    decode on the GPU like cv2 did; streams it reads as RGB (Adobe transform 0 / ids R,G,B without
+    JFIF) are refused by melf_decode_jpeg and reach the reading path through cv2.imread."""
+    import json
+    from helpers import jpeg_colour_space_bases, jpeg_colour_space_variants, write_params_file
+    from meterelf_b200 import _engine
+    with open(os.path.join(GOLDEN, 'jpeg_colorspace.json')) as fp:
+        vectors = {(v['name'], v['variant']): v for v in json.load(fp)}
+    eng = golden_set(1).engine()
+    for (name, data) in jpeg_colour_space_bases():
+        variants = jpeg_colour_space_variants(data)
+        ycc = [(key, v) for (key, v, is_rgb) in variants if not is_rgb]
+        (h, w) = vectors[(name, 'jfif')]['shape']
+        got = decode_on_gpu(eng, [v for (_k, v) in ycc], h, w)
+        for (img, (key, _v)) in zip(got, ycc):
+            assert hashlib.sha256(img.tobytes()).hexdigest() == vectors[(name, key)]['sha256'], (name, key)
+        for (key, v, is_rgb) in variants:
+            if is_rgb:
+                with pytest.raises(_engine.EngineError) as exc:
+                    decode_on_gpu(eng, [v], h, w)
+                assert exc.value.code == _engine.ERR_UNSUPPORTED
+    # through the Python API: an RGB-labelled sample file gives what cv2.imread gives
+    import cv2
+    import meterelf_b200
+    gs = golden_set(1)
+    params_file = write_params_file(gs, tmp_path)
+    (name, data) = jpeg_colour_space_bases()[0]
+    paths = []
+    for (key, v, is_rgb) in jpeg_colour_space_variants(data):
+        if key in ('jfif', 'adobe0', 'ids_rgb'):
+            paths.append(str(tmp_path / (key + '.jpg')))
+            with open(paths[-1], 'wb') as fp:
+                fp.write(v)
+    got = list(meterelf_b200.get_meter_values(params_file, paths))
+    (x0, y0, x1, y1) = gs.meter_rect
+    crops = np.stack([np.ascontiguousarray(cv2.imread(p)[y0:y1, x0:x1]) for p in paths])
+    want = oracle.read_batch(gs.oracle_params(), crops)
+    for (g, wnt, p) in zip(got, want, paths):
+        if int(wnt['status']) == 0:
+            assert g.error is None and g.value == float(wnt['value']), p
+        else:
+            assert g.error is not None and g.value is None, p
+            assert ('UNKNOWN ' + g.error.get_message()) == format_result_line(wnt, gs.names), p

@@ -61,3 +61,36 @@ def test_oracle_matches_cv2_on_files_cut_short():
     for case in cases:
         img = oracle.decode_jpeg(streams[case['name']][:case['keep']])
         assert hashlib.sha256(img.tobytes()).hexdigest() == case['sha256'], (case['name'], case['keep'])
+
+
+def test_colour_space_choice_follows_libjpeg():
+    """3-component files are RGB, not YCbCr, for libjpeg when an Adobe APP14 marker says
+    transform 0 or the component ids are 'R','G','B' (no JFIF marker).  The oracle decodes every
+    variant like cv2.imdecode did (make_golden_jpeg_colorspace.py); the product's header probe
+    accepts exactly the YCbCr ones, so the RGB ones take the cv2.imread route."""
+    import json
+    from helpers import jpeg_colour_space_bases, jpeg_colour_space_variants
+    from meterelf_b200 import _engine, _image
+    with open(os.path.join(GOLDEN, 'jpeg_colorspace.json')) as fp:
+        vectors = {(v['name'], v['variant']): v for v in json.load(fp)}
+    n_rgb = 0
+    for (name, data) in jpeg_colour_space_bases():
+        base_sha = None
+        for (key, variant, is_rgb) in jpeg_colour_space_variants(data):
+            v = vectors[(name, key)]
+            assert v['rgb'] == is_rgb
+            img = oracle.decode_jpeg(variant)
+            assert hashlib.sha256(img.tobytes()).hexdigest() == v['sha256'], (name, key)
+            if key == 'jfif':
+                base_sha = v['sha256']
+            assert (v['sha256'] == base_sha) == (not is_rgb), (name, key)   # the RGB ones really differ
+            geometry = _image.gpu_ingest_geometry(variant)
+            if is_rgb:
+                n_rgb += 1
+                assert geometry is None, (name, key)
+                with pytest.raises(_engine.EngineError) as exc:
+                    _engine.jpeg_info(variant)
+                assert exc.value.code == _engine.ERR_UNSUPPORTED and 'RGB' in str(exc.value)
+            else:
+                assert geometry is not None and geometry[:2] == tuple(v['shape']), (name, key)
+    assert n_rgb == 8
