@@ -4,18 +4,23 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 One "step" = one pass of the whole path (locate dials + read 4 dials + value) over one
-HBM-resident synthetic batch (default 4096 frames of 640x480x3 u8 per GPU = 3.77 GB,
-larger than L2, so no flush between steps; --size 1280x720 gives BASELINE.json's second
-throughput config, 32768 frames split over the GPUs).  Frames are "S-planted" (SURVEY.md 8d):
-uniform noise canvases with decoded sample meter crops pasted at the meter_rect with a
-seeded +-6 px jitter, so every stage runs on every frame and the expected readings are
-known.  Prints ONE JSON line (rank 0).  Frames shard by index over the GPUs: no data-path
-collective; torch.distributed is used only for the barrier and the max-over-ranks time.
+HBM-resident synthetic batch (4096 frames of 640x480x3 u8 per GPU = 3.77 GB, larger than L2, so no
+flush between steps).  Frames are "S-planted" (SURVEY.md 8d): uniform noise canvases with decoded
+sample meter crops pasted at the meter_rect with a seeded +-6 px jitter, so every stage runs on every
+frame and the expected readings are known.  Params reach the engine the product's own way:
+``params.yml`` + template file -> ``_params.load`` -> ``_reading.get_engine``.
+
+Prints ONE JSON line (rank 0).  Besides the headline (BASELINE.json configs[2]) it carries
+``config3`` (configs[3]: 1280x720 x 32768 frames in total, strong-scaled over the GPUs), ``set2``
+(the second sample geometry), ``micro_bench`` (configs[4], N=1), ``ingest`` (JPEG bytes -> readings,
+every N) and ``cpu_baseline`` (the unmodified reference on the host cores + the C port).  Frames shard
+by index over the GPUs: no data-path collective; torch.distributed is used for the barrier, the
+max-over-ranks time and the host-side gather of records that rank 0 checks for EVERY rank.
 """
 import argparse
 import json
+import math
 import os
-import subprocess
 import sys
 import tempfile
 import time
@@ -24,14 +29,11 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, 'tests'))
+sys.path.insert(0, os.path.join(ROOT, 'tests'))        # fixtures only (golden crops, params as arrays)
 
 METRIC = 'meter readings/sec (640x480 frames)'
 UNIT = 'frames/s'
-FRAME_H, FRAME_W = 640, 480        # default: the sample frames are portrait, 480 wide x 640 tall
-SMI_QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
-             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+TMPL_W, TMPL_H = 188, 119
 
 
 def load_peaks():
@@ -39,71 +41,25 @@ def load_peaks():
     if os.path.exists(path):
         with open(path) as fp:
             d = json.load(fp)
-        return dict(hbm_gbs=d['hbm_gbs'], bf16_tflops=d['bf16_tflops'], source='measured')
-    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source='fallback')
+        return dict(hbm_gbs=d['hbm_gbs'], bf16_tflops=d['bf16_tflops'],
+                    bf16_tflops_sustained=d.get('bf16_tflops_sustained', d['bf16_tflops']), source='measured')
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1590.0, source='fallback')
 
 
-def set_frame_size(size):
-    global FRAME_H, FRAME_W
-    (w, h) = (int(v) for v in size.lower().split('x'))
-    (FRAME_H, FRAME_W) = (h, w)
-
-
-def workload_config(frames):
-    return {
-        'workload': 'synthetic %dx%d (w x h) BGR batch of %d frames per GPU, S-planted sample meter '
-                    'crops (sample-images1 params, meter_rect 250x250, template 188x119)'
-                    % (FRAME_W, FRAME_H, frames),
-        'frames_per_gpu': frames, 'frame_h': FRAME_H, 'frame_w': FRAME_W,
-        'bytes_per_frame': FRAME_H * FRAME_W * 3,
-        'l2': 'batch (%.2f GB) is larger than L2; no flush between steps' % (
-            frames * FRAME_H * FRAME_W * 3 / 1e9),
-        'parallelism': 'frames sharded by index, one process per GPU, host-side gather',
-    }
-
-
-def planted_offsets(n, seed):
-    rng = np.random.default_rng(seed)
-    return rng.integers(-6, 7, size=(n, 2))
-
-
-def make_frames_host(gs, crops, n, seed):
-    """Host (numpy) version of the synthetic batch, used for the CPU arms and checks."""
-    rng = np.random.default_rng(seed + 1)
-    (x0, y0, x1, y1) = gs.meter_rect
-    frames = rng.integers(0, 256, size=(n, FRAME_H, FRAME_W, 3), dtype=np.uint8)
-    off = planted_offsets(n, seed)
-    for i in range(n):
-        (dx, dy) = off[i]
-        frames[i, y0 + dy:y1 + dy, x0 + dx:x1 + dx] = crops[i % len(crops)]
-    return frames
-
-
-def make_frames_device(torch, gs, crops, n, seed, device):
-    g = torch.Generator(device=device)
-    g.manual_seed(seed + 1)
-    frames = torch.randint(0, 256, (n, FRAME_H, FRAME_W, 3), dtype=torch.uint8, device=device,
-                           generator=g)
-    d_crops = torch.from_numpy(np.ascontiguousarray(crops)).to(device)
-    (x0, y0, x1, y1) = gs.meter_rect
-    off = planted_offsets(n, seed)
-    for i in range(n):
-        (dx, dy) = (int(off[i][0]), int(off[i][1]))
-        frames[i, y0 + dy:y1 + dy, x0 + dx:x1 + dx] = d_crops[i % len(crops)]
-    return frames
-
-
-def valid_crops(gs):
-    sub = gs.subset()
-    names = [str(s) for s in sub['names']]
-    keep = [i for (i, fn) in enumerate(names) if gs.expected[fn]['status'] == 0]
-    return sub['crops'][keep]
+def load_traffic():
+    """dram__bytes_read + dram__bytes_write per launch from the committed ncu captures
+    (tools/ncu_summary.py traffic ... > profiles/r0N_traffic.json, newest round first)."""
+    for name in ('r02_traffic.json', 'r01_traffic.json'):
+        path = os.path.join(ROOT, 'profiles', name)
+        if os.path.exists(path):
+            with open(path) as fp:
+                return json.load(fp)
+    return {}
 
 
 class NvmlSampler:
     """SM clock, power and throttle reasons polled in-process through NVML every ~2 ms, so that a
-    timed region of a few tens of milliseconds still gets a useful number of samples (nvidia-smi
-    cannot loop faster than a few samples per second)."""
+    timed region of a few tens of milliseconds still gets a useful number of samples."""
 
     REASONS = (('hw_slowdown', 0x8), ('hw_thermal_slowdown', 0x40), ('sw_thermal_slowdown', 0x20),
                ('sw_power_cap', 0x4))
@@ -146,71 +102,43 @@ class NvmlSampler:
             mask = 0
             for r in self.rows:
                 mask |= r[2]
-            out.update(sm_mhz=float(np.median(busy)), power_w_max=pmax,
+            out.update(sm_mhz=float(np.median(busy)), sm_mhz_min=float(min(busy)), power_w_max=pmax,
                        reasons=sorted(name for (name, bit) in self.REASONS if mask & bit))
         return out
+
+
+class NullSampler:
+    def stop(self):
+        return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0, 'sampler': 'unavailable'}
 
 
 def start_clock_sampler(gpu_index):
     try:
         return NvmlSampler(gpu_index)
     except Exception:
-        return ClockSampler(gpu_index)
+        return NullSampler()
 
 
-class ClockSampler:
-    def __init__(self, gpu_index):
-        self.tmp = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+def bind_to_gpu_cpus(gpu_index):
+    """Pin this rank to the CPUs NVML lists as local to its GPU before any page-locked buffer is
+    allocated (first touch puts the pages on that NUMA node).  Returns what was done."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for (i, w) in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
         try:
-            self.proc = subprocess.Popen(
-                ['nvidia-smi', '-i', str(gpu_index), '--query-gpu=' + SMI_QUERY,
-                 '--format=csv,noheader,nounits', '-lms', '100'],
-                stdout=self.tmp, stderr=subprocess.DEVNULL)
-        except OSError:
-            self.proc = None
-
-    def stop(self):
-        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
+            numa = int(pynvml.nvmlDeviceGetNumaNodeId(h))
         except Exception:
-            self.proc.kill()
-        self.tmp.flush()
-        self.tmp.seek(0)
-        sm, smax, power, reasons = [], [], [], set()
-        for line in self.tmp.read().splitlines():
-            cols = [c.strip() for c in line.split(',')]
-            if len(cols) < 9:
-                continue
-            try:
-                sm.append(float(cols[1])); smax.append(float(cols[2])); power.append(float(cols[3]))
-            except ValueError:
-                continue
-            for (name, val) in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown',
-                                    'sw_power_cap'), cols[5:9]):
-                if val.lower().startswith('active'):
-                    reasons.add(name)
-        os.unlink(self.tmp.name)
-        if sm:
-            busy = [s for (s, p) in zip(sm, power) if p >= 0.5 * max(power)] or sm
-            out.update(sm_mhz=float(np.median(busy)), sm_max_mhz=max(smax), samples=len(sm),
-                       power_w_max=max(power), reasons=sorted(reasons))
-        return out
-
-
-def cpu_arm(gs, frames_host, n_threads):
-    """The oracle port on host cores over full frames (meter_rect window by pointer math)."""
-    import oracle
-    (x0, y0, x1, y1) = gs.meter_rect
-    view = frames_host[:, y0:y1, x0:x1]
-    O = gs.oracle_params()
-    t0 = time.perf_counter()
-    res = oracle.read_batch(O, view, n_threads=n_threads)
-    dt = time.perf_counter() - t0
-    return (res, dt)
+            numa = None
+        return {'cpus': len(cpus), 'cpu_first': min(cpus) if cpus else None,
+                'cpu_last': max(cpus) if cpus else None, 'numa_node': numa}
+    except Exception as error:                          # noqa: BLE001 - reporting only
+        return {'cpus': len(os.sched_getaffinity(0)), 'error': str(error)[:80]}
 
 
 _RESULT_FD = None
@@ -235,59 +163,260 @@ def emit(line):
         os.write(_RESULT_FD, text)
 
 
-def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port; the reference itself is
-    Python + OpenCV and cannot travel to the GPU box) on all host cores, same workload."""
-    rank = int(os.environ.get('RANK', '0'))
-    if rank != 0:
-        return
-    from helpers import golden_set
-    gs = golden_set(1)
-    cores = len(os.sched_getaffinity(0))
-    sample = max(cores * 64, 256)              # ~1.5 s of CPU work per step
-    frames = make_frames_host(gs, valid_crops(gs), sample, seed=1234)
-    times = []
-    for i in range(args.warmup + args.steps):
-        (_res, dt) = cpu_arm(gs, frames, cores)
-        if i >= args.warmup:
-            times.append(dt)
-    total = sum(times)
-    value = sample * len(times) / total
-    line = {
-        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
-        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': 1e3 * total / len(times), 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'u8/int32/f64', 'data': 'synthetic',
-        'config': workload_config(args.frames),
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                         'sample': '%d frames per step' % sample},
-        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+# ---------------------------------------------------------------------------------------------
+# workloads: sample params through the product's own setup path, S-planted synthetic frames
+# ---------------------------------------------------------------------------------------------
+class Workload:
+    """Sample params `set_no` (from the committed fixture arrays: the reference tree does not exist
+    on the GPU box) written out as params.yml + template file and loaded the way a user's are:
+    ``_params.load`` -> ``_reading.get_engine`` (cv2-free dial masks, melf_create)."""
+
+    def __init__(self, set_no, tmpdir, device):
+        from helpers import golden_set, write_params_file
+        from meterelf_b200 import _params, _reading
+        self.gs = golden_set(set_no)
+        d = os.path.join(tmpdir, 'set%d' % set_no)
+        os.makedirs(d, exist_ok=True)
+        self.params_file = write_params_file(self.gs, d)
+        self.params = _params.load(self.params_file)
+        self.names = list(self.params.dial_centers.keys())
+        self.rect = self.params.meter_rect.top_left + self.params.meter_rect.bottom_right
+        self.engine = None if device is None else _reading.get_engine(self.params, cropped_input=False, device=device)
+        sub = self.gs.subset()
+        names = [str(s) for s in sub['names']]
+        keep = [i for (i, fn) in enumerate(names) if self.gs.expected[fn]['status'] == 0]
+        self.crops = sub['crops'][keep]                    # decoded sample meter_rect crops that read fine
+
+    @property
+    def crop_hw(self):
+        (x0, y0, x1, y1) = self.rect
+        return (y1 - y0, x1 - x0)
+
+    def macs_per_frame(self):
+        (ch, cw) = self.crop_hw
+        return (cw - TMPL_W + 1) * (ch - TMPL_H + 1) * TMPL_W * TMPL_H
+
+
+def planted_offsets(n, seed):
+    return np.random.default_rng(seed).integers(-6, 7, size=(n, 2))
+
+
+def make_frames_device(torch, wl, n, fh, fw, seed, device):
+    """(n, fh, fw, 3) u8 on the device: noise canvases, sample crops pasted at meter_rect +- 6 px."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed + 1)
+    frames = torch.empty((n, fh, fw, 3), dtype=torch.uint8, device=device)
+    chunk = max(1, (1 << 30) // (fh * fw * 3))
+    for a in range(0, n, chunk):
+        b = min(n, a + chunk)
+        frames[a:b] = torch.randint(0, 256, (b - a, fh, fw, 3), dtype=torch.uint8, device=device, generator=g)
+    d_crops = torch.from_numpy(np.ascontiguousarray(wl.crops)).to(device)
+    (x0, y0, x1, y1) = wl.rect
+    off = planted_offsets(n, seed)
+    for i in range(n):
+        (dx, dy) = (int(off[i][0]), int(off[i][1]))
+        frames[i, y0 + dy:y1 + dy, x0 + dx:x1 + dx] = d_crops[i % len(wl.crops)]
+    return frames
+
+
+def make_crops_host(wl, n, seed):
+    """What the meter_rect window of make_frames_device-style frames looks like, built on the host
+    for the reference arm (noise + the jittered sample crop, cut to meter_rect)."""
+    rng = np.random.default_rng(seed + 1)
+    (ch, cw) = wl.crop_hw
+    pad = 6
+    out = np.empty((n, ch, cw, 3), np.uint8)
+    off = planted_offsets(n, seed)
+    for i in range(n):
+        canvas = rng.integers(0, 256, size=(ch + 2 * pad, cw + 2 * pad, 3), dtype=np.uint8)
+        (dx, dy) = off[i]
+        canvas[pad + dy:pad + dy + ch, pad + dx:pad + dx + cw] = wl.crops[i % len(wl.crops)]
+        out[i] = canvas[pad:pad + ch, pad:pad + cw]
+    return out
+
+
+def port_read(wl, crops, n_threads):
+    """The C port of the reference (oracle/melf_oracle.c) over meter_rect crops; (records, seconds)."""
+    import oracle
+    O = wl.gs.oracle_params()
+    t0 = time.perf_counter()
+    res = oracle.read_batch(O, crops, n_threads=n_threads)
+    return (res, time.perf_counter() - t0)
+
+
+def records_differ(a, b, n_dials):
+    return not (a['status'] == b['status'] and a['match_x'] == b['match_x'] and a['match_y'] == b['match_y']
+                and a['failed_dial'] == b['failed_dial'] and a['unreadable_mask'] == b['unreadable_mask']
+                and np.array_equal(a['dial_pos'][:n_dials], b['dial_pos'][:n_dials], equal_nan=True)
+                and (a['value'] == b['value'] or (a['value'] != a['value'] and b['value'] != b['value'])))
+
+
+class Dist:
+    """The little of torch.distributed the bench needs (identity at N=1)."""
+
+    def __init__(self, torch, device):
+        import torch.distributed as dist
+        self.torch, self.dist, self.device = torch, dist, device
+        self.rank = int(os.environ.get('RANK', '0'))
+        self.world = int(os.environ.get('WORLD_SIZE', '1'))
+        if self.world > 1:
+            os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')   # NCCL's banner goes to stdout by default
+            dist.init_process_group('nccl', device_id=device)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, value, op='max'):
+        t = self.torch.tensor([float(value)], dtype=self.torch.float64, device=self.device)
+        if self.world > 1:
+            self.dist.all_reduce(t, op={'max': self.dist.ReduceOp.MAX, 'sum': self.dist.ReduceOp.SUM,
+                                        'min': self.dist.ReduceOp.MIN}[op])
+        return float(t.item())
+
+    def all_values(self, value):
+        """One float from every rank, in rank order (on every rank)."""
+        t = self.torch.zeros(self.world, dtype=self.torch.float64, device=self.device)
+        t[self.rank] = float(value)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return [float(v) for v in t.cpu()]
+
+    def gather(self, arr):
+        """Rank-ordered concatenation of equal-length host arrays on rank 0 (None elsewhere):
+        the product's own host-side gather, ``_sharding.gather_records``."""
+        from meterelf_b200 import _sharding
+        return _sharding.gather_records(arr, self.world * len(arr), dst=0)
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+# one workload on the GPUs: device-resident steps, per-kernel times, end to end, per-rank check
+# ---------------------------------------------------------------------------------------------
+def measure_workload(torch, D, wl, fh, fw, n, steps, warmup, min_seconds, local, e2e_frames, check_frames,
+                     want_kernels=True):
+    """n frames of fw x fh per GPU.  Returns (summary dict for rank 0, device frames, last records)."""
+    from meterelf_b200 import _engine
+    eng = wl.engine
+    device = D.device
+    d_frames = make_frames_device(torch, wl, n, fh, fw, 1234 + D.rank, device)
+    d_out = torch.zeros((n, _engine.RESULT_DTYPE.itemsize), dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream()
+    (row_stride, frame_stride) = (fw * 3, fh * fw * 3)
+
+    def step():
+        eng.read_device(d_frames.data_ptr(), n, fh, fw, row_stride, frame_stride, d_out.data_ptr(), stream.cuda_stream)
+
+    def timed(k):
+        """k steps between two events, barrier + synchronize on both sides; max over ranks, ms."""
+        D.barrier()
+        sampler = start_clock_sampler(local) if D.rank == 0 else None
+        launches0 = _engine.launch_count()
+        (e0, e1) = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        e0.record(stream)
+        for _ in range(k):
+            step()
+        e1.record(stream)
+        D.barrier()
+        ms = D.reduce(e0.elapsed_time(e1), 'max')
+        return (ms, _engine.launch_count() - launches0, sampler.stop() if sampler else None)
+
+    for _ in range(max(warmup, 3)):
+        step()
+    (burst_ms, burst_launches, burst_clocks) = timed(steps)
+    # the headline is the sustained number: keep stepping until the timed region is min_seconds long
+    k2 = max(steps, int(math.ceil(min_seconds * 1e3 / max(burst_ms / steps, 1e-3))))
+    k2 = int(D.reduce(k2, 'max'))
+    (sus_ms, sus_launches, sus_clocks) = timed(k2)
+    res = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n).copy()
+
+    out = {
+        'frames_per_gpu': n, 'frame_w': fw, 'frame_h': fh, 'steps': k2, 'ms_per_step': sus_ms / k2,
+        'value': D.world * n * k2 / (sus_ms / 1e3), 'timed_region_s': sus_ms / 1e3, 'clocks': sus_clocks,
+        'gpu_launches': int(sus_launches),
+        'burst': {'steps': steps, 'ms_per_step': burst_ms / steps, 'value': D.world * n * steps / (burst_ms / 1e3),
+                  'clocks': burst_clocks, 'gpu_launches': int(burst_launches)},
     }
-    emit(line)
+
+    # ---- per-kernel durations: the same steps again with CUDA events around every launch ------
+    if want_kernels:
+        ksteps = max(3, min(steps, 20))
+        eng.profile_enable(True)
+        for _ in range(ksteps):
+            step()
+        prof = eng.profile_read()
+        eng.profile_enable(False)
+        out['kernel_ms_per_step'] = {k: (v[0] / ksteps) for (k, v) in prof.items() if v[1]}
+        out['kernel_launches_per_step'] = {k: v[1] // ksteps for (k, v) in prof.items() if v[1]}
+
+    # ---- end to end through the host API: pinned host frames in, host records out --------------
+    if e2e_frames:
+        n_e2e = min(n, e2e_frames)
+        h_frames = torch.empty((n_e2e, fh, fw, 3), dtype=torch.uint8).pin_memory()
+        h_frames.copy_(d_frames[:n_e2e])
+        h_np = h_frames.numpy()
+        eng.read_frames(h_np[:64])
+        esteps = max(2, min(steps, 10))
+        D.barrier()
+        t0 = time.perf_counter()
+        for _ in range(esteps):
+            h_res = eng.read_frames(h_np)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        (ch, cw) = wl.crop_hw
+        h2d = int(n_e2e * ch * cw * 3)
+        rates = D.all_values(h2d * esteps / dt / 1e9)
+        out['e2e'] = {'value': D.world * n_e2e * esteps / D.reduce(dt, 'max'), 'unit': UNIT,
+                      'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': int(n_e2e * _engine.RESULT_DTYPE.itemsize),
+                      'frames_per_step': n_e2e, 'steps': esteps, 'h2d_gbs_per_rank': [round(r, 2) for r in rates],
+                      'route': 'melf_read_batch: page-locked host BGR frames, only the meter_rect rows cross PCIe'}
+        same = int(np.array_equal(h_res['status'], res['status'][:n_e2e]) and
+                   h_res['dial_pos'].tobytes() == res['dial_pos'][:n_e2e].tobytes())
+        out['e2e']['records_equal_device_path_all_ranks'] = bool(D.reduce(same, 'min'))
+        del h_frames
+
+    # ---- every rank's records against the CPU port on a sample of that rank's own frames -------
+    k = min(n, check_frames)
+    (x0, y0, x1, y1) = wl.rect
+    crops = np.ascontiguousarray(d_frames[:k, y0:y1, x0:x1].cpu().numpy())
+    g_crops = D.gather(crops.reshape(k, -1).view(np.dtype((np.void, crops[0].size))).reshape(k))
+    g_recs = D.gather(res[:k].copy())
+    ok = D.all_values(int(np.sum(res['status'] == 0)))
+    if D.rank == 0:
+        (ch, cw) = wl.crop_hw
+        all_crops = np.frombuffer(g_crops.tobytes(), np.uint8).reshape(D.world * k, ch, cw, 3)
+        cores = len(os.sched_getaffinity(0))
+        (port, port_dt) = port_read(wl, all_crops, cores)
+        mism = [sum(records_differ(g_recs[r * k + i], port[r * k + i], len(wl.names)) for i in range(k))
+                for r in range(D.world)]
+        out['check'] = {'frames_read_ok_per_rank': [int(v) for v in ok], 'frames_per_rank': n,
+                        'checked_per_rank': k, 'mismatches_vs_port_per_rank': mism,
+                        'how': 'records and input crops of every rank gathered on rank 0 (_sharding.gather_records)'}
+        out['_port'] = {'value': D.world * k / port_dt, 'cores': cores, 'frames': D.world * k}
+        out['_crops_all'] = all_crops
+        out['_recs_all'] = g_recs
+    return (out, d_frames, res)
 
 
-def load_traffic():
-    """dram__bytes_read + dram__bytes_write per launch from the committed ncu capture
-    (tools/ncu_summary.py traffic ... > profiles/r01_traffic.json); None when absent."""
-    path = os.path.join(ROOT, 'profiles', 'r01_traffic.json')
-    if os.path.exists(path):
-        with open(path) as fp:
-            return json.load(fp)
-    return {}
-
-
-def ingest_leg(torch, eng, gs, n_streams, reps=3):
-    """SURVEY 8f-1, reported beside the headline: the reference's real input is JPEG files, so this
-    leg times melf_read_jpeg_batch -- host JPEG bytes in (page-locked), host readings out, decode
-    bit-identical to cv2.imread on the GPU -- over the portrait sample files of set 1 repeated to
-    n_streams, and checks every reading against the reference's golden line."""
+def ingest_leg(torch, D, wl, n_streams, reps=3):
+    """SURVEY 8f-1, at every N: the reference's real input is JPEG files, so this leg times
+    melf_read_jpeg_batch -- host JPEG bytes in (page-locked), host records out, decode bit-identical
+    to cv2.imread on the GPU -- over the portrait sample files of set 1 repeated to n_streams per GPU,
+    and checks every rank's readings against the reference's golden lines."""
     from helpers import GOLDEN, format_result_line
     from test_jpeg_oracle import load_streams
     from meterelf_b200 import _engine
+    eng = wl.engine
     full = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
     streams = load_streams(full if os.path.exists(full) else os.path.join(GOLDEN, 'jpeg_subset.npz'))
     base = [s for s in streams if s[4] == 1 and s[2] == (640, 480)]
-    data = [base[i % len(base)][1] for i in range(n_streams)]
+    shift = D.rank * 7                                   # every rank reads the files in another order
+    data = [base[(i + shift) % len(base)][1] for i in range(n_streams)]
     (blob, offsets) = _engine.pack_streams(data)
     blob_p = torch.from_numpy(blob.copy()).pin_memory().numpy()
     results = np.zeros((n_streams,), _engine.RESULT_DTYPE)
@@ -298,6 +427,7 @@ def ingest_leg(torch, eng, gs, n_streams, reps=3):
     for _ in range(2):
         call()
     launches0 = _engine.launch_count()
+    D.barrier()
     t0 = time.perf_counter()
     for _ in range(reps):
         call()
@@ -305,253 +435,356 @@ def ingest_leg(torch, eng, gs, n_streams, reps=3):
     launches = (_engine.launch_count() - launches0) // reps
     bad = 0
     for i in range(len(base)):
-        exp = gs.expected[base[i][0]]
-        got = format_result_line(results[i], gs.names)
-        bad += (got != exp['line']) if exp['status'] == 0 else (got.split(' (match val')[0] != exp['line'].split(' (match val')[0])
+        exp = wl.gs.expected[base[(i + shift) % len(base)][0]]
+        got = format_result_line(results[i], wl.names)
+        bad += (got != exp['line']) if exp['status'] == 0 else (
+            got.split(' (match val')[0] != exp['line'].split(' (match val')[0])
+    rates = D.all_values(float(offsets[-1]) / dt / 1e9)
+    bad_all = D.all_values(bad)
     return {'metric': 'meter readings/sec from JPEG bytes (480x640 4:2:0 files, %.1f KB avg)' % (int(offsets[-1]) / n_streams / 1024),
-            'value': n_streams / dt, 'unit': UNIT, 'streams_per_step': n_streams, 'steps': reps,
-            'ms_per_step': dt * 1e3, 'h2d_bytes_per_step': int(offsets[-1]),
+            'value': D.world * n_streams / D.reduce(dt, 'max'), 'unit': UNIT, 'streams_per_gpu': n_streams, 'steps': reps,
+            'ms_per_step': D.reduce(dt, 'max') * 1e3, 'h2d_bytes_per_step': int(offsets[-1]),
             'd2h_bytes_per_step': int(results.nbytes), 'gpu_launches_per_step': int(launches),
-            'golden_lines_checked': len(base), 'golden_line_mismatches': int(bad),
-            'note': 'melf_read_jpeg_batch: header walk on the host, Huffman / IDCT / upsampling / colour on the '
-                    'GPU (bit-identical to cv2.imread), then the same locate and dial kernels; GPU-bound '
-                    '(Huffman stage), see DESIGN.md section 8'}
+            'h2d_gbs_per_rank': [round(r, 2) for r in rates],
+            'golden_lines_checked_per_rank': len(base), 'golden_line_mismatches_per_rank': [int(b) for b in bad_all],
+            'route': 'melf_read_jpeg_batch (the default route of get_meter_values for baseline JPEG files): header walk '
+                     'on the host, Huffman / IDCT / upsampling / colour on the GPU (bit-identical to cv2.imread), '
+                     'then the same locate and dial kernels; GPU-bound (Huffman stage), DESIGN.md section 8'}
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    from helpers import golden_set
+def convert_stage(torch, wl, d_frames, fh, fw, steps, local, peaks, traffic):
+    """Stage 1 as a standalone fused pass over full frames (north_star's >= 50 % of HBM target)."""
     from meterelf_b200 import _engine
-
-    rank = int(os.environ.get('RANK', '0'))
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    local = int(os.environ.get('LOCAL_RANK', '0'))
-    if not torch.cuda.is_available():
-        raise _engine.EngineUnavailableError('bench needs a CUDA device; there is no CPU fallback')
-    torch.cuda.set_device(local)
-    device = torch.device('cuda', local)
-    if world > 1:
-        # NCCL's version banner goes to stdout by default; stdout carries exactly one JSON line
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
-        dist.init_process_group('nccl', device_id=device)
-
-    gs = golden_set(1)
-    crops = valid_crops(gs)
-    n = args.frames
-    seed = 1234 + rank
-    eng = gs.engine(cropped_input=False, device=local)
-    d_frames = make_frames_device(torch, gs, crops, n, seed, device)
-    d_out = torch.zeros((n, _engine.RESULT_DTYPE.itemsize), dtype=torch.uint8, device=device)
+    nconv = min(len(d_frames), 1024)
+    device = d_frames.device
     stream = torch.cuda.current_stream()
-    row_stride, frame_stride = FRAME_W * 3, FRAME_H * FRAME_W * 3
-
-    def step():
-        eng.read_device(d_frames.data_ptr(), n, FRAME_H, FRAME_W, row_stride, frame_stride,
-                        d_out.data_ptr(), stream.cuda_stream)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    warmup = max(args.warmup, 3)
-    for _ in range(warmup):
-        step()
-    barrier()
-    sampler = start_clock_sampler(local) if rank == 0 else None
-    launches0 = _engine.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(stream)
-    for _ in range(args.steps):
-        step()
-    ev1.record(stream)
-    barrier()
-    launches = _engine.launch_count() - launches0
-    ms = ev0.elapsed_time(ev1)
-    t = torch.tensor([ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    value = world * n * args.steps / (ms_total / 1e3)
-
-    # ---- correctness spot check of the timed output (not timed) ------------------------
-    res = d_out.cpu().numpy().view(_engine.RESULT_DTYPE).reshape(n)
-    n_ok = int(np.sum(res['status'] == 0))
-
-    # ---- per-kernel durations: the same steps again with CUDA events around every launch --
-    ksteps = max(3, min(args.steps, 20))
-    eng.profile_enable(True)
-    for _ in range(ksteps):
-        step()
-    prof = eng.profile_read()
-    eng.profile_enable(False)
-    kernel_ms = {k: (v[0] / ksteps) for (k, v) in prof.items() if v[1]}
-    kernel_launches = {k: v[1] // ksteps for (k, v) in prof.items() if v[1]}
-
-    # ---- stage 1 as a standalone fused pass over the full frames (5 B/px) ---------------
-    nconv = min(n, 1024)
-    d_l = torch.empty((nconv, FRAME_H, FRAME_W), dtype=torch.uint8, device=device)
-    d_m = torch.empty((nconv, FRAME_H, FRAME_W), dtype=torch.uint8, device=device)
+    d_l = torch.empty((nconv, fh, fw), dtype=torch.uint8, device=device)
+    d_m = torch.empty((nconv, fh, fw), dtype=torch.uint8, device=device)
 
     def convert_only():
-        _engine.convert_hls_device(local, d_frames.data_ptr(), nconv, FRAME_H, FRAME_W, row_stride,
-                                   frame_stride, gs.hue_shift, True, 0, d_l.data_ptr(),
+        _engine.convert_hls_device(local, d_frames.data_ptr(), nconv, fh, fw, fw * 3, fh * fw * 3,
+                                   wl.gs.hue_shift, True, 0, d_l.data_ptr(),
                                    (116, 35, 95), (134, 125, 165), d_m.data_ptr(), stream.cuda_stream)
     for _ in range(3):
         convert_only()
     torch.cuda.synchronize()
-    csteps = max(5, min(args.steps, 50))
-    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    csteps = max(5, min(steps, 50))
+    (c0, c1) = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
     c0.record(stream)
     for _ in range(csteps):
         convert_only()
     c1.record(stream)
     torch.cuda.synchronize()
     conv_ms = c0.elapsed_time(c1) / csteps
-    clocks = sampler.stop() if sampler else None
-    del d_l, d_m
+    gbs = 5.0 * fh * fw * nconv / (conv_ms / 1e3) / 1e9
+    return {'kernel': 'melf_convert_tab_kernel (fused BGR->HLS + hue shift + L plane + mask, full frames)',
+            'bound': 'hbm', 'achieved': gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s', 'frac': gbs / peaks['hbm_gbs'],
+            'traffic': traffic.get('melf_convert_tab_kernel'), 'ms_per_launch': conv_ms,
+            'note': 'algorithmic 5 B/px x %d px; peak %s' % (fh * fw * nconv, peaks['source'])}
 
-    # ---- end to end through the public host API: pinned host frames in, results out -----
-    n_e2e = min(n, args.e2e_frames)
-    h_frames = torch.empty((n_e2e, FRAME_H, FRAME_W, 3), dtype=torch.uint8).pin_memory()
-    h_frames.copy_(d_frames[:n_e2e])
-    h_np = h_frames.numpy()
-    eng.read_frames(h_np[:64])
-    esteps = max(2, min(args.steps, 10))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(esteps):
-        h_res = eng.read_frames(h_np)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    te = torch.tensor([dt], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    (x0, y0, x1, y1) = gs.meter_rect
-    e2e = {'value': world * n_e2e * esteps / float(te.item()), 'unit': UNIT,
-           'h2d_bytes_per_step': int(n_e2e * (y1 - y0) * (x1 - x0) * 3),
-           'd2h_bytes_per_step': int(n_e2e * _engine.RESULT_DTYPE.itemsize),
-           'frames_per_step': n_e2e, 'steps': esteps,
-           'note': 'melf_read_batch: pinned host frames, only meter_rect rows cross PCIe '
-                   '(PCIe-bound: profiles/r01_pcie_probe.txt measures 50.4 GB/s for this copy shape)'}
-    assert np.array_equal(h_res['status'], res['status'][:n_e2e])
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+def micro_bench(torch, wl, local, int8_peak):
+    """BASELINE.json configs[4]: the 188x119 dial template against single-channel search windows of
+    growing size through melf_match_template (cv2.matchTemplate TM_CCOEFF + minMaxLoc semantics);
+    the small windows are checked against exact numpy int64 arithmetic."""
+    import oracle
+    eng = wl.engine
+    tmpl = np.ascontiguousarray(wl.gs.template)
+    (th, tw) = tmpl.shape
+    dev = torch.device('cuda', local)
+    g = torch.Generator(device=dev)
+    g.manual_seed(7)
+    rows = []
+    st = torch.cuda.current_stream()
+    for (w, h) in [(220, 135), (250, 250), (320, 240), (640, 480), (1280, 720)]:
+        n = max(8, min(4096, (2048 << 20) // (w * h)))
+        frames = torch.randint(0, 256, (n, h, w), dtype=torch.uint8, device=dev, generator=g)
+        frames[0, 3:3 + th, 5:5 + tw] = torch.from_numpy(tmpl).to(dev)
+        d_xy = torch.zeros((n, 2), dtype=torch.int32, device=dev)
+        d_val = torch.zeros((n,), dtype=torch.float32, device=dev)
 
-    # ---- CPU baseline (oracle port) on a bounded sample of the same frames -------------
-    cores = len(os.sched_getaffinity(0))
-    sample = min(n, args.cpu_frames)
-    host_sample = d_frames[:sample].cpu().numpy()
-    (cpu_res, cpu_dt) = cpu_arm(gs, host_sample, cores)
-    mism = 0
-    for i in range(sample):
-        a, b = res[i], cpu_res[i]
-        same = (a['status'] == b['status'] and a['match_x'] == b['match_x'] and
-                a['match_y'] == b['match_y'] and
-                np.array_equal(a['dial_pos'][:4], b['dial_pos'][:4], equal_nan=True))
-        mism += 0 if same else 1
+        def run():
+            eng.match_template_device(frames.data_ptr(), 1, n, h, w, w, h * w, False,
+                                      d_xy.data_ptr(), d_val.data_ptr(), 0, st.cuda_stream)
+        for _ in range(3):
+            run()
+        torch.cuda.synchronize()
+        ok = (int(d_xy[0, 0]), int(d_xy[0, 1])) == (5, 3)
+        if w * h <= 320 * 240:                          # the CPU port's exact integer arg-max
+            (mx, my, mv, _map) = oracle.match_template(frames[1].cpu().numpy(), tmpl, want_map=False)
+            ok = ok and (int(d_xy[1, 0]), int(d_xy[1, 1]), float(d_val[1])) == (mx, my, float(mv))
+        (e0, e1) = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        reps = 10
+        e0.record(st)
+        for _ in range(reps):
+            run()
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        pos = (w - tw + 1) * (h - th + 1)
+        tops = 2.0 * pos * tw * th * n / (ms / 1e3) / 1e12
+        rows.append({'window': '%dx%d' % (w, h), 'result_map': '%dx%d' % (w - tw + 1, h - th + 1), 'frames': n,
+                     'ms_per_batch': ms, 'frames_per_s': n / (ms / 1e3), 'algorithmic_tops': tops,
+                     'frac_of_int8_peak': tops / int8_peak, 'argmax_check': bool(ok)})
+        del frames
+    return {'what': 'template-correlation micro-bench: 188x119 template, window-size sweep (configs[4])',
+            'int8_peak_tops': int8_peak, 'rows': rows}
 
+
+def sharded_check(D, wl):
+    """The product's multi-GPU path with the real Engine on every GPU: the SAME global batch on every
+    rank, _sharding.read_frames_sharded reads the rank's slice and gathers; rank 0 compares all of it
+    with the CPU port."""
+    from meterelf_b200 import _reading, _sharding
+    eng = _reading.get_engine(wl.params, cropped_input=True, device=D.device.index)
+    crops = np.ascontiguousarray(np.concatenate([wl.crops] * 4)[:16 * D.world + 3])
+    got = _sharding.read_frames_sharded(eng.read_frames, crops, dst=0)
+    if D.rank != 0:
+        return None
+    (want, _dt) = port_read(wl, crops, 4)
+    bounds = _sharding.shard_bounds(len(crops), D.world)
+    return {'frames': len(crops), 'how': '_sharding.read_frames_sharded(Engine.read_frames, frames), gather on rank 0',
+            'mismatches_vs_port_per_rank': [
+                sum(records_differ(got[i], want[i], len(wl.names)) for i in range(a, b)) for (a, b) in bounds]}
+
+
+def reference_pool_run(wl, crops, cores, runs=1):
+    """The UNMODIFIED reference (oracle/_ref, one process per core) over meter_rect crops:
+    (frames/s, records) or (None, None) when oracle/_ref is absent."""
+    import oracle
+    if not oracle.ref_available():
+        return (None, None)
+    with oracle.RefPool(wl.params_file, crops, cores) as pool:
+        walls = []
+        for _ in range(runs):
+            (wall, recs) = pool.run()
+            walls.append(wall)
+    return (len(crops) / (sum(walls) / len(walls)), recs)
+
+
+def workload_config(wl, fw, fh, n, world, total=None):
+    (ch, cw) = wl.crop_hw
+    return {
+        'workload': 'synthetic %dx%d (w x h) BGR batch of %d frames per GPU%s, S-planted sample meter crops '
+                    '(sample-images%d params, meter_rect %dx%d, template %dx%d)'
+                    % (fw, fh, n, (' (%d in total, strong-scaled)' % total) if total else '', wl.gs.set_no, cw, ch,
+                       TMPL_W, TMPL_H),
+        'frames_per_gpu': n, 'frame_h': fh, 'frame_w': fw, 'bytes_per_frame': fh * fw * 3,
+        'l2': 'batch (%.2f GB per GPU) is larger than L2; no flush between steps' % (n * fh * fw * 3 / 1e9),
+        'parallelism': 'frames sharded by index, one process per GPU (%d), host-side gather of records' % world,
+        'params': 'params.yml + template file -> _params.load -> _reading.get_engine',
+    }
+
+
+def locate_roofline(wl, km, n, step_ms, peaks, traffic, sustained):
+    """Roofline object of the dominant kernel (tensor-bound)."""
+    tc_ms = km.get('match_tc')
+    if not tc_ms:
+        return None
+    macs = wl.macs_per_frame()
+    tops = 2.0 * macs * n / (tc_ms / 1e3) / 1e12
+    peak_burst = 2.0 * peaks['bf16_tflops']
+    peak_sus = 2.0 * peaks['bf16_tflops_sustained']
+    (ch, cw) = wl.crop_hw
+    crop_bytes = ch * cw * 3 * n
+    name = os.environ.get('MELF_MATCH_KERNEL_NAME', 'melf_match_fused_ov_kernel')
+    return {
+        'kernel': name + ' (BGR crop -> lightness + window sums in the shadow of the MMAs, drain under the next '
+                         'pass; TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
+        'bound': 'tensor', 'achieved': tops, 'peak': peak_burst, 'unit': 'TOP/s', 'frac': tops / peak_burst,
+        'traffic': traffic.get(name), 'ms_per_launch': tc_ms,
+        'peak_sustained': peak_sus, 'frac_of_sustained_peak': tops / peak_sus,
+        'peak_int8_issue_rate': 8192 * 2 * 148 * 1.965e9 / 1e12,
+        'frac_of_int8_issue_rate': tops / (8192 * 2 * 148 * 1.965e9 / 1e12),
+        'hbm_view': {'algorithmic_bytes': crop_bytes, 'achieved_gbs': crop_bytes / (tc_ms / 1e3) / 1e9,
+                     'frac_of_hbm_peak': crop_bytes / (tc_ms / 1e3) / 1e9 / peaks['hbm_gbs']},
+        'note': 'algorithmic 2*%d op/frame x %d frames per launch (SURVEY 8d: result positions x 22372 MAC); '
+                'ms_per_launch = CUDA events around the launch on its own stream, kernels timed alone after the %s '
+                'run; peak = 2 x %s cuBLAS bf16 dense (burst; int8:bf16 tensor ratio), peak_sustained = 2 x the '
+                'sustained figure, peak_int8_issue_rate = 8192 MAC/clk/SM x 148 SMs x 1965 MHz; kernel share of '
+                'step %.2f' % (macs, n, 'sustained' if sustained else 'burst', peaks['source'], tc_ms / step_ms),
+    }
+
+
+def run_ours(args):
+    import torch
+    from meterelf_b200 import _engine
+
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise _engine.EngineUnavailableError('bench needs a CUDA device; there is no CPU fallback')
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    affinity = bind_to_gpu_cpus(local)
+    D = Dist(torch, device)
+    tmp = tempfile.TemporaryDirectory()
     peaks = load_peaks()
     traffic = load_traffic()
-    step_ms = ms_total / args.steps
-    rw, rh = 250 - 188 + 1, 250 - 119 + 1
-    macs = rw * rh * 188 * 119
-    tc_ms = kernel_ms.get('match_tc')
+    wl = Workload(1, tmp.name, local)
+    (fh, fw, n) = (640, 480, args.frames)      # the sample frames are portrait: 480 wide x 640 tall
+
+    (head, d_frames, res) = measure_workload(torch, D, wl, fh, fw, n, args.steps, args.warmup, args.min_seconds,
+                                             local, args.e2e_frames, args.check_frames)
+    stage = [convert_stage(torch, wl, d_frames, fh, fw, args.steps, local, peaks, traffic)]
+
+    # ---- CPU baseline on rank 0: the unmodified reference, one process per core, + the C port ------
+    cpu = None
+    if D.rank == 0:
+        import oracle
+        cores = len(os.sched_getaffinity(0))
+        k = head['check']['checked_per_rank']
+        sample = min(n, max(cores * args.cpu_frames_per_core, k))
+        (x0, y0, x1, y1) = wl.rect
+        crops0 = np.ascontiguousarray(d_frames[:sample, y0:y1, x0:x1].cpu().numpy())
+        crops_all = np.concatenate([crops0, head['_crops_all'][k:]])         # + the other ranks' check frames
+        recs_all = np.concatenate([res[:sample], head['_recs_all'][k:]])
+        (ref_fps, ref_recs) = reference_pool_run(wl, crops_all, cores)
+        (port, port_dt) = port_read(wl, crops_all, cores)
+        port_fps = len(crops_all) / port_dt
+        cpu = {'value': ref_fps if ref_fps else port_fps, 'unit': UNIT, 'cores': cores,
+               'kind': 'reference' if ref_fps else 'port',
+               'sample': '%d frames: the first %d of rank 0\'s batch + %d check frames of every other rank'
+                         % (len(crops_all), sample, k),
+               'what': 'unmodified reference package (oracle/_ref), ImageFile(name, params, bgr_image=crop) -> '
+                       'get_meter_value, one process per core, cv2 single-threaded' if ref_fps else
+                       'oracle/_ref absent: C port of the reference (oracle/melf_oracle.c), one thread per core',
+               'port': {'value': port_fps, 'unit': UNIT, 'cores': cores, 'kind': 'port'},
+               'mismatches_vs_gpu': (oracle.ref_mismatches(ref_recs, recs_all, len(wl.names)) if ref_recs else
+                                     sum(records_differ(a, b, len(wl.names)) for (a, b) in zip(recs_all, port))),
+               'port_mismatches_vs_gpu': sum(records_differ(a, b, len(wl.names)) for (a, b) in zip(recs_all, port))}
+    del d_frames
+    torch.cuda.empty_cache()
+
+    ingest = ingest_leg(torch, D, wl, args.ingest_streams) if args.ingest_streams > 0 else None
+    shard = sharded_check(D, wl)
+
+    # ---- BASELINE.json configs[3]: 1280x720, 32768 frames in total over the GPUs (strong scaling) ----
+    c3 = None
+    if args.config3_frames > 0:
+        n3 = max(1, args.config3_frames // D.world)
+        (c3, d3, _r3) = measure_workload(torch, D, wl, 720, 1280, n3, max(3, min(args.steps, 10)), 3,
+                                         min(args.min_seconds, 1.0), local, min(args.e2e_frames, 2048), 32)
+        del d3
+        torch.cuda.empty_cache()
+
+    # ---- the second sample geometry (220x135 meter_rect, 33x17 result map) ---------------------------
+    wl2 = Workload(2, tmp.name, local)
+    (s2, d2, _r2) = measure_workload(torch, D, wl2, fh, fw, n, args.steps, 3, min(args.min_seconds, 0.5), local, 0, 64)
+    del d2
+    torch.cuda.empty_cache()
+
+    if D.rank != 0:
+        D.close()
+        return
+
+    def public(d):
+        return {k: v for (k, v) in d.items() if not k.startswith('_')}
+
+    km = head['kernel_ms_per_step']
+    step_ms = head['ms_per_step']
+    roofline = locate_roofline(wl, km, n, step_ms, peaks, traffic, True)
+    if km.get('dials'):
+        stage.append({'kernel': 'melf_dials_kernel (per-dial masks, contour selection, angles, value)',
+                      'bound': 'issue/latency (SURVEY 8d stage 3)', 'ms_per_launch': km['dials'],
+                      'frames_per_s': n / (km['dials'] / 1e3), 'traffic': traffic.get('melf_dials_kernel'),
+                      'note': 'timed alone; share of the sum of kernel times %.2f' % (km['dials'] / sum(km.values()))})
     int8_peak = 2.0 * peaks['bf16_tflops']
-    fused = not kernel_ms.get('match_prep')
-    overlap = os.environ.get('MELF_MATCH_OVERLAP', '1') not in ('0', '')
-    tc_name = ('melf_match_fused_ov_kernel' if overlap else 'melf_match_fused_kernel') if fused else 'melf_match_tc_kernel'
-    if tc_ms:
-        tops = 2.0 * macs * n / (tc_ms / 1e3) / 1e12
-        crop_bytes = 250 * 250 * 3 * n
-        roofline = {
-            'kernel': tc_name + (' (BGR crop -> lightness + window sums in the shadow of the MMAs, drain under the next pass; ' if fused else ' (') +
-                      'TM_CCOEFF on tcgen05 kind::i8, exact integer correlation + arg-max)',
-            'bound': 'tensor', 'achieved': tops, 'peak': int8_peak, 'unit': 'TOP/s',
-            'frac': tops / int8_peak, 'traffic': traffic.get(tc_name),
-            'ms_per_launch': tc_ms,
-            'hbm_view': {'algorithmic_bytes': crop_bytes, 'achieved_gbs': crop_bytes / (tc_ms / 1e3) / 1e9,
-                         'frac_of_hbm_peak': crop_bytes / (tc_ms / 1e3) / 1e9 / peaks['hbm_gbs'],
-                         'note': 'the only DRAM traffic of the fused kernel is one read of the meter_rect crop '
-                                 '(187500 B/frame); it is far from HBM-bound'} if fused else None,
-            'note': 'algorithmic 2*%d op/frame x %d frames per launch (SURVEY 8d: 63x132 positions x 22372 MAC); '
-                    'peak = 2 x %s bf16 dense (int8:bf16 tensor ratio); issued MACs are 1.50x the algorithmic '
-                    'ones (K 188->256, N 133->144, M 63->64); kernel share of step %.2f'
-                    % (macs, n, peaks['source'], tc_ms / step_ms),
-        }
-    else:
-        roofline = None
-    conv_bytes = 5.0 * FRAME_H * FRAME_W * nconv
-    conv_gbs = conv_bytes / (conv_ms / 1e3) / 1e9
-    stage = [{
-        'kernel': 'melf_convert_tab_kernel (fused BGR->HLS + hue shift + L plane + mask, full frames)',
-        'bound': 'hbm', 'achieved': conv_gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
-        'frac': conv_gbs / peaks['hbm_gbs'], 'traffic': traffic.get('melf_convert_tab_kernel'),
-        'ms_per_launch': conv_ms,
-        'note': 'algorithmic 5 B/px x %d px; peak %s' % (FRAME_H * FRAME_W * nconv, peaks['source'])}]
-    if kernel_ms.get('match_prep'):
-        prep_bytes = n * (250 * 250 * 3 + 67584 + 64 * 144 * 4)
-        gbs = prep_bytes / (kernel_ms['match_prep'] / 1e3) / 1e9
-        stage.append({
-            'kernel': 'melf_match_prep_kernel (meter_rect BGR -> lightness slab + window sums)',
-            'bound': 'hbm', 'achieved': gbs, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
-            'frac': gbs / peaks['hbm_gbs'], 'traffic': traffic.get('melf_match_prep_kernel'),
-            'ms_per_launch': kernel_ms['match_prep'],
-            'note': 'algorithmic 187500 B in + 67584 + 36864 B out per frame; share of step %.2f'
-                    % (kernel_ms['match_prep'] / step_ms)})
-    if kernel_ms.get('dials'):
-        stage.append({
-            'kernel': 'melf_dials_kernel (per-dial masks, contour selection, angles, value)',
-            'bound': 'issue/latency (SURVEY 8d stage 3)', 'ms_per_launch': kernel_ms['dials'],
-            'frames_per_s': n / (kernel_ms['dials'] / 1e3),
-            'traffic': traffic.get('melf_dials_kernel'),
-            'note': 'share of step %.2f' % (kernel_ms['dials'] / step_ms)})
     line = {
-        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-        'warmup': warmup, 'ms_per_step': step_ms,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'metric': METRIC, 'value': head['value'], 'unit': UNIT, 'n_gpus': D.world, 'steps': head['steps'],
+        'steps_requested': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': step_ms,
+        'timed_region_s': head['timed_region_s'], 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'u8/int32 (correlation), f32 (HLS), f64 (angles)', 'data': 'synthetic',
-        'config': workload_config(n),
-        'e2e': e2e, 'gpu_launches': int(launches), 'clocks': clocks,
-        'roofline': roofline, 'stage_rooflines': stage,
-        'kernel_ms_per_step': kernel_ms, 'kernel_launches_per_step': kernel_launches,
-        'cpu_baseline': {'value': sample / cpu_dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                         'sample': '%d frames of the same batch' % sample,
-                         'mismatches_vs_gpu': mism},
-        'check': {'frames_read_ok': n_ok, 'frames': n},
+        'config': workload_config(wl, fw, fh, n, D.world),
+        'e2e': head.get('e2e'), 'gpu_launches': head['gpu_launches'], 'clocks': head['clocks'],
+        'burst': head['burst'], 'roofline': roofline, 'stage_rooflines': stage,
+        'kernel_ms_per_step': km, 'kernel_launches_per_step': head['kernel_launches_per_step'],
+        'cpu_baseline': cpu, 'check': head['check'], 'sharded_check': shard, 'ingest': ingest,
+        'affinity': affinity,
+        'note': 'value = sustained: the timed region is max(--steps, --min-seconds worth of) steps; burst = exactly '
+                '--steps steps, timed first',
     }
-    if world == 1 and args.ingest_streams > 0 and (FRAME_H, FRAME_W) == (640, 480):
-        line['ingest'] = ingest_leg(torch, eng, gs, args.ingest_streams)
+    if c3:
+        c3p = public(c3)
+        c3p['config'] = workload_config(wl, 1280, 720, c3['frames_per_gpu'], D.world, args.config3_frames)
+        c3p.update(metric='meter readings/sec (1280x720 frames)', unit=UNIT, scaling='strong')
+        c3p['roofline'] = locate_roofline(wl, c3['kernel_ms_per_step'], c3['frames_per_gpu'], c3['ms_per_step'],
+                                          peaks, traffic, True)
+        line['config3'] = c3p
+    s2p = public(s2)
+    s2p['config'] = workload_config(wl2, fw, fh, n, D.world)
+    s2p['roofline'] = locate_roofline(wl2, s2['kernel_ms_per_step'], n, s2['ms_per_step'], peaks, traffic, True)
+    line['set2'] = s2p
+    if D.world == 1 and args.micro_bench:
+        line['micro_bench'] = micro_bench(torch, wl, local, int8_peak)
     emit(line)
-    if world > 1:
-        dist.destroy_process_group()
+    D.close()
+    tmp.cleanup()
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path on all host cores -- the
+    unmodified reference package from oracle/_ref (vendored by __graft_entry__.build()), one process
+    per core, each step a bounded sample of the workload (cores x 64 meter_rect crops of S-planted
+    frames).  Falls back to the C port only when oracle/_ref is absent."""
+    if int(os.environ.get('RANK', '0')) != 0:
+        return
+    import oracle
+    tmp = tempfile.TemporaryDirectory()
+    wl = Workload(1, tmp.name, None)
+    cores = len(os.sched_getaffinity(0))
+    sample = max(cores * args.cpu_frames_per_core, 64)
+    crops = make_crops_host(wl, sample, seed=1234)
+    times = []
+    kind = 'reference' if oracle.ref_available() else 'port'
+    if kind == 'reference':
+        with oracle.RefPool(wl.params_file, crops, cores) as pool:
+            for i in range(args.warmup + args.steps):
+                (wall, recs) = pool.run(want_results=(i == 0))
+                if i == 0:
+                    (port, _dt) = port_read(wl, crops, cores)
+                    bad = oracle.ref_mismatches(recs, port, len(wl.names))
+                if i >= args.warmup:
+                    times.append(wall)
+    else:
+        bad = None
+        for i in range(args.warmup + args.steps):
+            (_res, dt) = port_read(wl, crops, cores)
+            if i >= args.warmup:
+                times.append(dt)
+    total = sum(times)
+    value = sample * len(times) / total
+    cfg = workload_config(wl, 480, 640, args.frames, args.gpus)
+    cfg['params'] = 'params.yml + template file -> the reference\'s own _params.load'
+    cfg['timed_per_step'] = '%d frames (cores x %d), the meter_rect crops of such frames' % (sample, args.cpu_frames_per_core)
+    emit({
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * total / len(times),
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8/f32/f64 (OpenCV)',
+        'data': 'synthetic', 'config': cfg,
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': kind,
+                         'sample': '%d frames per step' % sample, 'port_mismatches_vs_reference': bad},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    })
+    tmp.cleanup()
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--size', default='480x640', help='frame size WxH (sample frames are 480x640; '
-                    'BASELINE.json also names 1280x720)')
-    ap.add_argument('--frames', type=int, default=0, help='frames per GPU (default 4096; '
-                    '32768 / n_gpus for 1280x720)')
+    ap.add_argument('--min-seconds', type=float, default=2.0,
+                    help='the headline loops until its timed region is this long (sustained clocks)')
+    ap.add_argument('--frames', type=int, default=4096, help='640x480 frames per GPU')
+    ap.add_argument('--config3-frames', type=int, default=32768, help='1280x720 frames in total (0 = skip)')
     ap.add_argument('--e2e-frames', type=int, default=4096)
-    ap.add_argument('--cpu-frames', type=int, default=8192, help='CPU baseline sample (frames)')
-    ap.add_argument('--ingest-streams', type=int, default=32768,
-                    help='JPEG streams per step of the ingest leg (N=1 only; 0 = skip)')
+    ap.add_argument('--check-frames', type=int, default=128, help='frames of every rank checked on rank 0')
+    ap.add_argument('--cpu-frames-per-core', type=int, default=64, help='CPU baseline sample per host core')
+    ap.add_argument('--ingest-streams', type=int, default=32768, help='JPEG streams per GPU and step (0 = skip)')
+    ap.add_argument('--micro-bench', type=int, default=1)
     args = ap.parse_args()
     protect_stdout()
-    set_frame_size(args.size)
-    if not args.frames:
-        world = int(os.environ.get('WORLD_SIZE', '1'))
-        args.frames = 4096 if FRAME_H * FRAME_W <= 640 * 480 else max(1, 32768 // max(world, args.gpus, 1))
     if args.impl == 'reference':
         run_reference(args)
     else:

@@ -60,7 +60,8 @@ typedef struct melf_dial {
 /* Everything the path needs from Params (_params.py:30-64). Host pointers; copied. */
 typedef struct melf_params {
     uint32_t struct_size;          /* sizeof(melf_params), ABI check                     */
-    int32_t n_dials;               /* 1..MELF_MAX_DIALS, YAML order = evaluation order   */
+    int32_t n_dials;               /* 0..MELF_MAX_DIALS, YAML order = evaluation order;
+                                      0 = locate-only ctx (melf_match_template only)     */
     int32_t tmpl_w, tmpl_h;        /* dials_template_size                                */
     const uint8_t *tmpl;           /* tmpl_h*tmpl_w grayscale template (_image.py:72-81) */
     int32_t rect_x0, rect_y0, rect_x1, rect_y1; /* meter_rect; clipped to the frame like
@@ -156,6 +157,12 @@ int melf_convert_hls(int device, const uint8_t *d_bgr, int n, int h, int w,
                      uint8_t *d_hls, uint8_t *d_light,
                      const uint8_t *lo, const uint8_t *hi, uint8_t *d_mask, void *stream);
 
+/* get_mask_by_color on an image that is HLS already (_utils.py:113-119 = cv2.inRange, inclusive
+ * bounds, per channel): d_img is n frames of h x w 3-channel pixels (frame f at + f*frame_stride,
+ * rows row_stride apart), d_mask n*h*w bytes, 255 where lo <= pixel <= hi.  lo/hi: 3 bytes, host. */
+int melf_in_range(int device, const uint8_t *d_img, int n, int h, int w, size_t row_stride,
+                  size_t frame_stride, const uint8_t *lo, const uint8_t *hi, uint8_t *d_mask, void *stream);
+
 /* match_template (_utils.py:91-97): TM_CCOEFF of every frame's meter_rect crop against
  * the ctx template + minMaxLoc.  channels = 3: d_img is BGR and the lightness plane is
  * computed on the fly; channels = 1: d_img is an 8-bit single-channel image.
@@ -169,7 +176,9 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
 /* ImageFile.get_bgr_image's cv2.imread (_image.py:49) for n JPEG streams held in HOST memory:
  * stream i is jpeg[offsets[i] .. offsets[i+1]).  The pixels are bit-identical to OpenCV's bundled
  * libjpeg-turbo (ISLOW IDCT, fancy upsampling).  Supported: 8-bit baseline/extended sequential
- * Huffman, one scan, YCbCr 4:4:4 / 4:2:2 / 4:2:0 or grey, no restart intervals; every stream of a
+ * Huffman, one scan, YCbCr 4:4:4 / 4:2:2 / 4:2:0 or grey, with or without restart intervals (DRI);
+ * 3-component streams that libjpeg reads as RGB (Adobe APP14 transform 0 or component ids 'R','G','B'
+ * without a JFIF marker) are MELF_ERR_UNSUPPORTED; every stream of a
  * call must decode to h x w pixels with the same subsampling.  Anything else: MELF_ERR_UNSUPPORTED /
  * MELF_ERR_INVALID with a text in melf_last_error -- never a silently different image.
  * A stream whose entropy data ends early (file cut short) is decoded like libjpeg decodes it
@@ -188,7 +197,8 @@ int melf_jpeg_info(const uint8_t *jpeg, size_t len, int *h, int *w, int *compone
                    int *v_samp);
 
 /* get_meter_values over JPEG files already read into memory (_api.py:22-33 without the file
- * I/O): decode, crop to meter_rect, locate and read, in pipelined chunks on two streams.
+ * I/O): decode, crop to meter_rect, locate and read, in pipelined chunks of up to 8192 streams on up
+ * to 8 CUDA streams (MELF_JPEG_SLOTS / MELF_JPEG_CHUNK).
  * HOST streams in, HOST results out.  Synchronous. */
 int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets, int n,
                          melf_result *out);

@@ -78,7 +78,8 @@ _SYMBOLS = (
     'melf_create', 'melf_destroy', 'melf_last_error', 'melf_abi_version',
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
-    'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch')
+    'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch',
+    'melf_in_range')
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a', 'jpeg_upload', 'jpeg_destuff',
                  'jpeg_huffman', 'jpeg_idct', 'jpeg_color')
@@ -133,6 +134,9 @@ def load_library() -> C.CDLL:
             C.c_size_t, C.c_void_p]
         lib.melf_jpeg_info.argtypes = [C.c_void_p, C.c_size_t] + [C.POINTER(C.c_int)] * 5
         lib.melf_read_jpeg_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        lib.melf_in_range.argtypes = [
+            C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p,
+            C.c_void_p, C.c_void_p, C.c_void_p]
         lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
         lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
@@ -145,8 +149,8 @@ def build_cparams(template: Image, meter_rect: Tuple[int, int, int, int], hue_sh
     """Plain data -> ``melf_params``.  ``dials``: YAML-ordered dicts with keys name,
     center, color_range (h, l, s), negative_momentum, angle_of_zero, mask, circle_mask.
     Returns the struct and the list of arrays that must stay alive with it."""
-    if not 1 <= len(dials) <= MAX_DIALS:
-        raise ValueError('between 1 and {} dials are supported'.format(MAX_DIALS))
+    if len(dials) > MAX_DIALS:     # no dials = a locate-only context (match_template with any template)
+        raise ValueError('at most {} dials are supported'.format(MAX_DIALS))
     keep: List[Any] = []
     tmpl = np.ascontiguousarray(template, dtype=np.uint8)
     if tmpl.ndim != 2:
@@ -301,6 +305,18 @@ def convert_hls_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stri
     rc = lib.melf_convert_hls(device, d_bgr, n, h, w, row_stride, frame_stride, hue_shift,
                               1 if s_tail else 0, d_hls or None, d_light or None,
                               lo_b, hi_b, d_mask or None, stream or None)
+    if rc:
+        raise EngineError(rc, (lib.melf_last_error(None) or b'').decode())
+
+
+def in_range_device(device: int, d_img: int, n: int, h: int, w: int, row_stride: int, frame_stride: int,
+                    lo: Sequence[int], hi: Sequence[int], d_mask: int, stream: int = 0) -> None:
+    """``melf_in_range``: cv2.inRange of 3-channel u8 frames on the device."""
+    lib = load_library()
+    lo_b = (C.c_uint8 * 3)(*(int(v) for v in lo))
+    hi_b = (C.c_uint8 * 3)(*(int(v) for v in hi))
+    rc = lib.melf_in_range(device, d_img, n, h, w, row_stride, frame_stride, lo_b, hi_b, d_mask,
+                           stream or None)
     if rc:
         raise EngineError(rc, (lib.melf_last_error(None) or b'').decode())
 

@@ -118,6 +118,30 @@ class ImageFile:
                 self.filename, extra_info={'match val': match.max_val})
         return match
 
+    def _find_dials(self, img_hls: Image) -> TemplateMatchResult:
+        """The reference's signature (``_image.py:57-66``): locate on the L plane of an HLS image."""
+        from ._utils import match_template
+        match = match_template(numpy.ascontiguousarray(img_hls[:, :, 1]), get_dials_template(self.params))
+        if match.max_val < self.params.dials_match_threshold:
+            raise DialsNotFoundError(
+                self.filename, extra_info={'match val': match.max_val})
+        return match
+
+    def get_bgr_image_t(self) -> Image:
+        """The BGR image translated so that the matched dials rect lands on (30, 116)
+        (``_image.py:34-44``: ``cv2.warpAffine`` with an integer translation and a zero border is
+        an exact pixel copy; the batched form is ``melf_average_translated``)."""
+        bgr_image = self.get_bgr_image()
+        (x0, y0) = self.find_dials().rect.top_left
+        (dx, dy) = (30 - x0, 116 - y0)
+        (h, w) = bgr_image.shape[:2]
+        out = numpy.zeros_like(bgr_image)
+        (sx0, sx1) = (max(0, -dx), min(w, w - dx))
+        (sy0, sy1) = (max(0, -dy), min(h, h - dy))
+        if sx1 > sx0 and sy1 > sy0:
+            out[sy0 + dy:sy1 + dy, sx0 + dx:sx1 + dx] = bgr_image[sy0:sy1, sx0:sx1]
+        return out
+
     def get_dials_hls(self) -> Image:
         match = self.find_dials()
         ((x0, y0), (x1, y1)) = match.rect

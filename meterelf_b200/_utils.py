@@ -73,25 +73,75 @@ def convert_to_hls(image: Image, hue_shift: int = 0,
     return (hls, d_mask.cpu().numpy()) if color_range else hls
 
 
-def get_mask_by_color(bgr_image: Image, hue_shift: int, color: HlsColor,
-                      color_range: HlsColor) -> Image:
-    """inRange of the converted image around ``color`` (``_utils.py:113-119``), fused
-    with the conversion: takes the BGR image, not an HLS one."""
+def get_mask_by_color(hls_image: Image, color: HlsColor, color_range: HlsColor) -> Image:
+    """``cv2.inRange`` of an HLS image around ``color`` (``_utils.py:113-119``): 255 where every
+    channel lies within ``color +- color_range`` (clamped to 0..255, no hue wrap), else 0."""
+    torch = _torch()
+    (lo, hi) = color.get_range(color_range)
+    d_in = _upload(hls_image)
+    (h, w) = hls_image.shape[:2]
+    d_mask = torch.empty((h, w), dtype=torch.uint8, device='cuda')
+    _engine.in_range_device(torch.cuda.current_device(), d_in.data_ptr(), 1, h, w, w * 3, h * w * 3,
+                            [int(c) for c in lo], [int(c) for c in hi], d_mask.data_ptr(),
+                            torch.cuda.current_stream().cuda_stream)
+    return d_mask.cpu().numpy()
+
+
+def get_mask_by_color_bgr(bgr_image: Image, hue_shift: int, color: HlsColor,
+                          color_range: HlsColor) -> Image:
+    """``get_mask_by_color(convert_to_hls(bgr, hue_shift), ...)`` in one fused pass over the BGR
+    image (the HLS image is never written)."""
     return convert_to_hls(bgr_image, hue_shift, color.get_range(color_range))[1]
 
 
-def match_template_bgr(bgr_image: Image, template: Image, params) -> TemplateMatchResult:
-    """``match_template`` (``_utils.py:91-97``) on the lightness plane of a BGR image."""
-    from ._reading import get_engine
+_template_engines: dict = {}
+
+
+def _template_engine(template: Image, device: int) -> '_engine.Engine':
+    """Locate-only ``melf_ctx`` (no dials) for an arbitrary template, cached by content."""
+    tmpl = numpy.ascontiguousarray(template, dtype=numpy.uint8)
+    key = (tmpl.shape, hash(tmpl.tobytes()), device)
+    entry = _template_engines.get(key)
+    if entry is None or not numpy.array_equal(entry[0], tmpl):
+        (cparams, keep) = _engine.build_cparams(tmpl, (0, 0, 2 ** 30, 2 ** 30), 0, 0.0, [])
+        entry = (tmpl, _engine.Engine(cparams, keep, [], device))
+        if len(_template_engines) > 16:
+            _template_engines.clear()
+        _template_engines[key] = entry
+    return entry[1]
+
+
+def _match(engine, image: Image, template_shape) -> TemplateMatchResult:
     torch = _torch()
-    engine = get_engine(params, cropped_input=True)
-    d_in = _upload(bgr_image)
-    (h, w) = bgr_image.shape[:2]
+    channels = 3 if image.ndim == 3 else 1
+    d_in = _upload(image)
+    (h, w) = image.shape[:2]
     d_xy = torch.empty((2,), dtype=torch.int32, device='cuda')
     d_val = torch.empty((1,), dtype=torch.float32, device='cuda')
     engine.match_template_device(
-        d_in.data_ptr(), 3, 1, h, w, w * 3, h * w * 3, False, d_xy.data_ptr(),
+        d_in.data_ptr(), channels, 1, h, w, w * channels, h * w * channels, False, d_xy.data_ptr(),
         d_val.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
     (x, y) = (int(v) for v in d_xy.cpu())
-    (th, tw) = template.shape[:2]
+    (th, tw) = template_shape[:2]
     return TemplateMatchResult(Rect((x, y), (x + tw, y + th)), float(d_val.cpu()[0]))
+
+
+def match_template(img: Image, template: Image) -> TemplateMatchResult:
+    """``cv2.matchTemplate(img, template, TM_CCOEFF)`` + ``cv2.minMaxLoc`` on a single-channel
+    8-bit image (``_utils.py:91-97``): rect of the best match and its score.  Exact integer
+    arithmetic, the first maximum in raster order wins (DESIGN.md section 2 for how that relates to
+    cv2's float32 DFT on near-ties)."""
+    if img.ndim != 2 or template.ndim != 2:
+        raise ValueError('match_template takes single-channel images')
+    if img.shape[0] < template.shape[0] or img.shape[1] < template.shape[1]:
+        raise ValueError('image smaller than the template')     # cv2.matchTemplate raises cv2.error
+    torch = _torch()
+    return _match(_template_engine(template, torch.cuda.current_device()), img, template.shape)
+
+
+def match_template_bgr(bgr_image: Image, template: Image, params) -> TemplateMatchResult:
+    """``match_template`` on the lightness plane of a BGR image, fused (the plane is never written)."""
+    from ._reading import get_engine
+    torch = _torch()
+    return _match(get_engine(params, cropped_input=True, device=torch.cuda.current_device()),
+                  bgr_image, template.shape)

@@ -21,6 +21,8 @@ cudaError_t melf_launch_match_unpack(const u64 *key, int n, int res_w, int32_t *
 #include "melf_jpeg.h"
 
 cudaError_t melf_launch_convert(const MelfConvertArgs &a, int num_sms, cudaStream_t stream);
+cudaError_t melf_launch_in_range(const uint8_t *img, size_t row_stride, size_t frame_stride, int n, int h, int w,
+                                 uint32_t lo, uint32_t hi, uint8_t *mask, int num_sms, cudaStream_t stream);
 bool melf_match_tc_supported(int tmpl_w, int tmpl_h);
 size_t melf_match_tc_toeplitz_bytes(int tmpl_h);
 void melf_match_tc_build_toeplitz(const uint8_t *tmpl, int tmpl_w, int tmpl_h, uint8_t *out);
@@ -34,6 +36,21 @@ size_t melf_match_fused_ov_scratch_bytes(int num_sms);
 cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
+
+// Every entry point works on its own device and leaves the calling thread's current device as it
+// found it (one process may drive several GPUs, and callers own buffers on "their" device).
+struct DeviceScope {
+    int prev = -1;
+    cudaError_t status;
+    explicit DeviceScope(int device)
+    {
+        status = cudaGetDevice(&prev);
+        if (status == cudaSuccess && prev != device) status = cudaSetDevice(device); else if (status == cudaSuccess) prev = -1;
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
 
 std::atomic<uint64_t> g_launches{0};
 std::mutex g_err_mutex;
@@ -213,7 +230,9 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
                 ctx->d_tc_scratch[scratch_slot] = nullptr; ctx->tc_scratch_items[scratch_slot] = 0;
                 const size_t bytes = melf_match_fused_ov_scratch_bytes(ctx->num_sms);     // the larger of the two layouts
                 MELF_CUDA(ctx, cudaMalloc(&ctx->d_tc_scratch[scratch_slot], bytes));
-                MELF_CUDA(ctx, cudaMemset(ctx->d_tc_scratch[scratch_slot], 0, bytes));
+                // on the stream the kernels run on (a memset on the legacy stream is not ordered against
+                // a cudaStreamNonBlocking stream)
+                MELF_CUDA(ctx, cudaMemsetAsync(ctx->d_tc_scratch[scratch_slot], 0, bytes, stream));
                 ctx->tc_scratch_items[scratch_slot] = -1;         // marks "fused layout"
             }
             t.slabs = ctx->d_tc_scratch[scratch_slot];
@@ -290,6 +309,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
              size_t row_stride, size_t frame_stride, const MelfGeom &geom, u64 *d_keys, melf_result *d_out, const melf_taps *taps,
              cudaStream_t stream, int scratch_slot)
 {
+    if (ctx->params.n_dials < 1) return fail(ctx, MELF_ERR_INVALID, "locate-only context (no dials): nothing to read");
     int rc = launch_locate(ctx, d_bgr, 3, n, frame_h, frame_w, row_stride, frame_stride, geom, d_keys,
                            nullptr, stream, scratch_slot);
     if (rc) return rc;
@@ -297,7 +317,7 @@ int run_path(melf_ctx *ctx, const uint8_t *d_bgr, int n, int frame_h, int frame_
         if (ctx->d_dial_slots[scratch_slot]) cudaFree(ctx->d_dial_slots[scratch_slot]);
         ctx->d_dial_slots[scratch_slot] = nullptr; ctx->dial_slots_cap[scratch_slot] = 0;
         MELF_CUDA(ctx, cudaMalloc(&ctx->d_dial_slots[scratch_slot], (size_t)n * sizeof(MelfDialSlot)));
-        MELF_CUDA(ctx, cudaMemset(ctx->d_dial_slots[scratch_slot], 0, (size_t)n * sizeof(MelfDialSlot)));
+        MELF_CUDA(ctx, cudaMemsetAsync(ctx->d_dial_slots[scratch_slot], 0, (size_t)n * sizeof(MelfDialSlot), stream));
         ctx->dial_slots_cap[scratch_slot] = n;
     }
     MelfDialsArgs a{};
@@ -364,7 +384,7 @@ struct JpegSpans {
 void free_ctx(melf_ctx *ctx)
 {
     if (!ctx) return;
-    cudaSetDevice(ctx->device);
+    DeviceScope dev_scope(ctx->device);
     cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_need_pos); cudaFree(ctx->d_ring_angle);
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
@@ -423,8 +443,8 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
     if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceCount");
     if (device < 0 || device >= count)
         return fail(nullptr, MELF_ERR_CUDA, "no such CUDA device");
-    e = cudaSetDevice(device);
-    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
+    DeviceScope dev_scope(device);
+    if (dev_scope.status != cudaSuccess) return cuda_fail(nullptr, dev_scope.status, "cudaSetDevice");
 
     melf_ctx *ctx = new melf_ctx();
     ctx->device = device;
@@ -497,8 +517,9 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
         const char *impl = std::getenv("MELF_MATCH_IMPL");
         ctx->use_tc = !(impl && std::strcmp(impl, "dp4a") == 0);
     }
-    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_dials, dials.size() * sizeof(MelfDialDev)));
-    MELF_CREATE_CUDA(cudaMemcpy(ctx->d_dials, dials.data(), dials.size() * sizeof(MelfDialDev), cudaMemcpyHostToDevice));
+    MELF_CREATE_CUDA(cudaMalloc(&ctx->d_dials, (dials.size() ? dials.size() : 1) * sizeof(MelfDialDev)));
+    if (!dials.empty())
+        MELF_CREATE_CUDA(cudaMemcpy(ctx->d_dials, dials.data(), dials.size() * sizeof(MelfDialDev), cudaMemcpyHostToDevice));
     {
         const size_t nn = rings.need.size() ? rings.need.size() : 1;
         MELF_CREATE_CUDA(cudaMalloc(&ctx->d_need_pos, nn * sizeof(uint16_t)));
@@ -530,7 +551,8 @@ int melf_profile_enable(melf_ctx *ctx, int on)
 int melf_profile_read(melf_ctx *ctx, float *ms, int32_t *launches)
 {
     if (!ctx || !ms || !launches) return MELF_ERR_INVALID;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     MELF_CUDA(ctx, cudaDeviceSynchronize());
     for (int k = 0; k < MELF_PROF_KINDS; k++) { ms[k] = 0.f; launches[k] = 0; }
     for (const melf_ctx::Span &sp : ctx->spans) {
@@ -563,7 +585,8 @@ int melf_read_batch_async(melf_ctx *ctx, const uint8_t *d_bgr, int n, int h, int
         return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
     if (row_stride < (size_t)w * 3) return fail(ctx, MELF_ERR_INVALID, "row_stride < 3*w");
     if (n == 0) return MELF_OK;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     MelfGeom geom;
     int rc = make_geom(ctx, h, w, true, &geom);
     if (rc) return rc;
@@ -581,7 +604,8 @@ int melf_read_batch(melf_ctx *ctx, const uint8_t *bgr, int n, int h, int w,
         return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
     if (row_stride < (size_t)w * 3) return fail(ctx, MELF_ERR_INVALID, "row_stride < 3*w");
     if (n == 0) return MELF_OK;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     MelfGeom geom;
     int rc = make_geom(ctx, h, w, true, &geom);
     if (rc) return rc;
@@ -675,7 +699,8 @@ int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets
     if (n < 0 || h < 1 || w < 1 || (n > 0 && (!jpeg || !offsets || !d_bgr)))
         return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
     if (n == 0) return MELF_OK;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     MelfJpegBatch batch{jpeg, offsets, n};
     std::string err;
     uint64_t launches = 0;
@@ -692,7 +717,8 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
     if (!ctx) return MELF_ERR_INVALID;
     if (n < 0 || (n > 0 && (!jpeg || !offsets || !out))) return fail(ctx, MELF_ERR_INVALID, "bad batch arguments");
     if (n == 0) return MELF_OK;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     int h = 0, w = 0;
     std::string err;
     int rc = melf_jpeg_probe(jpeg + offsets[0], (size_t)(offsets[1] - offsets[0]), &h, &w, nullptr, nullptr,
@@ -801,7 +827,8 @@ int melf_convert_hls(int device, const uint8_t *d_bgr, int n, int h, int w,
         hue_shift < 0 || hue_shift > 255 || (d_mask && (!lo || !hi)))
         return fail(nullptr, MELF_ERR_INVALID, "bad melf_convert_hls arguments");
     if (n == 0) return MELF_OK;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope dev_scope(device);
+    cudaError_t e = dev_scope.status;
     if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
@@ -818,6 +845,24 @@ int melf_convert_hls(int device, const uint8_t *d_bgr, int n, int h, int w,
     return MELF_OK;
 }
 
+int melf_in_range(int device, const uint8_t *d_img, int n, int h, int w, size_t row_stride, size_t frame_stride,
+                  const uint8_t *lo, const uint8_t *hi, uint8_t *d_mask, void *stream)
+{
+    if (n < 0 || h < 1 || w < 1 || (n > 0 && (!d_img || !d_mask)) || !lo || !hi || row_stride < (size_t)w * 3)
+        return fail(nullptr, MELF_ERR_INVALID, "bad melf_in_range arguments");
+    if (n == 0) return MELF_OK;
+    DeviceScope dev_scope(device);
+    if (dev_scope.status != cudaSuccess) return cuda_fail(nullptr, dev_scope.status, "cudaSetDevice");
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const cudaError_t e = melf_launch_in_range(d_img, row_stride, frame_stride, n, h, w,
+                                               lo[0] | (lo[1] << 8) | (lo[2] << 16), hi[0] | (hi[1] << 8) | (hi[2] << 16),
+                                               d_mask, sms, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "melf_in_range kernel launch");
+    g_launches++;
+    return MELF_OK;
+}
+
 int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
                         size_t row_stride, size_t frame_stride, int use_rect,
                         int32_t *d_max_xy, float *d_max_val, float *d_result, void *stream)
@@ -827,7 +872,8 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
         !d_max_xy || !d_max_val || row_stride < (size_t)w * channels)
         return fail(ctx, MELF_ERR_INVALID, "bad melf_match_template arguments");
     if (n == 0) return MELF_OK;
-    MELF_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
     MelfGeom geom;
     int rc = make_geom(ctx, h, w, use_rect != 0, &geom);
     if (rc) return rc;

@@ -49,9 +49,12 @@ extern "C" int melf_average_translated(int device, const uint8_t *d_bgr, int n, 
 {
     if (n < 1 || h < 1 || w < 1 || !d_bgr || !d_match_xy || !d_out || row_stride < (size_t)3 * w)
         return MELF_ERR_INVALID;
-    if (cudaSetDevice(device) != cudaSuccess) return MELF_ERR_CUDA;
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess || cudaSetDevice(device) != cudaSuccess) return MELF_ERR_CUDA;
     const int total = h * w * 3;
     melf_average_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
         d_bgr, n, h, w, row_stride, frame_stride, d_match_xy, anchor_x, anchor_y, d_out);
-    return cudaGetLastError() == cudaSuccess ? MELF_OK : MELF_ERR_CUDA;
+    const cudaError_t e = cudaGetLastError();
+    if (prev != device) cudaSetDevice(prev);      // leave the caller's current device as it was
+    return e == cudaSuccess ? MELF_OK : MELF_ERR_CUDA;
 }

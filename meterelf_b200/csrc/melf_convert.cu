@@ -476,3 +476,58 @@ cudaError_t melf_launch_convert(const MelfConvertArgs &a_in, int num_sms, cudaSt
     }
     return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------------
+// cv2.inRange on a 3-channel u8 image (get_mask_by_color on an HLS image, _utils.py:113-119):
+// 3 B/px in, 1 B/px out, HBM-bound; 16 pixels per thread with 128-bit loads when the row is aligned
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+melf_in_range_kernel(const uint8_t *__restrict__ img, size_t row_stride, size_t frame_stride, int n, int h, int w,
+                     uint32_t lo, uint32_t hi, uint8_t *__restrict__ mask)
+{
+    const int groups = (w + 15) >> 4;
+    const long long total = (long long)n * h * groups;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int g = (int)(i % groups);
+        const long long rowi = i / groups;
+        const int y = (int)(rowi % h), f = (int)(rowi / h);
+        const uint8_t *src = img + (size_t)f * frame_stride + (size_t)y * row_stride + 48 * (size_t)g;
+        uint8_t *dst = mask + ((size_t)f * h + y) * (size_t)w + 16 * (size_t)g;
+        const int npx = min(16, w - 16 * g);
+        if (npx == 16 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+            const uint4 *v = reinterpret_cast<const uint4 *>(src);
+            const uint4 a = __ldg(v), b = __ldg(v + 1), c = __ldg(v + 2);
+            const uint32_t wv[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+            uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int px = 0; px < 16; ++px) {
+                const int b0 = 3 * px;
+                // bytes b0 .. b0+2 -> one packed H | L<<8 | S<<16 word
+                const uint32_t lo_w = wv[b0 >> 2], hi_w = wv[(b0 + 2) >> 2];
+                const uint32_t pix = __funnelshift_r(lo_w, hi_w, 8 * (b0 & 3)) & 0xffffffu;
+                o[px >> 2] |= (in_range255(pix, lo, hi) & 255u) << (8 * (px & 3));
+            }
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+        } else {
+            for (int px = 0; px < npx; ++px) {
+                const uint32_t pix = src[3 * px] | (src[3 * px + 1] << 8) | (src[3 * px + 2] << 16);
+                dst[px] = (uint8_t)in_range255(pix, lo, hi);
+            }
+        }
+    }
+}
+
+cudaError_t melf_launch_in_range(const uint8_t *img, size_t row_stride, size_t frame_stride, int n, int h, int w,
+                                 uint32_t lo, uint32_t hi, uint8_t *mask, int num_sms, cudaStream_t stream)
+{
+    const bool empty = (lo & 255) > (hi & 255) || ((lo >> 8) & 255) > ((hi >> 8) & 255) ||
+                       ((lo >> 16) & 255) > ((hi >> 16) & 255);
+    if (empty) return cudaMemsetAsync(mask, 0, (size_t)n * h * w, stream);     // like cv2.inRange
+    const long long total = (long long)n * h * ((w + 15) >> 4);
+    long long blocks = (total + 255) / 256;
+    if (blocks > (long long)num_sms * 8) blocks = (long long)num_sms * 8;
+    if (blocks < 1) blocks = 1;
+    melf_in_range_kernel<<<(unsigned)blocks, 256, 0, stream>>>(img, row_stride, frame_stride, n, h, w, lo, hi, mask);
+    return cudaGetLastError();
+}

@@ -49,8 +49,9 @@ int melf_host_check_params(const melf_params *P, std::string *err)
     if (!P) return fail(MELF_ERR_INVALID, "params is NULL");
     if (P->struct_size != sizeof(melf_params))
         return fail(MELF_ERR_INVALID, "melf_params.struct_size mismatch (ABI)");
-    if (P->n_dials < 1 || P->n_dials > MELF_MAX_DIALS)
-        return fail(MELF_ERR_INVALID, "n_dials must be 1..MELF_MAX_DIALS");
+    // n_dials == 0: a locate-only context (melf_match_template with any template, _utils.py:91-97)
+    if (P->n_dials < 0 || P->n_dials > MELF_MAX_DIALS)
+        return fail(MELF_ERR_INVALID, "n_dials must be 0..MELF_MAX_DIALS");
     if (!P->tmpl || P->tmpl_w < 1 || P->tmpl_h < 1)
         return fail(MELF_ERR_INVALID, "missing dials template");
     if (P->tmpl_w > 256 || P->tmpl_h > 256)

@@ -315,3 +315,127 @@ def decode_jpeg_coefficients(data: bytes, component: int) -> np.ndarray:
     if rc:
         raise JpegError('jpeg oracle: code %d' % rc)
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# oracle/_ref: the UNMODIFIED reference package, vendored at build time (git-ignored; it travels
+# to the GPU box with the gpurun snapshot) and run one process per core as the timed CPU arm
+# (ImageFile(name, params, bgr_image=crop) -> get_meter_value, _reading.py:19-115).
+# ---------------------------------------------------------------------------------------------
+REF_SOURCE = os.environ.get('MELF_REFERENCE_ROOT', '/root/reference')
+REF_DIR = os.path.join(_HERE, '_ref')
+
+
+def build_ref(force: bool = False) -> Optional[str]:
+    """Copy ``/root/reference/meterelf`` (Python sources, nothing to compile) to ``oracle/_ref/meterelf``
+    when the reference tree is present; returns the directory that holds the package, or None when
+    there is neither a reference tree nor an earlier copy."""
+    import shutil
+    src = os.path.join(REF_SOURCE, 'meterelf')
+    dst = os.path.join(REF_DIR, 'meterelf')
+    if os.path.isdir(src) and (force or not os.path.isdir(dst)):
+        if os.path.isdir(dst):
+            shutil.rmtree(dst)
+        os.makedirs(REF_DIR, exist_ok=True)
+        shutil.copytree(src, dst, ignore=shutil.ignore_patterns('__pycache__', '*.pyc'))
+    return REF_DIR if os.path.isdir(dst) else None
+
+
+def ref_available() -> bool:
+    return os.path.isdir(os.path.join(REF_DIR, 'meterelf'))
+
+
+class RefPool:
+    """``workers`` processes of the unmodified reference (``oracle/ref_worker.py``), each reading a
+    contiguous share of ``crops`` (n, h, w, 3 u8, already cut to meter_rect) with ``params_file``.
+    ``run()`` starts all workers together and returns (wall seconds, records or None)."""
+
+    def __init__(self, params_file: str, crops: np.ndarray, workers: int,
+                 threshold: Optional[float] = None) -> None:
+        import json
+        import sys
+        import tempfile
+        if not ref_available():
+            raise RuntimeError('oracle/_ref is absent: run __graft_entry__.build() where /root/reference exists')
+        self._json = json
+        self.n = len(crops)
+        self.workers = max(1, min(workers, self.n))
+        shm = '/dev/shm' if os.path.isdir('/dev/shm') and os.access('/dev/shm', os.W_OK) else None
+        self._tmp = tempfile.TemporaryDirectory(dir=shm)
+        path = os.path.join(self._tmp.name, 'crops.npy')
+        np.save(path, np.ascontiguousarray(crops))
+        env = dict(os.environ, OMP_NUM_THREADS='1', OPENBLAS_NUM_THREADS='1', MKL_NUM_THREADS='1',
+                   CUDA_VISIBLE_DEVICES='')
+        self.procs = []
+        for k in range(self.workers):
+            proc = subprocess.Popen([sys.executable, os.path.join(_HERE, 'ref_worker.py')],
+                                    stdin=subprocess.PIPE, stdout=subprocess.PIPE, env=env, text=True)
+            (lo, hi) = ((k * self.n) // self.workers, ((k + 1) * self.n) // self.workers)
+            self._send(proc, {'cmd': 'load', 'root': REF_DIR, 'params': params_file, 'frames': path,
+                              'lo': lo, 'hi': hi, 'threshold': threshold})
+            self.procs.append(proc)
+        for proc in self.procs:
+            assert 'ready' in self._recv(proc)
+
+    def _send(self, proc, msg) -> None:
+        proc.stdin.write(self._json.dumps(msg) + '\n')
+        proc.stdin.flush()
+
+    def _recv(self, proc) -> Dict[str, Any]:
+        line = proc.stdout.readline()
+        if not line:
+            raise RuntimeError('reference worker died (exit code %s)' % proc.poll())
+        return self._json.loads(line)
+
+    def run(self, want_results: bool = True):
+        import time
+        t0 = time.perf_counter()
+        for proc in self.procs:
+            self._send(proc, {'cmd': 'run', 'results': want_results})
+        replies = [self._recv(proc) for proc in self.procs]
+        wall = time.perf_counter() - t0
+        records = None
+        if want_results:
+            records = [r for rep in replies for r in rep['results']]
+            assert [r['i'] for r in records] == list(range(self.n))
+        return (wall, records)
+
+    def close(self) -> None:
+        for proc in self.procs:
+            try:
+                self._send(proc, {'cmd': 'quit'})
+                proc.stdin.close()
+            except Exception:
+                pass
+        for proc in self.procs:
+            try:
+                proc.wait(timeout=10)
+            except Exception:
+                proc.kill()
+        self.procs = []
+        self._tmp.cleanup()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc) -> None:
+        self.close()
+
+
+def ref_mismatches(ref_records: Sequence[Dict[str, Any]], got: np.ndarray, n_dials: int) -> int:
+    """How many of ``got`` (result records of the GPU path or of the port) differ from what the
+    reference workers returned for the same frames: status, failing / unreadable dials, float64 dial
+    positions and value bit for bit."""
+    bad = 0
+    for (r, g) in zip(ref_records, got):
+        same = int(g['status']) == r['status']
+        if same and r['status'] == 0:
+            want = [float.fromhex(v) for v in r['dial_pos']]
+            same = [float(v) for v in g['dial_pos'][:n_dials]] == want and (
+                r['value'] is None or float(g['value']) == float.fromhex(r['value']))
+        elif same and r['status'] == 2:
+            same = int(g['failed_dial']) == r['failed_dial']
+        elif same and r['status'] == 3:
+            same = int(g['unreadable_mask']) == r['unreadable_mask']
+        bad += 0 if same else 1
+    return bad
