@@ -1,17 +1,22 @@
-"""Offline calibration: dial centres from the average meter image (reference:
-``_calibration.py:16-84``).
+"""Offline calibration: where are the dial centres?  (reference: ``_calibration.py:16-84``)
 
-Same names and argument meaning as the reference.  The per-file work -- dial location
-(``ImageFile._find_dials``), the translation of ``get_bgr_image_t``, the float64 running mean
-and its denormalisation -- runs batched on the GPU (``melf_match_template`` +
-``melf_average_translated``); the needle mask of the average image is the fused
-convert + inRange operator.  ``cv2.findContours`` / ``cv2.fitEllipse`` over the four small
-needle-hub contours stay on the host exactly as in the reference (offline, once per meter).
+The public names and what they take and return are the reference's.  How the work is done is not:
+
+* per file, dial location + the translation of ``get_bgr_image_t`` + the float64 running mean + its
+  denormalisation are ONE batched GPU job (``melf_match_template`` + ``melf_average_translated``);
+* the needle-hub mask of the average image is the fused convert + inRange operator;
+* the hub outlines are followed and fitted here, without OpenCV: ``outer_borders`` is border
+  following after Suzuki & Abe (what ``cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_NONE)`` returns),
+  ``fit_ellipse`` is the least-squares conic fit ``cv2.fitEllipse`` documents (general conic through
+  the centred points, centre from the gradient equations, re-fit of the quadratic part, axes from
+  its eigen-structure).  Both are checked against cv2 in ``tests/test_calibration.py``.
+
 There is no CPU fallback for the GPU part.
 """
 import glob
+import math
 import random
-from typing import Iterable, List, Sequence, Union
+from typing import Iterable, List, Sequence, Tuple, Union
 
 import numpy
 
@@ -19,53 +24,159 @@ from . import _engine
 from ._image import ImageFile
 from ._params import Params as _Params
 from ._types import DialCenter, Image
-from ._utils import _torch, get_mask_by_color
+from ._utils import _torch, get_mask_by_color_bgr
 from .exceptions import DialsNotFoundError
 
 #: where ``get_bgr_image_t`` moves the top-left corner of the matched dials rect (``_image.py:39-42``)
 DIALS_ANCHOR = (30, 116)
 
+#: sample files without a meter in them, never used for calibration (``_calibration.py:71-79``)
+UNUSABLE_SAMPLES = ('20180814021309-01-e01.jpg', '20180814021310-00-e02.jpg')
 
-def find_dial_centers(
-        params: _Params,
-        files: Union[int, Iterable[str]] = 255,
-) -> List[DialCenter]:
-    avg_meter = get_average_meter_image(params, get_files(params, files))
-    return find_dial_centers_from_image(params, avg_meter)
+#: largest relative difference of the two ellipse axes a needle hub may have (``_calibration.py:54-55``)
+MAX_ECCENTRICITY = 0.2
 
-
-def get_files(
-        params: _Params,
-        files: Union[int, Iterable[str]] = 255
-) -> Iterable[str]:
-    if isinstance(files, int):
-        return random.sample(get_image_filenames(params), files)
-    return files
+# the 8 neighbours in clockwise order on the screen (y down), starting at west
+_RING = ((-1, 0), (-1, -1), (0, -1), (1, -1), (1, 0), (1, 1), (0, 1), (-1, 1))
 
 
-def find_dial_centers_from_image(
-        params: _Params,
-        avg_meter: Image,
-) -> List[DialCenter]:
-    import cv2
-    avg_meter_imgf = ImageFile('<average_image>', params, avg_meter)
-    match = avg_meter_imgf.find_dials()
-    ((x0, y0), (x1, y1)) = match.rect
-    # mask of the whole image, then the dials rect: OpenCV's scalar-tail columns are
-    # those of the full-width conversion, as in ImageFile.get_dials_hls
-    needles_mask = numpy.ascontiguousarray(
-        get_needles_mask_by_color(params, numpy.ascontiguousarray(avg_meter))[y0:y1, x0:x1])
-    found = cv2.findContours(needles_mask, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_NONE)
-    contours = found[-2]                      # OpenCV 3 returns (image, contours, hierarchy)
-    dial_centers = []
-    for contour in contours:
-        (center, size, angle) = cv2.fitEllipse(contour)
-        (height, width) = size
+def find_dial_centers(params: _Params, files: Union[int, Iterable[str]] = 255) -> List[DialCenter]:
+    """Centre and diameter of every needle hub, left to right."""
+    return find_dial_centers_from_image(params, get_average_meter_image(params, get_files(params, files)))
+
+
+def get_files(params: _Params, files: Union[int, Iterable[str]] = 255) -> Iterable[str]:
+    """An explicit list is used as it is; a number draws that many of the params' image files."""
+    if not isinstance(files, int):
+        return files
+    return random.sample(get_image_filenames(params), files)
+
+
+def get_image_filenames(params: _Params) -> List[str]:
+    usable = []
+    for path in glob.glob(params.image_glob):
+        if not any(name in path for name in UNUSABLE_SAMPLES):
+            usable.append(path)
+    return usable
+
+
+def outer_borders(mask: Image) -> List[numpy.ndarray]:
+    """Outer border of every 8-connected component of ``mask != 0`` as an (n, 2) array of (x, y),
+    pixel by pixel in following order (a pixel the border passes twice is listed twice), found in
+    raster order and returned newest first -- ``cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_NONE)``."""
+    fg = numpy.pad(numpy.asarray(mask) != 0, 1)               # zero frame: no bounds checks below
+    label = numpy.zeros(fg.shape, numpy.int32)
+    # background reachable from the frame (4-connected): a component whose raster-first pixel has
+    # enclosed background to its west sits in a hole of another component and is not external
+    outside = numpy.zeros(fg.shape, bool)
+    outside[0, 0] = True
+    stack = [(0, 0)]
+    (rows, cols) = fg.shape
+    while stack:
+        (cx, cy) = stack.pop()
+        for (nx, ny) in ((cx - 1, cy), (cx + 1, cy), (cx, cy - 1), (cx, cy + 1)):
+            if 0 <= nx < cols and 0 <= ny < rows and not fg[ny, nx] and not outside[ny, nx]:
+                outside[ny, nx] = True
+                stack.append((nx, ny))
+    borders: List[numpy.ndarray] = []
+    (ys, xs) = numpy.nonzero(fg)
+    for (y0, x0) in zip(ys.tolist(), xs.tolist()):
+        if label[y0, x0]:
+            continue
+        external = bool(outside[y0, x0 - 1])
+        # mark the whole component so that its other pixels do not start a border of their own
+        stack = [(x0, y0)]
+        label[y0, x0] = 1
+        while stack:
+            (cx, cy) = stack.pop()
+            for (dx, dy) in _RING:
+                (nx, ny) = (cx + dx, cy + dy)
+                if fg[ny, nx] and not label[ny, nx]:
+                    label[ny, nx] = 1
+                    stack.append((nx, ny))
+        if external:
+            borders.append(_follow_border(fg, x0, y0))
+    return borders[::-1]
+
+
+def _follow_border(fg: numpy.ndarray, x0: int, y0: int) -> numpy.ndarray:
+    """Suzuki-Abe border following from the raster-first pixel of a component (its west
+    neighbour is background).  ``fg`` carries a one-pixel zero frame; points come back unpadded."""
+    points = [(x0 - 1, y0 - 1)]
+    first = None
+    for k in range(8):                                        # clockwise from west
+        if fg[y0 + _RING[k][1], x0 + _RING[k][0]]:
+            first = (x0 + _RING[k][0], y0 + _RING[k][1])
+            break
+    if first is None:
+        return numpy.array(points, numpy.int32)               # a single pixel
+    (prev, cur) = (first, (x0, y0))
+    while True:
+        start = _RING.index((prev[0] - cur[0], prev[1] - cur[1]))
+        for t in range(1, 9):                                 # counter-clockwise, after `prev`
+            (dx, dy) = _RING[(start - t) % 8]
+            if fg[cur[1] + dy, cur[0] + dx]:
+                nxt = (cur[0] + dx, cur[1] + dy)
+                break
+        if nxt == (x0, y0) and cur == first:
+            break
+        (prev, cur) = (cur, nxt)
+        points.append((cur[0] - 1, cur[1] - 1))
+    return numpy.array(points, numpy.int32)
+
+
+def fit_ellipse(points: numpy.ndarray) -> Tuple[Tuple[float, float], Tuple[float, float], float]:
+    """((cx, cy), (width, height), angle in degrees) of the least-squares ellipse through at least
+    five points, with ``cv2.fitEllipse``'s conventions: float32 results, width <= height."""
+    pts = numpy.asarray(points, numpy.float64).reshape(-1, 2)
+    if len(pts) < 5:
+        raise ValueError('at least five points are needed to fit an ellipse')
+    mean = pts.astype(numpy.float32).mean(axis=0, dtype=numpy.float64).astype(numpy.float32).astype(numpy.float64)
+    (x, y) = (pts[:, 0] - mean[0], pts[:, 1] - mean[1])
+    # general conic  -A x^2 - B y^2 - C xy + D x + E y = 10000  through the centred points
+    conic = numpy.linalg.lstsq(numpy.stack([-x * x, -y * y, -x * y, x, y], axis=1),
+                               numpy.full(len(pts), 10000.0), rcond=None)[0]
+    # its centre: where both partial derivatives vanish
+    centre = numpy.linalg.lstsq(numpy.array([[2 * conic[0], conic[2]], [conic[2], 2 * conic[1]]]),
+                                conic[3:5], rcond=None)[0]
+    # quadratic part again, around that centre:  A u^2 + B v^2 + C uv = 1
+    (u, v) = (x - centre[0], y - centre[1])
+    (a, b, c) = numpy.linalg.lstsq(numpy.stack([u * u, v * v, u * v], axis=1), numpy.ones(len(pts)), rcond=None)[0]
+    theta = -0.5 * math.atan2(c, b - a)
+    t = c / math.sin(-2.0 * theta) if abs(c) > 1e-8 else b - a
+    axes = []
+    for q in (abs(a + b - t), abs(a + b + t)):
+        axes.append(math.sqrt(2.0 / q) if q > 1e-8 else q)
+    f32 = numpy.float32
+    (width, height) = (float(f32(2 * axes[0])), float(f32(2 * axes[1])))
+    angle = theta * 180.0 / math.pi
+    if width > height:
+        (width, height) = (height, width)
+        angle += 90.0
+    angle = float(f32(angle))
+    if angle < -180:
+        angle += 360
+    if angle > 360:
+        angle -= 360
+    return ((float(f32(f32(centre[0]) + f32(mean[0]))), float(f32(f32(centre[1]) + f32(mean[1])))),
+            (width, height), angle)
+
+
+def find_dial_centers_from_image(params: _Params, avg_meter: Image) -> List[DialCenter]:
+    located = ImageFile('<average_image>', params, avg_meter).find_dials()
+    ((left, top), (right, bottom)) = located.rect
+    # the mask is taken over the whole image and cut afterwards: OpenCV's scalar-tail columns
+    # (SURVEY 8a-1) are then those of the full-width conversion, as in ImageFile.get_dials_hls
+    whole = get_needles_mask_by_color(params, numpy.ascontiguousarray(avg_meter))
+    hubs = []
+    for border in outer_borders(whole[top:bottom, left:right]):
+        (centre, (width, height), _angle) = fit_ellipse(border)
         diameter = (width + height) / 2.0
-        if abs(height - width) / diameter > 0.2:
+        if abs(height - width) / diameter > MAX_ECCENTRICITY:
             raise ValueError('Needle center not circle enough')
-        dial_centers.append(DialCenter(center, int(round(diameter))))
-    return sorted(dial_centers, key=(lambda x: x.center[0]))
+        hubs.append(DialCenter(centre, int(round(diameter))))
+    hubs.sort(key=lambda hub: hub.center[0])
+    return hubs
 
 
 def get_average_meter_image(params: _Params, files: Iterable[str]) -> Image:
@@ -81,9 +192,10 @@ def average_of_crops(params: _Params, crops: Sequence[Image],
     """``get_average_meter_image`` for already decoded + cropped frames of one size."""
     from ._reading import get_engine
     torch = _torch()
+    device = torch.cuda.current_device()
     frames = numpy.stack([numpy.ascontiguousarray(c) for c in crops])
     (n, h, w) = frames.shape[:3]
-    engine = get_engine(params, cropped_input=True)
+    engine = get_engine(params, cropped_input=True, device=device)
     stream = torch.cuda.current_stream().cuda_stream
     d_in = torch.from_numpy(frames).cuda()
     d_xy = torch.empty((n, 2), dtype=torch.int32, device='cuda')
@@ -96,23 +208,13 @@ def average_of_crops(params: _Params, crops: Sequence[Image],
             raise DialsNotFoundError(names[i] if names else '<frame %d>' % i,
                                      extra_info={'match val': float(val)})
     d_out = torch.empty((h, w, 3), dtype=torch.uint8, device='cuda')
-    _engine.average_translated_device(torch.cuda.current_device(), d_in.data_ptr(), n, h, w, w * 3,
+    _engine.average_translated_device(device, d_in.data_ptr(), n, h, w, w * 3,
                                       h * w * 3, d_xy.data_ptr(), DIALS_ANCHOR, d_out.data_ptr(), stream)
     return d_out.cpu().numpy()
-
-
-def get_image_filenames(params: _Params) -> List[str]:
-    return [
-        path for path in glob.glob(params.image_glob)
-        if all(bad_filename not in path for bad_filename in [
-                '20180814021309-01-e01.jpg',
-                '20180814021310-00-e02.jpg',
-        ])
-    ]
 
 
 def get_needles_mask_by_color(params: _Params, bgr_image: Image) -> Image:
     """inRange around ``needle_color`` (``_calibration.py:82-84``); takes the BGR image because the
     conversion and the range test are one fused GPU pass."""
-    return get_mask_by_color(bgr_image, params.hue_shift, params.needle_color,
-                             params.needle_color_range)
+    return get_mask_by_color_bgr(bgr_image, params.hue_shift, params.needle_color,
+                                 params.needle_color_range)

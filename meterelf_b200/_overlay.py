@@ -11,9 +11,12 @@ momentum vector, contour area), not from a second implementation: filled needle 
 (255, 255, 0) when its area exceeds 100, the momentum marker (radius-4 circle, red) 24 px from
 the dial centre, ring pixels of the needle in (0, 128, 128) and the ones that survive the
 momentum filter in (0, 255, 255), the dial centre (black dot, magenta radius-6 circle) in the
-4x pictures.  Differences to the reference's windows: the background is the decoded BGR
-crop itself (the reference converts its HLS image back to BGR), scaling is pixel replication
-(``cv2.resize`` interpolates), and the PNG encoder is ``zlib`` (no OpenCV needed).
+4x pictures.  The pictures are the reference's, pixel for pixel (``tests/golden/
+make_golden_overlay.py`` captures what the unmodified reference hands to ``cv2.imshow``): the
+background is the HLS dials rect converted back to BGR like ``cv2.cvtColor(HLS2BGR_FULL)`` does
+(``hls_to_bgr_full``; 4 of the 2^24 HLS colours come out one level off in one channel, float32
+near-ties of OpenCV's vectorised code), the 4x / 2x scaling is ``cv2.resize``'s fixed-point bilinear
+filter (``resize_linear``).  The PNG encoder is ``zlib`` (no OpenCV needed).
 """
 import math
 import os
@@ -57,9 +60,62 @@ def encode_png(bgr: numpy.ndarray) -> bytes:
             chunk(b'IDAT', zlib.compress(raw.tobytes(), 6)) + chunk(b'IEND', b''))
 
 
-def scale_image(img: numpy.ndarray, scale: int) -> numpy.ndarray:
+def hls_to_bgr_full(hls: numpy.ndarray) -> numpy.ndarray:
+    """``cv2.cvtColor(hls, cv2.COLOR_HLS2BGR_FULL)`` of an 8-bit image (``convert_to_bgr``,
+    ``_utils.py:105-110``), in the float32 operation order of OpenCV's vectorised ``HLS2RGB_f``:
+    hue range 255 for the inverse conversion (the forward one uses 256), p = l*s or s - l*s, the
+    four candidates l +- p and l +- (p - 2 f p), picked by hue sector; rint(v * 255) at the end."""
+    f32 = numpy.float32
+    hue = hls[..., 0].astype(f32)
+    light = (hls[..., 1].astype(f32) * f32(1.0 / 255.0)).astype(f32)
+    sat = (hls[..., 2].astype(f32) * f32(1.0 / 255.0)).astype(f32)
+    ls = (light * sat).astype(f32)
+    p = numpy.where(light <= f32(0.5), ls, (sat - ls).astype(f32))
+    raw = (hue * (f32(6.0) / f32(255.0))).astype(f32)
+    whole = numpy.trunc(raw).astype(f32)
+    frac = (raw - whole).astype(f32)
+    sector = (whole - (f32(6.0) * numpy.trunc((raw * f32(1.0 / 6.0)).astype(f32)).astype(f32)).astype(f32)).astype(f32)
+    twice = (frac + frac).astype(f32)
+    tab0 = (light + p).astype(f32)
+    tab1 = (light - p).astype(f32)
+    tab2 = (light + (p - (twice * p).astype(f32)).astype(f32)).astype(f32)
+    tab3 = ((light - p).astype(f32) + (twice * p).astype(f32)).astype(f32)
+    blue = numpy.where(sector < 2, tab1, numpy.where(sector <= 2, tab3, numpy.where(sector <= 4, tab0, tab2)))
+    green = numpy.where(sector < 1, tab3, numpy.where(sector <= 2, tab0, numpy.where(sector < 4, tab2, tab1)))
+    red = numpy.where(sector < 1, tab0, numpy.where(sector < 2, tab2, numpy.where(
+        sector < 4, tab1, numpy.where(sector <= 4, tab3, tab0))))
+    bgr = numpy.rint((numpy.stack([blue, green, red], axis=-1) * f32(255.0)).astype(f32))
+    return numpy.clip(bgr, 0, 255).astype(numpy.uint8)
+
+
+def resize_linear(img: numpy.ndarray, scale: int) -> numpy.ndarray:
+    """``cv2.resize(img, (w * scale, h * scale))`` (INTER_LINEAR) of an 8-bit image: sample positions
+    (d + 0.5) / scale - 0.5, 11-bit fixed-point coefficients, horizontal pass first; at the left / right
+    edge the fraction is dropped, at the top / bottom only the row index is clamped (so the truncating
+    fixed-point sum of the two equal rows stays what OpenCV computes)."""
     assert scale > 0
-    return numpy.repeat(numpy.repeat(img, scale, axis=0), scale, axis=1)
+    (h, w) = img.shape[:2]
+    src = img.reshape(h, w, -1).astype(numpy.int64)
+    pos = (numpy.arange(w * scale) + 0.5) / scale - 0.5
+    x0 = numpy.floor(pos).astype(numpy.int64)
+    fx = pos - x0
+    fx = numpy.where((x0 < 0) | (x0 >= w - 1), 0.0, fx)
+    x0 = numpy.clip(x0, 0, w - 1)
+    x1 = numpy.minimum(x0 + 1, w - 1)
+    (ax0, ax1) = (numpy.rint((1 - fx) * 2048).astype(numpy.int64), numpy.rint(fx * 2048).astype(numpy.int64))
+    pos = (numpy.arange(h * scale) + 0.5) / scale - 0.5
+    y0 = numpy.floor(pos).astype(numpy.int64)
+    fy = pos - y0
+    (ay0, ay1) = (numpy.rint((1 - fy) * 2048).astype(numpy.int64), numpy.rint(fy * 2048).astype(numpy.int64))
+    (y0, y1) = (numpy.clip(y0, 0, h - 1), numpy.clip(y0 + 1, 0, h - 1))
+    rows = src[:, x0] * ax0[None, :, None] + src[:, x1] * ax1[None, :, None]
+    out = (((ay0[:, None, None] * (rows[y0] >> 4)) >> 16) + ((ay1[:, None, None] * (rows[y1] >> 4)) >> 16) + 2) >> 2
+    return out.astype(numpy.uint8).reshape((h * scale, w * scale) + img.shape[2:])
+
+
+def scale_image(img: numpy.ndarray, scale: int) -> numpy.ndarray:
+    """``scale_image`` of the reference (``_utils.py:57-61``)."""
+    return resize_linear(img, scale)
 
 
 def window_to_mask(words: numpy.ndarray, win_x0: int, win_y0: int, shape: Tuple[int, int]) -> numpy.ndarray:
@@ -102,6 +158,7 @@ def read_with_taps(engine: _engine.Engine, frames: numpy.ndarray) -> Tuple[numpy
 
 def paint_frame(params: _Params, engine: _engine.Engine, crop: numpy.ndarray, record: Any,
                 needle_words: numpy.ndarray, counts: numpy.ndarray, momentum: numpy.ndarray,
+                hls: Optional[numpy.ndarray] = None,
                 ) -> Tuple[Optional[numpy.ndarray], List[Tuple[str, numpy.ndarray]]]:
     """(debug image of the dials rect, [(dial name, 4x picture after that dial)]) for one frame;
     (None, []) when the dials were not found (the reference raises before any window opens)."""
@@ -109,7 +166,13 @@ def paint_frame(params: _Params, engine: _engine.Engine, crop: numpy.ndarray, re
         return (None, [])
     (th, tw) = params.dials_template_size                 # (rows, columns), like ndarray.shape
     (mx, my) = (int(record['match_x']), int(record['match_y']))
-    debug = numpy.array(crop[my:my + th, mx:mx + tw], dtype=numpy.uint8)
+    if hls is None:
+        from ._utils import convert_to_hls
+        hls = convert_to_hls(numpy.ascontiguousarray(crop), params.hue_shift)
+    # convert_to_bgr (_utils.py:105-110): the hue shift taken off again (wrapping u8), HLS -> BGR
+    dials_hls = numpy.array(hls[my:my + th, mx:mx + tw], dtype=numpy.uint8)
+    dials_hls[..., 0] -= numpy.uint8(params.hue_shift)
+    debug = hls_to_bgr_full(dials_hls)
     (h, w) = debug.shape[:2]
     per_dial: List[Tuple[str, numpy.ndarray]] = []
     for (d, (name, dial)) in enumerate(get_dial_data(params).items()):
@@ -161,6 +224,8 @@ def write_overlays(params: _Params, engine: _engine.Engine, frames: numpy.ndarra
             written.append('{}.dial-{}.png'.format(stem, name))
             with open(written[-1], 'wb') as fp:
                 fp.write(encode_png(picture))
+        if int(records[i]['status']) != _engine.ST_OK:
+            continue                      # the reference raises before its last imshow (_reading.py:98-106)
         written.append(stem + '.png')
         with open(written[-1], 'wb') as fp:
             fp.write(encode_png(scale_image(debug, 2)))

@@ -246,6 +246,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             MELF_CUDA(ctx, cudaMemsetAsync(d_tl, 0, 64 * sizeof(long long), stream));
             t.timeline = d_tl;
         }
+        if (const char *skip = std::getenv("MELF_TC_DEBUG_SKIP")) t.debug_skip = std::atoi(skip);
         // default: drain of pass k under the MMAs of pass k + 1 (three TMEM accumulators);
         // MELF_MATCH_OVERLAP=0 selects the kernel with the drain between the passes (A/B runs)
         static const bool overlap = !(std::getenv("MELF_MATCH_OVERLAP") && !std::atoi(std::getenv("MELF_MATCH_OVERLAP")));

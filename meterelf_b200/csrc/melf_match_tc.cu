@@ -164,6 +164,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[33])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld1(uint32_t taddr, uint32_t &v)
 {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr));
@@ -684,6 +696,15 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
 // =======================================================================================
 namespace {
 
+#ifndef MELF_DRAIN_WIDE
+#define MELF_DRAIN_WIDE 0     // 1: 32 accumulator columns per tcgen05.ld, no prefetch -- measured no faster (drain 19-23 k clk per
+#endif                        // pass against 17-21 k, profiles/r02_timeline_b_*.txt): the drain is not bound by the number of TMEM loads
+#ifndef MELF_STAGE_RING
+#define MELF_STAGE_RING 0     // 1: BGR rows reach the workers through a cp.async ring in shared memory -- measured SLOWER (staging
+#endif                        // 55 k clk per pass against 48 k, profiles/r02_timeline_c_*.txt): global-load latency is not what binds it
+#ifndef MELF_STAGE_L2_PREFETCH
+#define MELF_STAGE_L2_PREFETCH 0   // 1: crop rows of the next pass prefetched into L2 before the window sums of this one -- measured
+#endif                             // no gain (staging 46 k clk instead of 49 k, but the pass 96 k instead of 91 k: profiles/r02_timeline_e_*.txt)
 #ifndef MELF_F_NSTAGE
 #define MELF_F_NSTAGE 2
 #define MELF_F_KSTEPS 8
@@ -693,8 +714,16 @@ constexpr int F_KSTEPS = MELF_F_KSTEPS;                       // K-steps (of 32)
 constexpr int F_STAGE_BYTES = 2 * F_KSTEPS * BSTRIP_BYTES;    // 4096 per K-step
 constexpr int F_SMEM_B = 2 * SLAB_BYTES;                      // 135168
 constexpr int F_SMEM_H = F_SMEM_B + F_NSTAGE * F_STAGE_BYTES; // H table, 256 rows x 16 words, + segment totals
-constexpr int F_SMEM_CTRL = F_SMEM_H + 16384 + 4096;
+// behind the H table: the rest of the 227 KB, together the staging ring of the BGR rows (the window
+// sums and the staging are consecutive phases of the same warps, so they can share the bytes)
+constexpr int F_RING_AREA = 232448 - 512 - F_SMEM_H;          // 31232
+constexpr int F_SMEM_CTRL = F_SMEM_H + F_RING_AREA;
 constexpr int F_SMEM_TOTAL = F_SMEM_CTRL + 512;
+constexpr int RING_ROWS = 16;                                 // slab rows per ring buffer
+constexpr int RING_PITCH = 784;                               // 750-byte rows at any 16-byte phase: 49 chunks
+constexpr int RING_CHUNKS = RING_PITCH / 16;
+constexpr int RING_BUF_BYTES = RING_ROWS * RING_PITCH;        // 12544
+static_assert(2 * RING_BUF_BYTES <= F_RING_AREA && 16384 + 4096 <= F_RING_AREA, "ring / H table do not fit");
 constexpr int F_WORKERS = TC_THREADS - 64;                    // warps 2..15
 constexpr int F_WORKER_WARPS = F_WORKERS / 32;
 constexpr size_t F_SCRATCH_PER_CTA = 2 * (size_t)SLAB_BYTES + 2 * (size_t)WSUM_WORDS * 4;
@@ -983,6 +1012,32 @@ __device__ __forceinline__ void window_sums(const MelfMatchTcArgs &A, const Item
     }
 }
 
+// The crop rows of the items of a LATER pass pulled from DRAM into L2 (one bulk prefetch per row), issued a
+// whole window-sum phase before stage_slabs reads them: ncu's source view had 25 % of all stall samples of
+// the kernel on the first use of stage_unit_f's global loads (long scoreboard, profiles/r02_ncu_locate_straight_source.txt)
+// -- DRAM latency with 14 warps and one unit in flight per lane.  Called by all F_WORKERS threads.
+__device__ __forceinline__ void prefetch_items_l2(const MelfMatchTcArgs &A, const Item (&its)[2], int wt)
+{
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int row_bytes = A.channels * min(KS * 16, A.geom.crop_w - it.x0);
+        const uint8_t *base = A.img + (size_t)it.frame * A.frame_stride + (size_t)(A.geom.crop_y0 + it.y0) * A.row_stride +
+                              (size_t)A.channels * (size_t)(A.geom.crop_x0 + it.x0);
+        for (int r = wt; r < n_rows; r += F_WORKERS) {
+            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)r * A.row_stride);
+            const uintptr_t a16 = src & ~(uintptr_t)15;
+            uintptr_t end = (src + (uintptr_t)row_bytes + 15) & ~(uintptr_t)15;
+            if (end > limit) end = limit;
+            if (end > a16)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(a16), "r"((uint32_t)(end - a16)) : "memory");
+        }
+    }
+}
+
 // lightness slabs of the (up to two) items of one pass -> this CTA's global scratch
 __device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item (&its)[2], uint8_t *scratch,
                                             int wwarp, int lane, int n_wwarps = F_WORKER_WARPS)
@@ -1016,6 +1071,101 @@ __device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item
             }
 #endif
             stg_keep(reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16), stage_unit_f(A, it, r, s, pol_stream), pol_keep);
+        }
+    }
+}
+
+// stage_slabs with the frame bytes passing through shared memory: every group of RING_ROWS crop rows is
+// fetched with cp.async (16-byte chunks, no registers held while the bytes are in flight) into one of two
+// ring buffers while the previous group is converted out of the other.  The straight version waits ~2.6 k
+// clk per unit on its global loads (24 % of all stall samples sat on their first use, profiles/
+// r01_v9_ncu_match_fused.txt); here the conversion reads shared memory and the latency of group g + 1 hides
+// behind the conversion of group g.  Called by all F_WORKERS threads.
+__device__ __forceinline__ void stage_slabs_ring(const MelfMatchTcArgs &A, const Item (&its)[2], uint8_t *scratch,
+                                                 uint8_t *ring, int wt)
+{
+    const uint32_t ring_s = smem_u32(ring);
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int n_groups = (n_rows + RING_ROWS - 1) / RING_ROWS;
+        const int n_px = min(KS * 16, A.geom.crop_w - it.x0);                 // pixels of a row that a slab can hold
+        const int row_bytes = A.channels * n_px;
+        const uint8_t *base = A.img + (size_t)it.frame * A.frame_stride + (size_t)(A.geom.crop_y0 + it.y0) * A.row_stride +
+                              (size_t)A.channels * (size_t)(A.geom.crop_x0 + it.x0);
+        uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        const u64 pol_keep = policy_evict_last();
+        auto issue = [&](int g) {
+            const uint32_t buf = ring_s + (uint32_t)(g & 1) * RING_BUF_BYTES;
+            for (int i = wt; i < RING_ROWS * RING_CHUNKS; i += F_WORKERS) {
+                const int r = i / RING_CHUNKS, c = i - r * RING_CHUNKS;
+                const int row = g * RING_ROWS + r;
+                if (row >= n_rows) continue;
+                const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)row * A.row_stride);
+                const uintptr_t a16 = (src & ~(uintptr_t)15) + 16u * (uintptr_t)c;
+                if (a16 >= src + (uintptr_t)row_bytes) continue;               // behind the last byte needed
+                // bytes behind the end of the frame memory are not read (zero fill)
+                // (the bytes needed lie inside the frame memory, the tail of their last chunk may not: zero fill)
+                const uint32_t n_src = a16 + 16 <= limit ? 16u : (uint32_t)(limit - a16);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                             :: "r"(buf + (uint32_t)(r * RING_PITCH + 16 * c)), "l"(a16), "r"(n_src) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        issue(0);
+#pragma unroll 1
+        for (int g = 0; g < n_groups; ++g) {
+            if (g + 1 < n_groups) issue(g + 1); else asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            worker_sync();                                   // everybody's chunks of group g have landed
+            if (wt < RING_ROWS * KS) {
+                // unit = 16 pixels; lane = (strip & 3) * 8 + row & 7: a quarter warp stores 128 contiguous bytes
+                const int r = (wt & 7) + 8 * (wt >> 7), sidx = (wt >> 3) & 15;
+                const int row = g * RING_ROWS + r;
+                if (row < ((n_rows + 7) & ~7)) {
+                    uint4 out = make_uint4(0, 0, 0, 0);
+                    if (row < n_rows && 16 * sidx < n_px) {
+                        const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)row * A.row_stride);
+                        const uint32_t pos = (uint32_t)(src & 15) + (uint32_t)(A.channels * 16 * sidx);   // byte in the ring row
+                        const uint8_t *rp = ring + (g & 1) * RING_BUF_BYTES + r * RING_PITCH + (pos & ~15u);
+                        const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
+                        uint32_t e[17];
+#pragma unroll
+                        for (int cidx = 0; cidx < 4; ++cidx) {
+                            uint4 q = make_uint4(0, 0, 0, 0);
+                            if (cidx < (A.channels == 3 ? 4 : 2) && (int)(pos >> 4) + cidx < RING_CHUNKS)
+                                q = *reinterpret_cast<const uint4 *>(rp + 16 * cidx);
+                            e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+                        }
+                        e[16] = 0;
+                        uint32_t v[12];
+                        switch (ws) {
+                        case 0:
+#pragma unroll
+                            for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j], e[j + 1], bs);
+                            break;
+                        case 1:
+#pragma unroll
+                            for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 1], e[j + 2], bs);
+                            break;
+                        case 2:
+#pragma unroll
+                            for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 2], e[j + 3], bs);
+                            break;
+                        default:
+#pragma unroll
+                            for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 3], e[j + 4], bs);
+                            break;
+                        }
+                        out = A.channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
+                    }
+                    stg_keep(reinterpret_cast<uint4 *>(dst + sidx * STRIP_BYTES + row * 16), out, pol_keep);
+                }
+            }
+            worker_sync();                                   // the buffer may be refilled
         }
     }
 }
@@ -1462,7 +1612,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
                 if (tl) waited += clock64() - w0;
                 const int kk0 = s * F_KSTEPS;                                     // first K-step of the stage
                 const uint32_t abase = b_addr + st * F_STAGE_BYTES;               // Toeplitz K-steps = A
-                if (lead && items[0].valid) {
+                if (lead && items[0].valid && !(A.debug_skip & 8)) {
 #pragma unroll
                     for (int j = 0; j < F_KSTEPS; ++j) {
                         const int kk = kk0 + j;
@@ -1480,7 +1630,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
                     tc_fence_after();
                 }
                 if (lead) {
-                    if (items[1].valid) {
+                    if (items[1].valid && !(A.debug_skip & 8)) {
 #pragma unroll
                         for (int j = 0; j < F_KSTEPS; ++j) {
                             const int kk = kk0 + j;
@@ -1521,7 +1671,11 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
             // prologue: slabs of this CTA's first pass
             Item its[2];
             pass_items(blockIdx.x, its);
+#if MELF_STAGE_RING
+            stage_slabs_ring(A, its, scratch, smem + F_SMEM_H, wt);
+#else
             stage_slabs(A, its, scratch, wwarp, lane);
+#endif
             fence_async_all();
             mbar_arrive(smem_u32(&ctrl->prep_done));
         }
@@ -1534,18 +1688,29 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
             uint32_t *wsum = wsum_base + (pc & 1) * 2 * WSUM_WORDS;
 
             // ---- window sums of this pass, slabs of the next one ----------------------------------
+#if MELF_STAGE_L2_PREFETCH
+            if (has_next) {
+                Item nxt[2];
+                pass_items(pass + gridDim.x, nxt);
+                prefetch_items_l2(A, nxt, wt);
+            }
+#endif
             mbar_wait(smem_u32(&ctrl->slab_full), pc & 1);
 #pragma unroll 1
             for (int slot = 0; slot < 2; ++slot) {
                 const Item cur = slot ? items[1] : items[0];
-                if (cur.valid)
+                if (cur.valid && !(A.debug_skip & 2))
                     window_sums(A, cur, smem + SMEM_SLABS + slot * SLAB_BYTES, Htab, wsum + slot * WSUM_WORDS, wt);
             }
             if (tl && wt == 0) tl[6] = clock64();
-            if (has_next) {
+            if (has_next && !(A.debug_skip & 1)) {
                 Item nxt[2];
                 pass_items(pass + gridDim.x, nxt);
+#if MELF_STAGE_RING
+                stage_slabs_ring(A, nxt, scratch, smem + F_SMEM_H, wt);
+#else
                 stage_slabs(A, nxt, scratch, wwarp, lane);
+#endif
             }
             if (tl && wt == 0) tl[7] = clock64();
             fence_async_all();
@@ -1565,6 +1730,53 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
                 float *map = WRITE_MAP ? A.result + (size_t)it.frame * A.geom.res_w * A.geom.res_h : nullptr;
                 long long best_num = kNone;
                 uint32_t best_idx = 0;
+                if (A.debug_skip & 4) {
+                    // measurement only: accumulators are not read
+                } else
+#if MELF_DRAIN_WIDE
+                if (it.valid) {
+                    // 32 result rows per step: one x32 (+ x1) accumulator load instead of two x16 (+ x1) -- every
+                    // tcgen05.ld queues behind the MMAs in flight, so fewer, larger loads wait less often; the
+                    // even lane of a pair scores rows +0..15, the odd lane rows +16..31
+                    const int n_wide = (it.n_cols + 31) >> 5;
+                    uint32_t sw_nx[16];
+                    auto fetch_s = [&](int c) {
+                        const int y0c = 32 * c + 16 * odd;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            sw_nx[j] = (c < n_wide && col_ok && y0c + j < it.h_c) ? __ldcg(S + (y0c + j) * 64) : 0u;
+                    };
+                    fetch_s(q_index);
+#pragma unroll 1
+                    for (int c = q_index; c < n_wide; c += q_members) {
+                        const int yl0 = 32 * c + 16 * odd;
+                        uint32_t d[33], sw[16];
+                        tmem_ld32(taddr + 32 * c, d);
+                        tmem_ld1(taddr + 32 * c + 32, d[32]);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) sw[j] = sw_nx[j];
+                        fetch_s(c + q_members);
+                        tmem_ld_wait();
+                        uint32_t idx = (uint32_t)(it.y0 + yl0) * (uint32_t)A.geom.res_w + (uint32_t)(it.x0 + x);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j, idx += (uint32_t)A.geom.res_w) {
+                            // even sends D[2x][y0+16+j] and receives D[2x+1][y0+j+1]; odd the other way round
+                            const uint32_t other = __shfl_xor_sync(0xffffffffu, odd ? d[j + 1] : d[16 + j], 1);
+                            const uint32_t mine = odd ? d[17 + j] : d[j];
+                            const long long num = (long long)((u64)n_t32 * (u64)(mine + other)) -
+                                                  (long long)((u64)sum_t32 * (u64)sw[j]);
+                            const bool ok = col_ok && yl0 + j < it.h_c;
+                            if (WRITE_MAP) { if (ok) map[idx] = score_of(num, A.n_t); }
+                            const long long gain = num - best_num;
+                            bool take = ok && gain > far;
+                            if (ok && gain > 0 && !take)
+                                take = score_of(num, A.n_t) > score_of(best_num, A.n_t);
+                            best_num = take ? num : best_num;
+                            best_idx = take ? idx : best_idx;
+                        }
+                    }
+                }
+#else
                 if (it.valid) {
                     // the window sums of a chunk are fetched (L2) while the previous chunk is scored
                     uint32_t sw_nx[8];
@@ -1616,6 +1828,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
                         }
                     }
                 }
+#endif
                 // this warp is done with the slot's accumulator
                 tc_fence_before();
                 __syncwarp();

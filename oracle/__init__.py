@@ -338,6 +338,10 @@ def build_ref(force: bool = False) -> Optional[str]:
             shutil.rmtree(dst)
         os.makedirs(REF_DIR, exist_ok=True)
         shutil.copytree(src, dst, ignore=shutil.ignore_patterns('__pycache__', '*.pyc'))
+        # the reference's own test file, run unchanged against the drop-in by
+        # tests/test_dropin_reference_suite.py (the sample files come from the golden fixtures)
+        os.makedirs(os.path.join(REF_DIR, 'tests'), exist_ok=True)
+        shutil.copy(os.path.join(REF_SOURCE, 'tests', 'test_meterelf.py'), os.path.join(REF_DIR, 'tests'))
     return REF_DIR if os.path.isdir(dst) else None
 
 

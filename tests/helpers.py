@@ -224,6 +224,30 @@ def jpeg_colour_space_bases():
     return [(n, blob[off[names.index(n)]:off[names.index(n) + 1]]) for n in JPEG_COLOUR_SPACE_BASES]
 
 
+# frames whose debug pictures tests/golden/make_golden_overlay.py captured from the reference:
+# sample crops by file name, synthetic blob frames by (case of SYNTHETIC_CASES, index)
+OVERLAY_CASES = [
+    dict(key='set1:20180814215230-01-e136.jpg', set=1, name='20180814215230-01-e136.jpg', threshold=None),
+    dict(key='set2:20181001_113527-01-e14.jpg', set=2, name='20181001_113527-01-e14.jpg', threshold=None),
+] + [dict(key='%s[%d]' % (case, i), set=set_no, synthetic=(case, i), threshold=-1e30)
+     for (case, set_no, picks) in (('set2_seed5', 2, (2, 3, 5, 8, 13, 21, 24, 30, 34)), ('set3_seed6', 3, (2, 4, 7, 11, 16, 31)),
+                                   ('set1_seed7', 1, (3, 6, 9, 10, 14, 20)))
+     for i in picks]
+
+
+def overlay_case_frame(case):
+    """The meter_rect crop of one OVERLAY_CASES entry."""
+    gs = golden_set(case['set'])
+    if 'name' in case:
+        sub = gs.subset()
+        names = [str(n) for n in sub['names']]
+        return np.ascontiguousarray(sub['crops'][names.index(case['name'])])
+    (key, index) = case['synthetic']
+    (seed, n) = next((c[2], c[3]) for c in SYNTHETIC_CASES if c[0] == key)
+    (x0, y0, x1, y1) = gs.meter_rect
+    return np.ascontiguousarray(synthetic_batch(seed, n, y1 - y0, x1 - x0)[index])
+
+
 def jpeg_colour_space_variants(data):
     """[(key, bytes, libjpeg reads it as RGB)] -- one baseline 3-component stream re-labelled so
     that libjpeg's colour space choice (jdapimin.c default_decompress_parms) takes each of its
@@ -277,7 +301,7 @@ def jpeg_colour_space_variants(data):
     ]
 
 
-def write_params_file(gs, directory):
+def write_params_file(gs, directory, image_glob='*.png'):
     """params.yml + dials.png for golden set `gs` in `directory` (no reference tree needed);
     returns the path of params.yml."""
     import cv2
@@ -290,7 +314,7 @@ def write_params_file(gs, directory):
         diameter=int(gs.diameters[i]), negative_momentum=gs.dials[i]['negative_momentum'])
         for i in range(len(gs.names))]
     (x0, y0, x1, y1) = gs.meter_rect
-    doc = dict(image_glob='*.png', meter_rect=dict(top_left=[x0, y0], bottom_right=[x1, y1]),
+    doc = dict(image_glob=image_glob, meter_rect=dict(top_left=[x0, y0], bottom_right=[x1, y1]),
                dials_template='dials.png', dials_template_match_threshold=int(gs.match_threshold),
                dials_template_size=[gs.tmpl_w, gs.tmpl_h], hue_shift=gs.hue_shift,
                needle_color=dict(h=125, l=80, s=130), needle_color_range=dict(h=9, l=45, s=35),

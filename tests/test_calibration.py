@@ -56,6 +56,44 @@ def test_oracle_average_matches_reference_on_all_files():
     assert np.array_equal(avg, G['full_avg'])
 
 
+def test_outer_borders_and_fit_ellipse_are_cv2s():
+    """The cv2-free contour following and conic fit of the product's calibration
+    (``meterelf_b200/_calibration.py``) against ``cv2.findContours(RETR_EXTERNAL, CHAIN_APPROX_NONE)``
+    point for point (nested components dropped, frame pixels included) and ``cv2.fitEllipse``."""
+    cv2 = pytest.importorskip('cv2')
+    from meterelf_b200 import _calibration as cal
+    rng = np.random.default_rng(0)
+    n_fits = 0
+    for it in range(160):
+        (h, w) = (int(rng.integers(25, 80)), int(rng.integers(25, 100)))
+        c = int(rng.integers(1, 6))
+        m = np.kron(rng.random((h // c + 2, w // c + 2)) < rng.uniform(0.2, 0.7), np.ones((c, c), bool))[:h, :w]
+        m = m.astype(np.uint8) * 255
+        blobs = it % 2 == 0
+        if blobs:                                     # hub-like shapes: filled ellipses, some overlapping
+            m[:] = 0
+            for _ in range(3):
+                cv2.ellipse(m, (int(rng.integers(10, w)), int(rng.integers(10, h))),
+                            (int(rng.integers(3, 12)), int(rng.integers(3, 12))), float(rng.uniform(0, 180)),
+                            0, 360, 255, -1)
+        want = cv2.findContours(m, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_NONE)[-2]
+        got = cal.outer_borders(m)
+        assert len(got) == len(want), it
+        for (g, r) in zip(got, want):
+            r = r.reshape(-1, 2)
+            assert np.array_equal(g, r), it
+            if blobs and len(r) >= 12:
+                (rc, rs, _ra) = cv2.fitEllipse(r)
+                if min(rs) < 4:
+                    continue
+                (gc, gsz, _ga) = cal.fit_ellipse(g)
+                n_fits += 1
+                assert np.allclose(gc, rc, atol=1e-4) and np.allclose(gsz, rs, atol=1e-4), (it, gc, rc, gsz, rs)
+    assert n_fits > 100
+    with pytest.raises(ValueError):
+        cal.fit_ellipse(np.zeros((4, 2)))
+
+
 def _params(tmp_path):
     from meterelf_b200 import _params
     return _params.load(write_params_file(golden_set(1), tmp_path))
@@ -70,7 +108,7 @@ def test_gpu_average_and_centers_match_reference_on_subset(tmp_path):
     assert avg.dtype == np.uint8 and np.array_equal(avg, G['subset_avg'])
     centers = _calibration.find_dial_centers_from_image(params, avg)
     assert [c.diameter for c in centers] == [int(d) for d in G['subset_diameters']]
-    # cv2.fitEllipse runs on the host on identical contours: float32 results, identical up to noise
+    # the product's own conic fit on the product's own contours: float32 results like cv2.fitEllipse's
     assert np.allclose(np.array([c.center for c in centers]), G['subset_centers'], atol=1e-3)
     assert centers == sorted(centers, key=lambda c: c.center[0])
 

@@ -9,6 +9,8 @@ the coarse momentum direction (CUDA libm vs glibc), which feeds a < 0.25 compari
 never the result itself.
 """
 import ctypes as C
+import hashlib
+import json
 import os
 
 import numpy as np
@@ -309,6 +311,54 @@ def test_match_template_gray_sizes_and_ties(h, w):
     assert tuple(d_xy[2].cpu().numpy()) == (tx, ty)
 
 
+def test_operators_with_the_reference_signatures(tmp_path):
+    """``match_template(img, template)`` with ANY template (``_utils.py:91-97``),
+    ``get_mask_by_color(hls_image, color, color_range)`` on an HLS image (``_utils.py:113-119``),
+    ``ImageFile._find_dials(img_hls)`` and ``ImageFile.get_bgr_image_t()`` (``_image.py:34-66``)."""
+    from helpers import write_params_file
+    from meterelf_b200 import _colors, _image, _params, _utils
+    from meterelf_b200.exceptions import DialsNotFoundError
+    rng = np.random.default_rng(12)
+    for (ih, iw, th, tw) in ((40, 60, 9, 13), (64, 64, 64, 64), (90, 300, 31, 200), (140, 130, 129, 40)):
+        img = rng.integers(0, 256, (ih, iw), dtype=np.uint8)
+        tmpl = rng.integers(0, 256, (th, tw), dtype=np.uint8)
+        got = _utils.match_template(img, tmpl)
+        (x, y, val, _map) = oracle.match_template(img, tmpl, want_map=False)
+        assert got.rect == ((x, y), (x + tw, y + th)) and np.float32(got.max_val) == val, (ih, iw, th, tw)
+    with pytest.raises(ValueError):
+        _utils.match_template(np.zeros((5, 5), np.uint8), np.zeros((6, 3), np.uint8))
+    for (h, w) in ((1, 1), (7, 16), (33, 250), (119, 188)):
+        hls = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        for (color, crange) in (((125, 80, 130), (9, 45, 35)), ((3, 250, 128), (12, 35, 255)), ((0, 0, 0), (0, 0, 0))):
+            (c, r) = (_colors.HlsColor(*color), _colors.HlsColor(*crange))
+            got = _utils.get_mask_by_color(hls, c, r)
+            (lo, hi) = c.get_range(r)
+            want = np.all((hls >= np.array(lo)) & (hls <= np.array(hi)), axis=2).astype(np.uint8) * 255
+            assert got.dtype == np.uint8 and np.array_equal(got, want), (h, w, color)
+    gs = golden_set(1)
+    params = _params.load(write_params_file(gs, tmp_path))
+    sub = gs.subset()
+    names = [str(n) for n in sub['names']]
+    crop = sub['crops'][names.index('20180814215230-01-e136.jpg')]
+    imgf = _image.ImageFile('x.jpg', params, crop)
+    hls = oracle.convert_to_hls(crop, gs.hue_shift)
+    (x, y, val, _map) = oracle.match_template(np.ascontiguousarray(hls[:, :, 1]), gs.template, want_map=False)
+    found = imgf._find_dials(hls)
+    assert found.rect.top_left == (x, y) and np.float32(found.max_val) == val
+    moved = imgf.get_bgr_image_t()
+    (dx, dy) = (30 - x, 116 - y)
+    want = np.zeros_like(crop)
+    (h, w) = crop.shape[:2]
+    want[max(0, dy):min(h, h + dy), max(0, dx):min(w, w + dx)] = crop[max(0, -dy):min(h, h - dy), max(0, -dx):min(w, w - dx)]
+    assert np.array_equal(moved, want)
+    import cv2
+    m = np.array([[1, 0, dx], [0, 1, dy]], dtype=np.float32)
+    assert np.array_equal(moved, cv2.warpAffine(crop, m, (w, h)))             # what the reference computes
+    dark = _image.ImageFile('dark.jpg', params, np.zeros_like(crop))
+    with pytest.raises(DialsNotFoundError):
+        dark._find_dials(np.zeros_like(crop))
+
+
 # ---------------------------------------------------------------------------------------
 # the Python drop-in layer on top of the C ABI
 # ---------------------------------------------------------------------------------------
@@ -495,22 +545,56 @@ def test_debug_overlays_are_written_as_png_files(tmp_path, monkeypatch):
     assert files == sorted(['a.png.png'] + ['a.png.dial-%s.png' % n for n in gs.names])
     final = cv2.imread(str(out_dir / 'a.png.png'))
     assert final.shape == (2 * gs.tmpl_h, 2 * gs.tmpl_w, 3)
-    small = final[::2, ::2]
-    assert np.array_equal(small, final[1::2, 1::2])
-    # the painted pixel counts are the tap counts of the same frame
-    params = _params.load(params_file)
-    eng = _reading.get_engine(params, cropped_input=True)
-    (records, taps) = _overlay.read_with_taps(eng, crop[None])
-    assert int(records[0]['status']) == 0
-    kept = int((small == np.array(_overlay.BGR_RING_KEPT, np.uint8)).all(axis=2).sum())
-    assert kept == int(taps['counts'][0, :, 1].sum()) > 0
-    assert (small == np.array(_overlay.BGR_NEEDLE, np.uint8)).all(axis=2).sum() > 100
-    (mx, my) = (int(records[0]['match_x']), int(records[0]['match_y']))
-    untouched = (small == crop[my:my + gs.tmpl_h, mx:mx + gs.tmpl_w]).all(axis=2)
-    assert untouched.mean() > 0.8                        # the background is the decoded crop itself
     last = cv2.imread(str(out_dir / ('a.png.dial-%s.png' % gs.names[-1])))
     assert last.shape == (4 * gs.tmpl_h, 4 * gs.tmpl_w, 3)
-    assert (last == np.array(_overlay.BGR_MAGENTA, np.uint8)).all(axis=2).sum() >= 20
+    # the files hold exactly what the reference showed for this frame (overlay_expected.json)
+    with open(os.path.join(GOLDEN, 'overlay_expected.json')) as fp:
+        exp = {e['case']: e for e in json.load(fp)}['set1:20180814215230-01-e136.jpg']
+    shown = [cv2.imread(str(out_dir / ('a.png.dial-%s.png' % n))) for n in gs.names] + [final]
+    assert [hashlib.sha256(np.ascontiguousarray(img).tobytes()).hexdigest() for img in shown] == [
+        w['sha256'] for w in exp['windows']]
+
+
+def test_debug_pictures_equal_what_the_reference_shows(tmp_path):
+    """SURVEY 8f-4 pinned to the reference: the arrays the unmodified reference hands to cv2.imshow in
+    debug mode (captured by tests/golden/make_golden_overlay.py with cv2.imshow mocked, as the
+    reference's own tests do) against _overlay.paint_frame -- per-dial 4x pictures and the final 2x
+    picture, sample frames of both sets and synthetic frames ending in every status."""
+    from helpers import OVERLAY_CASES, overlay_case_frame, write_params_file
+    from meterelf_b200 import _overlay, _params, _reading
+    with open(os.path.join(GOLDEN, 'overlay_expected.json')) as fp:
+        expected = {e['case']: e for e in json.load(fp)}
+    loaded = {}
+    n_windows = 0
+    seen = set()
+    for case in OVERLAY_CASES:
+        exp = expected[case['key']]
+        if exp['status'] < 0:
+            continue                     # the reference's debug mode crashes on this frame (zero momentum)
+        key = (case['set'], case['threshold'])
+        if key not in loaded:
+            d = tmp_path / ('p%d' % len(loaded))
+            d.mkdir()
+            params = _params.load(write_params_file(golden_set(case['set']), d))
+            if case['threshold'] is not None:
+                params.dials_match_threshold = case['threshold']
+            loaded[key] = (params, _reading.get_engine(params, cropped_input=True))
+        (params, eng) = loaded[key]
+        frame = overlay_case_frame(case)
+        (records, taps) = _overlay.read_with_taps(eng, frame[None])
+        assert int(records[0]['status']) == exp['status'], case['key']
+        (debug, per_dial) = _overlay.paint_frame(params, eng, frame, records[0], taps['needle_mask'][0],
+                                                 taps['counts'][0], taps['momentum'][0])
+        shown = [img for (_name, img) in per_dial]
+        if exp['status'] == 0:
+            shown.append(_overlay.scale_image(debug, 2))
+        assert len(shown) == len(exp['windows']), case['key']
+        for (k, (img, w)) in enumerate(zip(shown, exp['windows'])):
+            assert list(img.shape) == w['shape'], (case['key'], k)
+            assert hashlib.sha256(np.ascontiguousarray(img).tobytes()).hexdigest() == w['sha256'], (case['key'], k)
+            n_windows += 1
+        seen.add(exp['status'])
+    assert seen == {0, 2, 3} and n_windows >= 60
 
 
 @pytest.mark.parametrize('hue_shift,lo,hi', [

@@ -175,8 +175,29 @@ def test_debug_overlay_helpers(monkeypatch):
         assert np.array_equal(cv2.imdecode(np.frombuffer(png, np.uint8), cv2.IMREAD_COLOR), img)
     except ImportError:
         pass
+    # scale_image = cv2.resize's fixed-point bilinear filter (_utils.py:57-61), hls_to_bgr_full =
+    # cv2.cvtColor(HLS2BGR_FULL) in the operation order of OpenCV's vectorised code
     big = _overlay.scale_image(img, 4)
-    assert big.shape == (52, 84, 3) and np.array_equal(big[::4, ::4], img) and np.array_equal(big[3::4, 3::4], img)
+    assert big.shape == (52, 84, 3)
+    try:
+        import cv2
+        cv2.ipp.setUseIPP(False)
+        for (h, w) in ((13, 21), (1, 1), (2, 33), (119, 188)):
+            src = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+            for scale in (2, 4):
+                assert np.array_equal(_overlay.resize_linear(src, scale), cv2.resize(src, (w * scale, h * scale)))
+        (L, S) = np.meshgrid(np.arange(256), np.arange(256), indexing='ij')
+        differing = 0
+        for hue in range(0, 256):
+            hls = np.stack([np.full_like(L, hue), L, S], axis=-1).astype(np.uint8)
+            want = cv2.cvtColor(hls, cv2.COLOR_HLS2BGR_FULL)
+            got = _overlay.hls_to_bgr_full(hls)
+            bad = np.any(got != want, axis=-1)
+            differing += int(bad.sum())
+            assert np.abs(got.astype(int) - want.astype(int)).max() <= 1
+        assert differing <= 8, differing      # 4 of 2^24 colours: float32 near-ties (rint of x.49998 / x.50002)
+    except ImportError:
+        pass
     words = np.zeros(64, np.uint64)
     words[0] = (1 << 3) | (1 << 63)
     words[63] = 1
