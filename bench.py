@@ -452,6 +452,45 @@ def ingest_leg(torch, D, wl, n_streams, reps=3):
                      'then the same locate and dial kernels; GPU-bound (Huffman stage), DESIGN.md section 8'}
 
 
+def api_leg(wl, n_files):
+    """The drop-in call itself: get_meter_values(params_file, filenames) over JPEG FILES (the sample files
+    of set 1 written to a RAM disk, repeated), file reads, header probes, GPU decode + read and the Python
+    objects of every result included (reference: _api.py:16-33, one cv2.imread + get_meter_value per file)."""
+    import shutil
+    from helpers import GOLDEN
+    from test_jpeg_oracle import load_streams
+    import meterelf_b200
+    full = os.path.join(GOLDEN, '_full', 'jpeg_all.npz')
+    streams = load_streams(full if os.path.exists(full) else os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    base = [s for s in streams if s[4] == 1 and s[2] == (640, 480)]
+    root = '/dev/shm' if os.path.isdir('/dev/shm') and os.access('/dev/shm', os.W_OK) else None
+    d = tempfile.mkdtemp(prefix='melf_api_', dir=root)
+    try:
+        paths = []
+        for (k, (name, data, _shape, _sha, _set)) in enumerate(base):
+            paths.append(os.path.join(d, name))
+            with open(paths[-1], 'wb') as fp:
+                fp.write(data)
+        names = [paths[i % len(paths)] for i in range(n_files)]
+        list(meterelf_b200.get_meter_values(wl.params_file, names[:1024]))          # warm-up
+        t0 = time.perf_counter()
+        got = list(meterelf_b200.get_meter_values(wl.params_file, names))
+        dt = time.perf_counter() - t0
+        bad = 0
+        for (i, item) in enumerate(got[:len(base)]):
+            exp = wl.gs.expected[base[i][0]]
+            line = '{:07.3f}'.format(item.value) if item.value else ('UNKNOWN ' + item.error.get_message() if item.error else '')
+            bad += (line != exp['line']) if exp['status'] == 0 else (
+                line.split(' (match val')[0] != exp['line'].split(' (match val')[0])
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    return {'metric': 'get_meter_values(params_file, filenames) over JPEG files on a RAM disk', 'value': n_files / dt,
+            'unit': 'files/s', 'files': n_files, 'seconds': dt, 'golden_line_mismatches': int(bad),
+            'golden_lines_checked': len(base),
+            'note': 'one Python process: file reads and header probes batched on host threads behind the C ABI, '
+                    'results converted once per batch; bound by the host (file system calls, Python objects), not the GPU'}
+
+
 def convert_stage(torch, wl, d_frames, fh, fw, steps, local, peaks, traffic):
     """Stage 1 as a standalone fused pass over full frames (north_star's >= 50 % of HBM target)."""
     from meterelf_b200 import _engine
@@ -716,6 +755,8 @@ def run_ours(args):
     line['set2'] = s2p
     if D.world == 1 and args.micro_bench:
         line['micro_bench'] = micro_bench(torch, wl, local, int8_peak)
+    if D.world == 1 and args.api_files > 0:
+        line['api'] = api_leg(wl, args.api_files)
     emit(line)
     D.close()
     tmp.cleanup()
@@ -783,6 +824,7 @@ def main():
     ap.add_argument('--cpu-frames-per-core', type=int, default=64, help='CPU baseline sample per host core')
     ap.add_argument('--ingest-streams', type=int, default=32768, help='JPEG streams per GPU and step (0 = skip)')
     ap.add_argument('--micro-bench', type=int, default=1)
+    ap.add_argument('--api-files', type=int, default=32768, help='files of the get_meter_values leg (N=1; 0 = skip)')
     args = ap.parse_args()
     protect_stdout()
     if args.impl == 'reference':

@@ -196,6 +196,15 @@ int melf_decode_jpeg(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *offsets
 int melf_jpeg_info(const uint8_t *jpeg, size_t len, int *h, int *w, int *components, int *h_samp,
                    int *v_samp);
 
+/* Host-side batch helpers of get_meter_values' per-file preamble (_api.py:22-27, _image.py:46-51): file
+ * sizes (-1 = cannot be opened), the files' bytes into one blob (ok[i] = 0: short read), and the header
+ * probe of n streams at once: info[8i..] = {h, w, components, h_samp, v_samp, EXIF orientation, end-of-image
+ * marker near the end (0/1), code} with code 0 = melf_read_jpeg_batch takes the stream, else the MELF_ERR_*
+ * melf_jpeg_info returns (such files take the cv2.imread route).  No GPU involved; a few host threads. */
+int melf_file_sizes(const char *const *paths, int n, int64_t *sizes);
+int melf_read_files(const char *const *paths, int n, uint8_t *blob, const uint64_t *offsets, int32_t *ok);
+int melf_jpeg_probe_batch(const uint8_t *jpeg, const uint64_t *offsets, int n, int32_t *info);
+
 /* get_meter_values over JPEG files already read into memory (_api.py:22-33 without the file
  * I/O): decode, crop to meter_rect, locate and read, in pipelined chunks of up to 8192 streams on up
  * to 8 CUDA streams (MELF_JPEG_SLOTS / MELF_JPEG_CHUNK).

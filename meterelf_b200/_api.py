@@ -10,10 +10,12 @@ from typing import Dict, Iterable, Iterator, NamedTuple, Optional
 
 from . import _debug, _params
 from ._image import ImageFile
-from ._reading import read_image_files
+from ._reading import Deferred, read_image_files
 from .exceptions import ImageProcessingError
 
-DEFAULT_BATCH_SIZE = 256
+# files per GPU batch: several waves of the persistent locate kernel (148 CTAs x 2 frames) and one
+# chunk of the JPEG pipeline (8192 streams); ~300 MB of JPEG bytes on the host for the sample files
+DEFAULT_BATCH_SIZE = 8192
 
 
 class MeterImageData(NamedTuple):
@@ -32,7 +34,10 @@ def get_meter_values(params_file: str, filenames: Iterable[str],
         if not chunk:
             return
         imgfs = [ImageFile(filename, params) for filename in chunk]
-        for (imgf, (meter_values, error)) in zip(imgfs, read_image_files(params, imgfs)):
+        for (imgf, item) in zip(imgfs, read_image_files(params, imgfs)):
+            if isinstance(item, Deferred):
+                raise item.error            # where the reference's loop would have raised (_api.py:22-33)
+            (meter_values, error) = item
             if error is not None and _debug.DEBUG:
                 raise error
             yield MeterImageData(imgf.filename, meter_values.get('value'), error, meter_values)

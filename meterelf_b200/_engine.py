@@ -79,7 +79,7 @@ _SYMBOLS = (
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
     'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch',
-    'melf_in_range')
+    'melf_in_range', 'melf_file_sizes', 'melf_read_files', 'melf_jpeg_probe_batch')
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a', 'jpeg_upload', 'jpeg_destuff',
                  'jpeg_huffman', 'jpeg_idct', 'jpeg_color')
@@ -137,6 +137,9 @@ def load_library() -> C.CDLL:
         lib.melf_in_range.argtypes = [
             C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p,
             C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.melf_file_sizes.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_void_p]
+        lib.melf_read_files.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.melf_jpeg_probe_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
         lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
@@ -264,10 +267,15 @@ class Engine:
     def read_jpeg_streams(self, streams: Sequence[bytes]) -> np.ndarray:
         """``get_meter_values`` over JPEG files already read into memory; RESULT_DTYPE[n]."""
         (blob, offsets) = pack_streams(streams)
-        out = np.zeros((len(streams),), RESULT_DTYPE)
-        if len(streams):
+        return self.read_jpeg_blob(blob, offsets)
+
+    def read_jpeg_blob(self, blob: np.ndarray, offsets: np.ndarray) -> np.ndarray:
+        """The same for streams that are already packed: stream i = blob[offsets[i]:offsets[i+1]]."""
+        n = len(offsets) - 1
+        out = np.zeros((n,), RESULT_DTYPE)
+        if n:
             self._check(self.lib.melf_read_jpeg_batch(
-                self._ctx, blob.ctypes.data, offsets.ctypes.data, len(streams), out.ctypes.data))
+                self._ctx, blob.ctypes.data, offsets.ctypes.data, n, out.ctypes.data))
         return out
 
     def decode_jpeg_device(self, blob: np.ndarray, offsets: np.ndarray, h: int, w: int, d_bgr: int,
@@ -328,6 +336,34 @@ def pack_streams(streams: Sequence[bytes]) -> Tuple[np.ndarray, np.ndarray]:
     np.cumsum(sizes, out=offsets[1:])
     blob = np.frombuffer(b''.join(bytes(s) for s in streams) or b'\0', np.uint8)
     return (blob, offsets)
+
+
+def read_files(paths: Sequence[str]) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """The bytes of ``paths`` in one blob: (blob u8, offsets u64[n+1], ok bool[n]); a file that cannot be
+    opened or read in full has ok False and an empty slice (``cv2.imread`` would return None for it)."""
+    lib = load_library()
+    n = len(paths)
+    c_paths = (C.c_char_p * n)(*(os.fsencode(p) for p in paths))
+    sizes = np.zeros((n,), np.int64)
+    lib.melf_file_sizes(c_paths, n, sizes.ctypes.data)
+    offsets = np.zeros(n + 1, np.uint64)
+    np.cumsum(np.maximum(sizes, 0), out=offsets[1:])
+    blob = np.empty((int(offsets[-1]) + 16,), np.uint8)
+    ok = np.zeros((n,), np.int32)
+    lib.melf_read_files(c_paths, n, blob.ctypes.data, offsets.ctypes.data, ok.ctypes.data)
+    return (blob, offsets, (ok != 0) & (sizes >= 0))
+
+
+JPEG_INFO_FIELDS = ('h', 'w', 'components', 'h_samp', 'v_samp', 'orientation', 'has_eoi', 'code')
+
+
+def jpeg_probe_batch(blob: np.ndarray, offsets: np.ndarray) -> np.ndarray:
+    """Header probe of every packed stream (no GPU): int32 (n, 8), columns ``JPEG_INFO_FIELDS``."""
+    n = len(offsets) - 1
+    info = np.zeros((n, 8), np.int32)
+    if n:
+        load_library().melf_jpeg_probe_batch(blob.ctypes.data, offsets.ctypes.data, n, info.ctypes.data)
+    return info
 
 
 def jpeg_info(data: bytes) -> Dict[str, int]:

@@ -74,7 +74,8 @@ struct MelfMatchTcArgs {
     long long item0, max_items;
     long long *timeline;         // optional debug: clock64 stamps of CTA 0's first 8 passes, 8 per pass
     int32_t debug_skip;          // measurement only (MELF_TC_DEBUG_SKIP, results become wrong): bit 0 no staging after
-                                 // the prologue, bit 1 no window sums, bit 2 no drain, bit 3 no MMAs
+                                 // the prologue, bit 1 no window sums, bit 2 no drain, bit 3 no MMAs,
+                                 // bit 4 staging without its global loads, bit 5 staging without the conversion
 };
 
 struct MelfConvertArgs {

@@ -207,3 +207,120 @@ extern "C" int melf_host_dial_tables(const melf_params *P, int d,
     std::memcpy(ring_sqd, rings.sqd.data(), dev.n_ring * sizeof(double));
     return MELF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Host-side batch helpers of the ingest row: what get_meter_values does per file
+// before any pixel exists -- open + read (cv2.imread's file access, _image.py:49) and the header
+// probe that decides whether the GPU decoder may take the stream -- for a whole batch of files on a
+// few host threads, so that the Python layer spends microseconds per batch, not per file.
+// ---------------------------------------------------------------------------------------------
+#include <cstdio>
+#include <thread>
+#include <sys/stat.h>
+
+#include "melf_jpeg.h"
+
+namespace {
+
+template <class F>
+void parallel_for(int n, int max_threads, F body)
+{
+    int nt = (int)std::thread::hardware_concurrency();
+    if (nt < 1) nt = 1;
+    if (nt > max_threads) nt = max_threads;
+    if (nt > (n + 63) / 64) nt = (n + 63) / 64;
+    if (nt <= 1) { for (int i = 0; i < n; i++) body(i); return; }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; t++)
+        pool.emplace_back([=] { for (int i = t; i < n; i += nt) body(i); });
+    for (std::thread &th : pool) th.join();
+}
+
+// EXIF orientation tag (0x0112) of a JPEG stream, 1 when absent: cv2.imread rotates by it, the ingest
+// kernels do not, so anything but 1 stays on the host (same walk as _image.exif_orientation)
+int exif_orientation(const uint8_t *d, size_t len)
+{
+    size_t pos = 2;
+    while (pos + 4 <= len && d[pos] == 0xFF) {
+        const int marker = d[pos + 1];
+        if (marker == 0xDA || marker == 0xD9) break;
+        const size_t size = ((size_t)d[pos + 2] << 8) | d[pos + 3];
+        if (size < 2) break;
+        if (marker == 0xE1 && pos + 2 + size <= len && size >= 2 + 14 && !std::memcmp(d + pos + 4, "Exif\0\0", 6)) {
+            const uint8_t *t = d + pos + 10;
+            const size_t tl = size - 8;
+            const bool le = t[0] == 'I' && t[1] == 'I';
+            auto rd = [&](size_t o, int nb) -> uint32_t {
+                uint32_t v = 0;
+                for (int k = 0; k < nb; k++) v |= (uint32_t)t[o + (le ? k : nb - 1 - k)] << (8 * k);
+                return v;
+            };
+            const size_t ifd = rd(4, 4);
+            if (ifd + 2 > tl) return 1;
+            const int entries = (int)rd(ifd, 2);
+            for (int k = 0; k < entries; k++) {
+                const size_t e = ifd + 2 + 12 * (size_t)k;
+                if (e + 12 > tl) break;
+                if (rd(e, 2) == 0x0112) return (int)rd(e + 8, 2);
+            }
+            return 1;
+        }
+        pos += 2 + size;
+    }
+    return 1;
+}
+
+}  // namespace
+
+extern "C" {
+
+// sizes[i] = size of paths[i] in bytes, or -1 when it cannot be opened (cv2.imread would return None)
+int melf_file_sizes(const char *const *paths, int n, int64_t *sizes)
+{
+    if (n < 0 || (n > 0 && (!paths || !sizes))) return MELF_ERR_INVALID;
+    parallel_for(n, 8, [&](int i) {
+        struct stat st;
+        sizes[i] = (stat(paths[i], &st) == 0 && S_ISREG(st.st_mode)) ? (int64_t)st.st_size : -1;
+    });
+    return MELF_OK;
+}
+
+// file i -> blob[offsets[i] .. offsets[i+1]); ok[i] = 0 when the file could not be read in full
+int melf_read_files(const char *const *paths, int n, uint8_t *blob, const uint64_t *offsets, int32_t *ok)
+{
+    if (n < 0 || (n > 0 && (!paths || !blob || !offsets || !ok))) return MELF_ERR_INVALID;
+    parallel_for(n, 16, [&](int i) {
+        const size_t want = (size_t)(offsets[i + 1] - offsets[i]);
+        ok[i] = 0;
+        if (FILE *fp = std::fopen(paths[i], "rb")) {
+            ok[i] = std::fread(blob + offsets[i], 1, want, fp) == want ? 1 : 0;
+            std::fclose(fp);
+        }
+    });
+    return MELF_OK;
+}
+
+// Header probe of n streams: info[8 i ..] = {h, w, components, h_samp, v_samp, EXIF orientation,
+// end-of-image marker within the last 64 bytes (0/1), code}; code 0 = the GPU decoder takes the stream,
+// else the MELF_ERR_* melf_jpeg_info would return (the file then takes the cv2.imread route).
+int melf_jpeg_probe_batch(const uint8_t *jpeg, const uint64_t *offsets, int n, int32_t *info)
+{
+    if (n < 0 || (n > 0 && (!jpeg || !offsets || !info))) return MELF_ERR_INVALID;
+    parallel_for(n, 8, [&](int i) {
+        const uint8_t *d = jpeg + offsets[i];
+        const size_t len = (size_t)(offsets[i + 1] - offsets[i]);
+        int32_t *o = info + 8 * (size_t)i;
+        int h = 0, w = 0, nc = 0, hs = 0, vs = 0;
+        o[7] = (len >= 2 && d[0] == 0xFF && d[1] == 0xD8) ? melf_jpeg_probe(d, len, &h, &w, &nc, &hs, &vs, nullptr)
+                                                          : MELF_ERR_INVALID;
+        o[0] = h; o[1] = w; o[2] = nc; o[3] = hs; o[4] = vs;
+        o[5] = o[7] == 0 ? exif_orientation(d, len) : 1;
+        int eoi = 0;
+        for (size_t k = len >= 64 ? len - 64 : 0; k + 1 < len; k++)
+            if (d[k] == 0xFF && d[k + 1] == 0xD9) { eoi = 1; break; }
+        o[6] = eoi;
+    });
+    return MELF_OK;
+}
+
+}  // extern "C"

@@ -878,9 +878,15 @@ __device__ __forceinline__ uint4 stage_unit_f(const MelfMatchTcArgs &A, const It
 #pragma unroll
     for (int cidx = 0; cidx < 4; ++cidx) {
         uint4 q = make_uint4(0, 0, 0, 0);
+        if (A.debug_skip & 16) {
+            // measurement only: the conversion without its global loads
+            q = make_uint4((uint32_t)addr * 2654435761u + cidx, (uint32_t)addr ^ 0x9e3779b9u, (uint32_t)(addr >> 3) + 77u * cidx, (uint32_t)addr * 40503u);
+        } else
         if (cidx < nchunk && reinterpret_cast<uintptr_t>(al + cidx) < limit) q = ldg_stream(al + cidx, pol_stream);
         e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
     }
+    if (A.debug_skip & 32)      // measurement only: the global loads without the conversion
+        return make_uint4(e[0] ^ e[4] ^ e[8] ^ e[12], e[1] ^ e[5] ^ e[9] ^ e[13], e[2] ^ e[6] ^ e[10] ^ e[14], e[3] ^ e[7] ^ e[11] ^ e[15]);
     uint32_t v[12];
     // shift right by `off` bytes; the word part is uniform across a warp whenever the row stride
     // is a multiple of 16, so the branches normally do not diverge

@@ -210,3 +210,48 @@ def test_debug_overlay_helpers(monkeypatch):
     assert _overlay.overlay_dir() == '/tmp/x'
     monkeypatch.delenv('MELF_DEBUG_DIR')
     assert _overlay.overlay_dir() is None
+
+
+def test_batch_file_reader_and_header_probe(tmp_path):
+    """melf_file_sizes / melf_read_files / melf_jpeg_probe_batch (the per-file preamble of
+    get_meter_values, batched behind the C ABI) against the one-stream Python forms."""
+    import os
+    from helpers import GOLDEN, jpeg_colour_space_bases, jpeg_colour_space_variants
+    from test_jpeg_oracle import load_streams
+    from meterelf_b200 import _engine, _image
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    cases = [(name, data) for (name, data, _s, _h, _n) in streams]
+    (name0, data0) = cases[0]
+    cases.append(('cut.jpg', data0[:len(data0) // 2]))                  # no end-of-image marker
+    cases.append(('head.jpg', data0[:100]))                             # headers cut short
+    cases.append(('not.jpg', b'\x89PNG\r\n\x1a\n' + b'\0' * 64))
+    cases.append(('empty.jpg', b''))
+    prog = bytearray(data0)
+    prog[prog.find(b'\xff\xc0') + 1] = 0xC2
+    cases.append(('progressive.jpg', bytes(prog)))
+    for (key, variant, _rgb) in jpeg_colour_space_variants(jpeg_colour_space_bases()[0][1]):
+        cases.append(('cs-%s.jpg' % key, variant))
+    paths = []
+    for (name, data) in cases:
+        paths.append(str(tmp_path / name))
+        with open(paths[-1], 'wb') as fp:
+            fp.write(data)
+    paths.append(str(tmp_path / 'missing.jpg'))
+    (blob, offsets, ok) = _engine.read_files(paths)
+    assert list(ok) == [True] * len(cases) + [False]
+    for (i, (name, data)) in enumerate(cases):
+        assert blob[int(offsets[i]):int(offsets[i + 1])].tobytes() == data, name
+    assert offsets[-1] == offsets[-2]                                   # the missing file: an empty slice
+    info = _engine.jpeg_probe_batch(blob, offsets)
+    assert info.shape == (len(paths), 8)
+    n_gpu = 0
+    for (i, (name, data)) in enumerate(cases):
+        want = _image.gpu_ingest_geometry(data) if data else None
+        row = info[i]
+        takes = bool(row[7] == 0 and row[5] == 1 and row[6] == 1)
+        assert takes == (want is not None), (name, row, want)
+        if want is not None:
+            assert tuple(int(v) for v in row[:5]) == want, name
+            n_gpu += 1
+    assert n_gpu >= 50 and info[-1, 7] != 0
+    assert len(_engine.read_files([])[1]) == 1 and _engine.jpeg_probe_batch(blob, offsets[:1]).shape == (0, 8)
