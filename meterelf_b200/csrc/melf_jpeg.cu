@@ -21,6 +21,7 @@
 //
 // All four are byte/integer kernels bounded by latency (Huffman) or HBM (the rest); no tensor work.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -403,7 +404,8 @@ __device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
 template <int G, bool SHARED>
 __global__ void __launch_bounds__(32)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
-                         const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ clean_len,
+                         const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ order,
+                         const uint32_t *__restrict__ clean_len,
                          int n, const JpegGeom g, const McuRect R, int16_t *__restrict__ coef)
 {
     extern __shared__ __align__(16) unsigned char huff_smem[];
@@ -411,12 +413,12 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     const int lane = threadIdx.x;
     const int img0 = blockIdx.x * G;
     for (int gi = 0; gi < (SHARED ? 1 : G) && img0 + gi < n; gi++) {
-        const JpegDesc d = desc[img0 + gi];
+        const JpegDesc d = desc[order[img0 + gi]];
         build_tables(S[gi], blob + d.base, d, lane);
     }
     __syncwarp();
-    const int img = img0 + lane;
-    if (lane >= G || img >= n) return;
+    if (lane >= G || img0 + lane >= n) return;
+    const int img = (int)order[img0 + lane];            // lanes take the streams longest first (host-sorted)
     const HuffSmem &T = S[SHARED ? 0 : lane];
     // the look-ahead tables are read through a shared-window address computed once (a generic pointer
     // makes the compiler rebuild the window base in every iteration, on the critical path of the lookup)
@@ -849,7 +851,9 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     // ---- host: marker walk, descriptors, staging copy ----
     const uint64_t blob0 = batch.offsets[first];
     const size_t blob_bytes = (size_t)(batch.offsets[first + count] - blob0);
-    const size_t desc_bytes = ((size_t)count * sizeof(JpegDesc) + 255) & ~(size_t)255;
+    // descriptors, then the lane order of the Huffman stage (u32 per stream), then the streams
+    const size_t order_off = ((size_t)count * sizeof(JpegDesc) + 15) & ~(size_t)15;
+    const size_t desc_bytes = (order_off + (size_t)count * 4 + 255) & ~(size_t)255;
     if (S.upload_pending) {             // the staging buffer is still the source of the previous upload
         JPEG_CUDA(cudaEventSynchronize(S.uploaded));
         S.upload_pending = false;
@@ -938,6 +942,18 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         descs[i].clean_off = clean_bytes;
         clean_bytes += (((size_t)descs[i].scan_len + 15) & ~(size_t)15) + 32;
     }
+    // Huffman stage: one lane per stream, a warp runs as long as its longest stream.  The lanes take the
+    // streams in order of entropy-coded length (the host has it from the marker walk), so the streams of a
+    // warp end together -- in stream order ncu counted 10.6 live lanes of 16 (profiles/r01_v19_ncu_jpeg_huffman.txt).
+    // Nothing else moves: coefficients, planes and frames stay indexed by stream.
+    {
+        uint32_t *order = reinterpret_cast<uint32_t *>(S.h_stage + order_off);
+        for (int i = 0; i < count; i++) order[i] = (uint32_t)i;
+        static const bool sorted = !(std::getenv("MELF_JPEG_SORT") && !std::atoi(std::getenv("MELF_JPEG_SORT")));
+        if (sorted)
+            std::sort(order, order + count, [&](uint32_t a, uint32_t b) {
+                return descs[a].scan_len != descs[b].scan_len ? descs[a].scan_len > descs[b].scan_len : a < b; });
+    }
     if (g.w != w || g.h != h) {
         if (err) *err = "the streams decode to " + std::to_string(g.w) + "x" + std::to_string(g.h) +
                         " pixels, not the " + std::to_string(w) + "x" + std::to_string(h) + " asked for";
@@ -994,6 +1010,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     JPEG_CUDA(cudaEventRecord(S.uploaded, stream));
     S.upload_pending = true;
     const JpegDesc *d_desc = reinterpret_cast<const JpegDesc *>(S.d_blob);
+    const uint32_t *d_order = reinterpret_cast<const uint32_t *>(S.d_blob + order_off);
     const uint8_t *d_streams = S.d_blob + desc_bytes;
     JPEG_CUDA(cudaMemsetAsync(S.d_coef, 0, coef_elems * 2, stream));
 
@@ -1011,12 +1028,12 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     case GG:                                                                                              \
         if (shared_tables) {                                                                              \
             melf_jpeg_huffman_kernel<GG, true><<<ctas, 32, hsmem, stream>>>(                              \
-                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, mr, S.d_coef);                     \
+                d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, count, g, mr, S.d_coef);            \
         } else {                                                                                          \
             JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false>,                           \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
             melf_jpeg_huffman_kernel<GG, false><<<ctas, 32, hsmem, stream>>>(                             \
-                d_streams, S.d_clean, d_desc, S.d_clean_len, count, g, mr, S.d_coef);                     \
+                d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, count, g, mr, S.d_coef);            \
         }                                                                                                 \
         break;
     switch (G) {

@@ -702,6 +702,15 @@ namespace {
 #ifndef MELF_STAGE_RING
 #define MELF_STAGE_RING 0     // 1: BGR rows reach the workers through a cp.async ring in shared memory -- measured SLOWER (staging
 #endif                        // 55 k clk per pass against 48 k, profiles/r02_timeline_c_*.txt): global-load latency is not what binds it
+#ifndef MELF_STAGE_TMA
+#define MELF_STAGE_TMA 1         // frame bytes brought in by bulk copies (TMA), one 208-byte row segment each, per-warp buffers
+#endif
+#ifndef MELF_STAGE_TMA_FENCE
+#define MELF_STAGE_TMA_FENCE 0   // 1: fence.proxy.async before every refill of a staging buffer (0: the loads out of it are forced to return first)
+#endif
+#ifndef MELF_STAGE_COALESCED
+#define MELF_STAGE_COALESCED 0   // 1: the same buffers filled by cp.async, lane j = chunk j -- measured no faster than stage_slabs (LDGSTS: one request per lane per cycle)
+#endif
 #ifndef MELF_STAGE_L2_PREFETCH
 #define MELF_STAGE_L2_PREFETCH 0   // 1: crop rows of the next pass prefetched into L2 before the window sums of this one -- measured
 #endif                             // no gain (staging 46 k clk instead of 49 k, but the pass 96 k instead of 91 k: profiles/r02_timeline_e_*.txt)
@@ -1077,6 +1086,221 @@ __device__ __forceinline__ void stage_slabs(const MelfMatchTcArgs &A, const Item
             }
 #endif
             stg_keep(reinterpret_cast<uint4 *>(dst + s * STRIP_BYTES + r * 16), stage_unit_f(A, it, r, s, pol_stream), pol_keep);
+        }
+    }
+}
+
+// stage_slabs with COALESCED frame loads.  In stage_slabs a lane fetches its own 64-byte window (row = lane & 7,
+// strip = lane >> 3): one LDG.128 of a warp touches 8 rows x 2-3 cache lines and the four of them touch the same
+// lines again -- about 80 tag look-ups per 1.5 KB unit.  The skip experiments (profiles/r02_skip_experiments_g.txt)
+// show the phase bound by exactly these loads (47 k clk per pass with the conversion removed, 28 k with the loads
+// removed) and slowed further by the MMAs' operand traffic on the same L1 / shared-memory data path.  Here the
+// warp reads the 8 row segments of a unit as consecutive 16-byte chunks (lane j = chunk j: about 7 lines per
+// LDG.128), parks them in a private 1664-byte shared-memory buffer and every lane picks its window from there
+// (row pitch 208 B = 13 chunks: the eight rows of a quarter warp fall into eight different bank groups).
+constexpr int CO_ROW_CHUNKS = 13;                             // 192 bytes at any 16-byte phase
+constexpr int CO_BUF_BYTES = 8 * CO_ROW_CHUNKS * 16;          // 1664 per worker warp
+static_assert(F_WORKER_WARPS * CO_BUF_BYTES <= F_RING_AREA, "per-warp staging buffers do not fit");
+
+__device__ __forceinline__ void stage_slabs_co(const MelfMatchTcArgs &A, const Item (&its)[2], uint8_t *scratch,
+                                               uint8_t *wbuf, int wwarp, int lane)
+{
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+    const int row_chunks = A.channels == 3 ? CO_ROW_CHUNKS : 5;            // 64 pixels of a row segment + phase
+    const int n_chunks = 8 * row_chunks;
+    const int seg_bytes = 64 * A.channels;
+    const uint32_t wbuf_s = smem_u32(wbuf);
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int n_units = ((n_rows + 7) >> 3) * 4;
+        uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        const u64 pol_keep = policy_evict_last();
+        const uint8_t *base = A.img + (size_t)it.frame * A.frame_stride + (size_t)(A.geom.crop_y0 + it.y0) * A.row_stride +
+                              (size_t)A.channels * (size_t)(A.geom.crop_x0 + it.x0);
+        // the unit's bytes, chunk by chunk, global -> shared without passing registers (cp.async: all four chunks
+        // of a lane in flight together; with LDG + STS ptxas, at the 128-register cap, reused the destination
+        // registers and serialised the round trips)
+        auto issue = [&](int u) {
+            const int rg = u >> 2, sg = u & 3;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 32 * c + lane;
+                if (j < n_chunks) {
+                    const int rr = A.channels == 3 ? j / CO_ROW_CHUNKS : j / 5;
+                    const int cc = j - rr * row_chunks;
+                    const uintptr_t seg = reinterpret_cast<uintptr_t>(base + (size_t)(rg * 8 + rr) * A.row_stride) +
+                                          (uintptr_t)(seg_bytes * sg);
+                    const uintptr_t a16 = (seg & ~(uintptr_t)15) + 16u * (uintptr_t)cc;
+                    // rows behind the crop are never looked at; a chunk whose tail leaves the frame memory is cut (zero fill)
+                    if (rg * 8 + rr < n_rows && a16 < limit) {
+                        const uint32_t n_src = a16 + 16 <= limit ? 16u : (uint32_t)(limit - a16);
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+                                     :: "r"(wbuf_s + 16u * (uint32_t)j), "l"(a16), "r"(n_src) : "memory");
+                    }
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        if (wwarp < n_units) issue(wwarp);
+#pragma unroll 1
+        for (int u = wwarp; u < n_units; u += F_WORKER_WARPS) {
+            const int rg = u >> 2, sg = u & 3;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            // ---- lane = (row, strip): its 64-byte window out of the buffer --------------------------------
+            const int r = lane & 7, sl = lane >> 3;
+            const int row = rg * 8 + r, sidx = sg * 4 + sl;
+            const bool live = it.y0 + row < A.geom.crop_h && it.x0 + 16 * sidx < A.geom.crop_w;
+            const uintptr_t seg = reinterpret_cast<uintptr_t>(base + (size_t)row * A.row_stride) + (uintptr_t)(seg_bytes * sg);
+            const uint32_t pos = (uint32_t)(seg & 15) + (uint32_t)(16 * A.channels * sl);
+            const uint8_t *rp = wbuf + r * (16 * row_chunks) + (pos & ~15u);
+            uint32_t e[17];
+#pragma unroll
+            for (int cidx = 0; cidx < 4; ++cidx) {
+                uint4 q = make_uint4(0, 0, 0, 0);
+                if (live && (int)(pos >> 4) + cidx < row_chunks) q = *reinterpret_cast<const uint4 *>(rp + 16 * cidx);
+                e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+            }
+            e[16] = 0;
+            __syncwarp();
+            // the buffer is free again: the next unit's bytes travel while this one is converted
+            if (u + F_WORKER_WARPS < n_units) issue(u + F_WORKER_WARPS);
+            uint4 out = make_uint4(0, 0, 0, 0);
+            if (live) {
+                const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
+                uint32_t v[12];
+                switch (ws) {
+                case 0:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j], e[j + 1], bs);
+                    break;
+                case 1:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 1], e[j + 2], bs);
+                    break;
+                case 2:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 2], e[j + 3], bs);
+                    break;
+                default:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 3], e[j + 4], bs);
+                    break;
+                }
+                out = A.channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
+            }
+            stg_keep(reinterpret_cast<uint4 *>(dst + sidx * STRIP_BYTES + row * 16), out, pol_keep);
+        }
+    }
+}
+
+// stage_slabs with the frame bytes brought in by the TMA engine: per unit (8 rows x 64 pixels) eight bulk
+// copies of one 208-byte row segment each (lanes 0-7 issue one apiece) into the warp's private buffer, completion
+// on the warp's own mbarrier; the next unit's copies are issued as soon as every lane has taken its 64-byte
+// window out of the buffer, so they travel while this unit is converted.  Why: the load/store units of an SM
+// serve a 16-byte-per-lane access at one 128-byte line per cycle and quarter warp, and stage_slabs' pattern
+// (8 different rows per quarter warp) makes each of its four LDG.128 cost 32 of those cycles -- 128+ cycles per
+// unit, the whole staging phase (profiles/r02_skip_experiments_g.txt: 47 k clk per pass with the conversion
+// removed).  cp.async (LDGSTS) is no better, one request per lane per cycle (r02_timeline_h_*.txt).  Bulk copies
+// do not pass the load/store units at all.
+__device__ __forceinline__ void stage_slabs_tma(const MelfMatchTcArgs &A, const Item (&its)[2], uint8_t *scratch,
+                                                uint8_t *wbuf, uint32_t bar, uint32_t &phase, int wwarp, int lane)
+{
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+    const int row_chunks = A.channels == 3 ? CO_ROW_CHUNKS : 5;            // 64 pixels of a row segment + phase
+    const int seg_bytes = 64 * A.channels;
+    const uint32_t wbuf_s = smem_u32(wbuf);
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int n_units = ((n_rows + 7) >> 3) * 4;
+        uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        const u64 pol_keep = policy_evict_last();
+        const uint8_t *base = A.img + (size_t)it.frame * A.frame_stride + (size_t)(A.geom.crop_y0 + it.y0) * A.row_stride +
+                              (size_t)A.channels * (size_t)(A.geom.crop_x0 + it.x0);
+        auto issue = [&](int u) {
+            const int rg = u >> 2, sg = u & 3;
+            uintptr_t a16 = 0;
+            uint32_t bytes = 0;
+            if (lane < 8 && rg * 8 + lane < n_rows) {
+                const uintptr_t seg = reinterpret_cast<uintptr_t>(base + (size_t)(rg * 8 + lane) * A.row_stride) +
+                                      (uintptr_t)(seg_bytes * sg);
+                a16 = seg & ~(uintptr_t)15;
+                if (a16 < limit) bytes = (uint32_t)min((uintptr_t)(16 * row_chunks), limit - a16);   // cut at the end of the frame memory
+            }
+            const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
+#if MELF_STAGE_TMA_FENCE
+            // the generic-proxy reads of the previous unit come before the async-proxy writes of this one
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
+            if (lane == 0) mbar_expect_tx(bar, total);
+            __syncwarp();
+            if (bytes) bulk_load(wbuf_s + (uint32_t)(lane * 16 * row_chunks), reinterpret_cast<const void *>(a16), bytes, bar);
+        };
+        if (wwarp < n_units) issue(wwarp);
+#pragma unroll 1
+        for (int u = wwarp; u < n_units; u += F_WORKER_WARPS) {
+            const int rg = u >> 2, sg = u & 3;
+            mbar_wait(bar, phase & 1);
+            ++phase;
+            // ---- lane = (row, strip): its 64-byte window out of the buffer --------------------------------
+            const int r = lane & 7, sl = lane >> 3;
+            const int row = rg * 8 + r, sidx = sg * 4 + sl;
+            const bool live = it.y0 + row < A.geom.crop_h && it.x0 + 16 * sidx < A.geom.crop_w;
+            const uintptr_t seg = reinterpret_cast<uintptr_t>(base + (size_t)row * A.row_stride) + (uintptr_t)(seg_bytes * sg);
+            const uint32_t pos = (uint32_t)(seg & 15) + (uint32_t)(16 * A.channels * sl);
+            const uint8_t *rp = wbuf + r * (16 * row_chunks) + (pos & ~15u);
+            uint32_t e[17];
+#pragma unroll
+            for (int cidx = 0; cidx < 4; ++cidx) {
+                uint4 q = make_uint4(0, 0, 0, 0);
+                if (live && (int)(pos >> 4) + cidx < row_chunks) q = *reinterpret_cast<const uint4 *>(rp + 16 * cidx);
+                e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+            }
+            e[16] = 0;
+#if !MELF_STAGE_TMA_FENCE
+            {
+                // the four loads must have RETURNED (not just been issued) before the buffer is handed back:
+                // a real instruction that reads one register of each
+                uint32_t seen;
+                asm volatile("xor.b32 %0, %1, %2;\n\txor.b32 %0, %0, %3;\n\txor.b32 %0, %0, %4;"
+                             : "=r"(seen) : "r"(e[0]), "r"(e[4]), "r"(e[8]), "r"(e[12]));
+                (void)seen;
+            }
+#endif
+            __syncwarp();
+            // the buffer is free again: the next unit's bytes travel while this one is converted
+            if (u + F_WORKER_WARPS < n_units) issue(u + F_WORKER_WARPS);
+            uint4 out = make_uint4(0, 0, 0, 0);
+            if (live) {
+                const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
+                uint32_t v[12];
+                switch (ws) {
+                case 0:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j], e[j + 1], bs);
+                    break;
+                case 1:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 1], e[j + 2], bs);
+                    break;
+                case 2:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 2], e[j + 3], bs);
+                    break;
+                default:
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) v[j] = __funnelshift_r(e[j + 3], e[j + 4], bs);
+                    break;
+                }
+                out = A.channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
+            }
+            stg_keep(reinterpret_cast<uint4 *>(dst + sidx * STRIP_BYTES + row * 16), out, pol_keep);
         }
     }
 }
@@ -1502,6 +1726,7 @@ struct CtrlO {
     unsigned long long slab_full;
     unsigned long long prep_done;
     unsigned long long drained[2];     // accumulator of the pass's slot 0 / slot 1 read out (14 warp arrivals)
+    unsigned long long stage[F_WORKER_WARPS];   // per worker warp: its staging buffer has been filled (bulk copies)
     uint32_t tmem_base;
     uint32_t pad;
 };
@@ -1532,6 +1757,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
         mbar_init(smem_u32(&ctrl->prep_done), F_WORKERS);
         mbar_init(smem_u32(&ctrl->drained[0]), F_WORKER_WARPS);
         mbar_init(smem_u32(&ctrl->drained[1]), F_WORKER_WARPS);
+        for (int w = 0; w < F_WORKER_WARPS; ++w) mbar_init(smem_u32(&ctrl->stage[w]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -1673,12 +1899,18 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
         const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;      // <= 193 * 128 (* 255)
         const long long kNone = -(1ll << 62);
         const long long far = (((long long)((u64)n_t32 * 255ull) * (long long)sum_t32 + A.n_t) >> 21) + 1;
+        uint32_t stage_phase = 0;                              // parity of this warp's staging barrier
+        (void)stage_phase;
         {
             // prologue: slabs of this CTA's first pass
             Item its[2];
             pass_items(blockIdx.x, its);
 #if MELF_STAGE_RING
             stage_slabs_ring(A, its, scratch, smem + F_SMEM_H, wt);
+#elif MELF_STAGE_TMA
+            stage_slabs_tma(A, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+#elif MELF_STAGE_COALESCED
+            stage_slabs_co(A, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, wwarp, lane);
 #else
             stage_slabs(A, its, scratch, wwarp, lane);
 #endif
@@ -1714,6 +1946,10 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
                 pass_items(pass + gridDim.x, nxt);
 #if MELF_STAGE_RING
                 stage_slabs_ring(A, nxt, scratch, smem + F_SMEM_H, wt);
+#elif MELF_STAGE_TMA
+                stage_slabs_tma(A, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+#elif MELF_STAGE_COALESCED
+                stage_slabs_co(A, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, wwarp, lane);
 #else
                 stage_slabs(A, nxt, scratch, wwarp, lane);
 #endif
