@@ -33,6 +33,13 @@ cudaError_t melf_launch_match_tc(const MelfMatchTcArgs &args, int num_sms, cudaS
 size_t melf_match_fused_scratch_bytes(int num_sms);
 cudaError_t melf_launch_match_fused(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 size_t melf_match_fused_ov_scratch_bytes(int num_sms);
+bool melf_match_small_supported(const MelfGeom &g, int tmpl_w, int tmpl_h, int channels);
+void melf_match_small_plan(MelfSmallArgs &a);
+size_t melf_match_small_tpos_bytes(const MelfSmallArgs &a);
+size_t melf_match_small_bop_bytes(const MelfSmallArgs &a);
+size_t melf_match_small_wsum_bytes(const MelfSmallArgs &a);
+void melf_match_small_build_tpos(const MelfSmallArgs &a, const uint8_t *tmpl, uint8_t *out);
+cudaError_t melf_launch_match_small(const MelfSmallArgs &a, cudaStream_t stream);
 cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream);
 
 namespace {
@@ -87,6 +94,15 @@ struct melf_ctx {
     bool profiling = false;
     struct Span { int kind; cudaEvent_t e0, e1; };
     std::vector<Span> spans;
+    // small-result-map path (positions as M, frames as N): template per position for ONE crop geometry,
+    // built on first use; frame operand + window sums per scratch slot
+    std::vector<uint8_t> h_tmpl;
+    uint8_t *d_tpos = nullptr;
+    int tpos_crop_w = -1, tpos_crop_h = -1;
+    uint8_t *d_small_bop[kScratchSlots] = {};
+    size_t small_bop_cap[kScratchSlots] = {};
+    uint32_t *d_small_wsum[kScratchSlots] = {};
+    size_t small_wsum_cap[kScratchSlots] = {};
     uint8_t *d_tc_scratch[kScratchSlots] = {};   // [0]: caller-stream path, [1], [2]: pipeline streams, ...
     long long tc_scratch_items[kScratchSlots] = {};
     long long sum_t = 0, n_t = 0;
@@ -192,6 +208,53 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
                   float *d_result, cudaStream_t stream, int scratch_slot)
 {
     MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
+    // small result maps (sample set 2): one GEMM per group of 32 frames, positions as M.  Measured on 4096 frames
+    // (profiles/r02_small_launches.csv): the GEMM 0.26 ms against 0.53 ms for the Toeplitz kernel, but the
+    // preparation kernel in front of it 0.35 ms -- the Toeplitz kernel converts in the shadow of its MMAs -- so the
+    // pair is not faster yet and the path is OFF unless MELF_MATCH_SMALL=1 (frames >= MELF_MATCH_SMALL_MIN, default 1).
+    static const bool small_on = std::getenv("MELF_MATCH_SMALL") && std::atoi(std::getenv("MELF_MATCH_SMALL"));
+    static const int small_min = std::getenv("MELF_MATCH_SMALL_MIN") ? std::atoi(std::getenv("MELF_MATCH_SMALL_MIN")) : 1;
+    if (ctx->use_tc && small_on && !d_result && n >= small_min &&
+        melf_match_small_supported(geom, ctx->params.tmpl_w, ctx->params.tmpl_h, channels)) {
+        MelfSmallArgs a{};
+        a.img = d_img;
+        const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride + (size_t)w * channels;
+        a.img_limit = reinterpret_cast<const uint8_t *>((reinterpret_cast<uintptr_t>(end) + 15) & ~(uintptr_t)15);
+        a.row_stride = row_stride; a.frame_stride = frame_stride; a.channels = channels; a.geom = geom;
+        a.n_frames = n; a.tmpl_w = ctx->params.tmpl_w; a.tmpl_h = ctx->params.tmpl_h;
+        a.sum_t = ctx->sum_t; a.n_t = ctx->n_t; a.match_key = d_keys;
+        melf_match_small_plan(a);
+        if (ctx->tpos_crop_w != geom.crop_w || ctx->tpos_crop_h != geom.crop_h) {
+            // (kernels of earlier calls may still read the old image)
+            MELF_CUDA(ctx, cudaDeviceSynchronize());
+            if (ctx->d_tpos) cudaFree(ctx->d_tpos);
+            ctx->d_tpos = nullptr; ctx->tpos_crop_w = ctx->tpos_crop_h = -1;
+            std::vector<uint8_t> tpos(melf_match_small_tpos_bytes(a));
+            melf_match_small_build_tpos(a, ctx->h_tmpl.data(), tpos.data());
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_tpos, tpos.size()));
+            MELF_CUDA(ctx, cudaMemcpy(ctx->d_tpos, tpos.data(), tpos.size(), cudaMemcpyHostToDevice));
+            ctx->tpos_crop_w = geom.crop_w; ctx->tpos_crop_h = geom.crop_h;
+        }
+        a.tpos = ctx->d_tpos;
+        const size_t bop_need = melf_match_small_bop_bytes(a), wsum_need = melf_match_small_wsum_bytes(a);
+        if (ctx->small_bop_cap[scratch_slot] < bop_need) {
+            if (ctx->d_small_bop[scratch_slot]) { MELF_CUDA(ctx, cudaStreamSynchronize(stream)); cudaFree(ctx->d_small_bop[scratch_slot]); }
+            ctx->d_small_bop[scratch_slot] = nullptr; ctx->small_bop_cap[scratch_slot] = 0;
+            MELF_CUDA(ctx, cudaMalloc(&ctx->d_small_bop[scratch_slot], bop_need));
+            ctx->small_bop_cap[scratch_slot] = bop_need;
+        }
+        if (ctx->small_wsum_cap[scratch_slot] < wsum_need) {
+            if (ctx->d_small_wsum[scratch_slot]) { MELF_CUDA(ctx, cudaStreamSynchronize(stream)); cudaFree(ctx->d_small_wsum[scratch_slot]); }
+            ctx->d_small_wsum[scratch_slot] = nullptr; ctx->small_wsum_cap[scratch_slot] = 0;
+            MELF_CUDA(ctx, cudaMalloc(reinterpret_cast<void **>(&ctx->d_small_wsum[scratch_slot]), wsum_need));
+            ctx->small_wsum_cap[scratch_slot] = wsum_need;
+        }
+        a.bop = ctx->d_small_bop[scratch_slot];
+        a.wsum = ctx->d_small_wsum[scratch_slot];
+        MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_small(a, stream); }));
+        g_launches += 2;
+        return MELF_OK;
+    }
     if (ctx->use_tc) {
         MelfMatchTcArgs t{};
         t.img = d_img;
@@ -389,6 +452,8 @@ void free_ctx(melf_ctx *ctx)
     cudaFree(ctx->d_dials); cudaFree(ctx->d_ring_pos); cudaFree(ctx->d_need_pos); cudaFree(ctx->d_ring_angle);
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
+    cudaFree(ctx->d_tpos);
+    for (int i = 0; i < kScratchSlots; i++) { cudaFree(ctx->d_small_bop[i]); cudaFree(ctx->d_small_wsum[i]); }
     cudaFree(ctx->d_keys);
     for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_dial_slots[i]);
     for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_tc_scratch[i]);
@@ -450,6 +515,7 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
     melf_ctx *ctx = new melf_ctx();
     ctx->device = device;
     ctx->params = *P;
+    ctx->h_tmpl.assign(P->tmpl, P->tmpl + (size_t)P->tmpl_w * P->tmpl_h);
     ctx->params.tmpl = nullptr;
     for (int d = 0; d < MELF_MAX_DIALS; d++) {
         ctx->params.dials[d].mask = nullptr;

@@ -78,6 +78,27 @@ struct MelfMatchTcArgs {
                                  // bit 4 staging without its global loads, bit 5 staging without the conversion
 };
 
+// Small result maps (sample set 2: 33 x 17 positions): result positions as the MMA's M, frames as its N
+// (melf_match_tc.cu, last section).
+struct MelfSmallArgs {
+    const uint8_t *img;          // BGR (channels = 3) or single channel frames
+    const uint8_t *img_limit;    // 16-byte aligned end of the readable image memory
+    size_t row_stride, frame_stride;
+    int32_t channels;
+    MelfGeom geom;
+    int32_t n_frames;
+    int32_t tmpl_w, tmpl_h;
+    int32_t n_pos, n_mt;         // res_w * res_h result positions in n_mt tiles of 128
+    int32_t cwp;                 // crop width padded to 32: K index of crop pixel (r, c) = r * cwp + c
+    int32_t n_kstages;           // ceil(crop_h * cwp / 64)
+    int32_t mt_k0[5], mt_k1[5];  // K-stage range in which tile mt has a non-zero template byte
+    const uint8_t *tpos;         // template per position: [n_kstages][n_mt][2 K-steps][2 strips][128 positions][16 B]
+    uint8_t *bop;                // frames as MMA operand: [group][K / 16][32 frames][16 B]
+    uint32_t *wsum;              // window sums: [group][n_mt * 128 positions][32 frames]
+    long long sum_t, n_t;
+    u64 *match_key;              // [n_frames]
+};
+
 struct MelfConvertArgs {
     const uint8_t *bgr;
     size_t row_stride, frame_stride;

@@ -34,6 +34,8 @@
 //       operands of the next pass are fetched under the epilogue of the current one.
 // Everything is integer-exact, so results are bit-identical to melf_match.cu and to the
 // oracle.
+#include <cstring>
+
 #include "melf_common.cuh"
 #include "melf_args.h"
 
@@ -2223,4 +2225,350 @@ extern "C" int melf_host_match_tc_plan(int res_w, int res_h, int tmpl_w, int tmp
     melf_match_tc_plan(a, 1);
     plan[0] = a.n_tx; plan[1] = a.n_ty; plan[2] = a.chunk_h; plan[3] = a.n_pairs;
     return 0;
+}
+
+// =============================================================================================
+// Small result maps: result positions as M, frames as N.
+//
+// With the Toeplitz formulation above one frame costs 60 x 8 MMAs whatever its result map: for sample set
+// 2 (meter_rect 220 x 135, 33 x 17 = 561 positions) they run at N = 32, i.e. at the instruction's fixed
+// cost (86 clk for the 4 KB Toeplitz tile) -- 5 % of the tensor peak.  When the whole map
+// has at most 640 positions the correlation is one plain GEMM per group of 32 frames:
+//     D[pos][frame] = sum_k Tpos[pos][k] * L_frame[k],   k = (r, c) over the crop,  Tpos[(y, x)][(r, c)] = T(r - y, c - x)
+// M = positions (5 tiles of 128), N = 32 frames, K = crop_h x 224 = 30240: 945 K-steps x 5 tiles = 4725 MMAs per
+// 32 frames instead of 480 per frame (3.3 x fewer), 75 % of the template operand non-zero.  Tpos (19 MB for
+// set 2, built once per crop geometry) streams from L2, 40 KB per stage; the frames' lightness is brought
+// into operand layout (and the window sums computed) by a small kernel in front.
+// Exact integer arithmetic like everything else here: bit-identical keys.
+// =============================================================================================
+namespace {
+
+constexpr int SM_N = 32;                               // frames per group = MMA N
+constexpr int SM_KS = 2;                               // K-steps of 32 per pipeline stage
+constexpr int SM_MT_MAX = 5;
+constexpr int SM_STAGES = 4;
+constexpr int SM_A_TILE = 2 * BSTRIP_BYTES;            // one K-step of one position tile: 4096
+constexpr int SM_B_STEP = 2 * SM_N * 16;               // one K-step of the frame operand: 1024
+constexpr int SM_PREP_THREADS = 256;
+constexpr int SM_PREP_ROWS = 16;                       // crop rows converted per round
+
+struct CtrlS {
+    unsigned long long full[SM_STAGES];
+    unsigned long long empty[SM_STAGES];
+    unsigned long long accum;
+    unsigned long long keys[SM_N];
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+}  // namespace
+
+// shared-memory geometry of the preparation kernel: pitches chosen so that the accesses below do not pile up on a
+// few banks (first version: 66 % of its shared-memory wavefronts were bank conflicts, 0.50 ms per 4096 frames)
+__host__ __device__ inline int sm_raw_pitch(int channels, int crop_w)
+{
+    int p = ((channels * crop_w + 15 + 15) & ~15) + 16;         // a row at any 16-byte phase
+    if (((p >> 4) & 1) == 0) p += 16;                           // odd number of 16-byte chunks: 8 rows, 8 bank groups
+    return p;
+}
+__host__ __device__ inline int sm_l_pitch(int cwp) { return cwp + 4; }       // odd number of words per row
+__host__ __device__ inline int sm_prep_smem(int channels, int crop_w, int crop_h, int cwp, int res_w)
+{
+    return ((crop_h * sm_l_pitch(cwp) + 15) & ~15) + SM_PREP_ROWS * sm_raw_pitch(channels, crop_w) + crop_h * (res_w | 1) * 4;
+}
+
+// One CTA per frame: crop -> lightness (coalesced 16-byte loads through a raw staging area), written straight
+// into operand order in global memory and kept in shared memory for the window sums of every result position.
+__global__ void __launch_bounds__(SM_PREP_THREADS)
+melf_small_prep_kernel(const MelfSmallArgs A)
+{
+    extern __shared__ __align__(16) uint8_t sp_smem[];
+    const int tid = threadIdx.x;
+    const int f = blockIdx.x;
+    const int cw = A.geom.crop_w, ch = A.geom.crop_h, cwp = A.cwp;
+    const int rw = A.geom.res_w, rh = A.geom.res_h;
+    const int lp = sm_l_pitch(cwp);
+    uint8_t *L = sp_smem;                                                   // [ch][lp]
+    const int raw_pitch = sm_raw_pitch(A.channels, cw);
+    uint8_t *raw = sp_smem + ((ch * lp + 15) & ~15);                         // [SM_PREP_ROWS][raw_pitch]
+    const int hp = rw | 1;
+    uint32_t *H = reinterpret_cast<uint32_t *>(raw + SM_PREP_ROWS * raw_pitch);   // [ch][hp]
+    const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+    const uint8_t *base = A.img + (size_t)f * A.frame_stride + (size_t)A.geom.crop_y0 * A.row_stride +
+                          (size_t)A.channels * (size_t)A.geom.crop_x0;
+    const int g = f / SM_N, slot = f - g * SM_N;
+    // the lightness bytes in operand order: [K / 16][frame slot][16 B]
+    uint8_t *B = A.bop + (size_t)g * A.n_kstages * (SM_KS * SM_B_STEP) + (size_t)slot * 16;
+    const int chunks = raw_pitch >> 4;
+    const int units = cwp >> 4;                                             // 16-pixel units per row
+    for (int r0 = 0; r0 < ch; r0 += SM_PREP_ROWS) {
+        const int nr = min(SM_PREP_ROWS, ch - r0);
+        for (int i = tid; i < nr * chunks; i += SM_PREP_THREADS) {
+            const int r = i / chunks, c = i - r * chunks;
+            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)(r0 + r) * A.row_stride);
+            const uintptr_t a16 = (src & ~(uintptr_t)15) + 16u * (uintptr_t)c;
+            uint4 q = make_uint4(0, 0, 0, 0);
+            if (a16 + 16 <= limit) q = __ldg(reinterpret_cast<const uint4 *>(a16));
+            *reinterpret_cast<uint4 *>(raw + r * raw_pitch + 16 * c) = q;
+        }
+        __syncthreads();
+        for (int i = tid; i < nr * units; i += SM_PREP_THREADS) {
+            const int u = i / nr, r = i - u * nr;                           // consecutive threads: consecutive rows
+            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)(r0 + r) * A.row_stride);
+            const uint32_t pos = (uint32_t)(src & 15) + (uint32_t)(16 * A.channels * u);
+            const uint8_t *rp = raw + r * raw_pitch + (pos & ~15u);
+            const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
+            uint32_t e[17];
+#pragma unroll
+            for (int cidx = 0; cidx < 4; ++cidx) {
+                uint4 q = make_uint4(0, 0, 0, 0);
+                if ((int)(pos >> 4) + cidx < chunks) q = *reinterpret_cast<const uint4 *>(rp + 16 * cidx);
+                e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+            }
+            e[16] = 0;
+            uint32_t v[12];
+#pragma unroll
+            for (int j = 0; j < 12; ++j) {
+                const uint32_t lo = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
+                const uint32_t hi = ws == 0 ? e[j + 1] : ws == 1 ? e[j + 2] : ws == 2 ? e[j + 3] : e[j + 4];
+                v[j] = __funnelshift_r(lo, hi, bs);
+            }
+            const uint4 conv = A.channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
+            uint32_t w4[4] = {conv.x, conv.y, conv.z, conv.w};
+            // pixels behind the crop (the padding up to cwp) are zero
+            const int left = cw - 16 * u;
+            if (left < 16) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int keep = left - 4 * k;                          // bytes of word k that are pixels
+                    w4[k] = keep >= 4 ? w4[k] : keep <= 0 ? 0u : (w4[k] & ((1u << (8 * keep)) - 1u));
+                }
+            }
+            uint32_t *lrow = reinterpret_cast<uint32_t *>(L + (size_t)(r0 + r) * lp + 16 * u);
+            lrow[0] = w4[0]; lrow[1] = w4[1]; lrow[2] = w4[2]; lrow[3] = w4[3];
+            const size_t k16 = (size_t)(r0 + r) * units + u;
+            *reinterpret_cast<uint4 *>(B + k16 * (SM_N * 16)) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+        __syncthreads();
+    }
+    // ---- window sums: horizontal sliding sums per row, then tmpl_h of them per position ----------------
+    for (int r = tid; r < ch; r += SM_PREP_THREADS) {
+        const uint8_t *row = L + (size_t)r * lp;
+        const uint32_t *row32 = reinterpret_cast<const uint32_t *>(row);
+        uint32_t s = 0;
+        const int full = A.tmpl_w >> 2;
+        for (int j = 0; j < full; ++j) s = __dp4a(row32[j], 0x01010101u, s);
+        for (int j = 4 * full; j < A.tmpl_w; ++j) s += row[j];
+        for (int x = 0; x < rw; ++x) {
+            H[r * hp + x] = s;
+            s += (uint32_t)row[x + A.tmpl_w < cwp ? x + A.tmpl_w : cwp - 1] - (uint32_t)row[x];
+        }
+    }
+    __syncthreads();
+    uint32_t *S = A.wsum + (size_t)g * (A.n_mt * 128) * SM_N + slot;
+    for (int p = tid; p < rw * rh; p += SM_PREP_THREADS) {
+        const int y = p / rw, x = p - y * rw;
+        uint32_t s = 0;
+        for (int i = 0; i < A.tmpl_h; ++i) s += H[(y + i) * hp + x];
+        S[(size_t)p * SM_N] = s;
+    }
+}
+
+// One CTA per group of 32 frames: warp 0 streams the stages (template tiles + the group's frame bytes), warp 1
+// issues the MMAs, warps 2-5 score the accumulators and take the arg-max per frame.
+__global__ void __launch_bounds__(192, 1)
+melf_small_gemm_kernel(const MelfSmallArgs A)
+{
+    uint8_t *smem = melf_tc_smem;
+    const int stage_bytes = A.n_mt * SM_KS * SM_A_TILE + SM_KS * SM_B_STEP;
+    CtrlS *ctrl = reinterpret_cast<CtrlS *>(smem + SM_STAGES * stage_bytes);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int g = blockIdx.x;
+    if (tid == 0) {
+        for (int s = 0; s < SM_STAGES; ++s) {
+            mbar_init(smem_u32(&ctrl->full[s]), 1);
+            mbar_init(smem_u32(&ctrl->empty[s]), 1);
+        }
+        mbar_init(smem_u32(&ctrl->accum), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < SM_N) ctrl->keys[tid] = 0ull;
+    __syncwarp();
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;"
+                     :: "r"(smem_u32(&ctrl->tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = ctrl->tmem_base;
+    const uint32_t smem_base = smem_u32(smem);
+    const int a_bytes = A.n_mt * SM_KS * SM_A_TILE;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const u64 pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
+            const uint8_t *bsrc = A.bop + (size_t)g * A.n_kstages * (SM_KS * SM_B_STEP);
+            for (int st = 0; st < A.n_kstages; ++st) {
+                const uint32_t slot = (uint32_t)st % SM_STAGES, ph = ((uint32_t)st / SM_STAGES) & 1;
+                mbar_wait(smem_u32(&ctrl->empty[slot]), ph ^ 1);
+                mbar_expect_tx(smem_u32(&ctrl->full[slot]), (uint32_t)stage_bytes);
+                bulk_load_keep(smem_base + slot * stage_bytes, A.tpos + (size_t)st * a_bytes, (uint32_t)a_bytes,
+                               smem_u32(&ctrl->full[slot]), pol_keep);
+                bulk_load_keep(smem_base + slot * stage_bytes + a_bytes, bsrc + (size_t)st * (SM_KS * SM_B_STEP),
+                               SM_KS * SM_B_STEP, smem_u32(&ctrl->full[slot]), pol_stream);
+            }
+        }
+    } else if (warp == 1) {
+        const bool lead = elect_one();
+        const uint32_t idesc = make_idesc(SM_N);
+        for (int st = 0; st < A.n_kstages; ++st) {
+            const uint32_t slot = (uint32_t)st % SM_STAGES, ph = ((uint32_t)st / SM_STAGES) & 1;
+            mbar_wait(smem_u32(&ctrl->full[slot]), ph);
+            tc_fence_after();
+            if (lead) {
+                const uint32_t abase = smem_base + slot * stage_bytes, bbase = abase + a_bytes;
+                for (int mt = 0; mt < A.n_mt; ++mt) {
+                    if (st < A.mt_k0[mt] || st >= A.mt_k1[mt]) continue;     // all-zero template bytes for this tile
+#pragma unroll
+                    for (int ks = 0; ks < SM_KS; ++ks)
+                        umma_i8(tmem + (uint32_t)(mt * SM_N), umma_desc(abase + (mt * SM_KS + ks) * SM_A_TILE, BSTRIP_BYTES),
+                                umma_desc(bbase + ks * SM_B_STEP, SM_N * 16), idesc, (st > A.mt_k0[mt] || ks > 0) ? 1u : 0u);
+                }
+                umma_commit(smem_u32(&ctrl->empty[slot]));
+            }
+            __syncwarp();
+        }
+        if (lead) umma_commit(smem_u32(&ctrl->accum));
+    } else {
+        const int qd = warp & 3;
+        mbar_wait(smem_u32(&ctrl->accum), 0);
+        tc_fence_after();
+        const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;
+        const int n_valid = min(SM_N, A.n_frames - g * SM_N);
+        // best key of a frame over the 32 positions of this warp, then one shared-memory atomic per warp
+        auto q4_keys = [&](int q4, u64 (&k4)[4]) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                u64 best = k4[k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
+                    best = other > best ? other : best;
+                }
+                if (lane == 0 && 4 * q4 + k < n_valid && best) atomicMax(&ctrl->keys[4 * q4 + k], best);
+            }
+        };
+        for (int mt = 0; mt < A.n_mt; ++mt) {
+            const int pos = mt * 128 + 32 * qd + lane;
+            u64 keys4[4];
+            uint32_t d[33];
+            tmem_ld32(tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(mt * SM_N), d);
+            tmem_ld_wait();
+            if (pos < A.n_pos) {
+                const uint4 *S = reinterpret_cast<const uint4 *>(A.wsum + ((size_t)g * (A.n_mt * 128) + pos) * SM_N);
+#pragma unroll
+                for (int q4 = 0; q4 < SM_N / 4; ++q4) {
+                    const uint4 sw = __ldcg(S + q4);
+                    const uint32_t s4[4] = {sw.x, sw.y, sw.z, sw.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const long long num = (long long)((u64)n_t32 * (u64)d[4 * q4 + k]) - (long long)((u64)sum_t32 * (u64)s4[k]);
+                        keys4[k] = melf_score_key(score_of(num, A.n_t), (uint32_t)pos);
+                    }
+                    q4_keys(q4, keys4);
+                }
+            } else {
+#pragma unroll
+                for (int q4 = 0; q4 < SM_N / 4; ++q4) {
+                    u64 none[4] = {0ull, 0ull, 0ull, 0ull};
+                    q4_keys(q4, none);
+                }
+            }
+        }
+        tc_fence_before();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int et = tid - 64;
+        if (et < n_valid) A.match_key[(size_t)g * SM_N + et] = ctrl->keys[et];
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem) : "memory");
+}
+
+// ---- host side of the small-map path ---------------------------------------------------------------------
+bool melf_match_small_supported(const MelfGeom &g, int tmpl_w, int tmpl_h, int channels)
+{
+    const long long n_pos = (long long)g.res_w * g.res_h;
+    const int cwp = (g.crop_w + 31) & ~31;
+    const long long k_total = (long long)g.crop_h * cwp;
+    const long long prep_smem = g.crop_h <= 1024 ? sm_prep_smem(channels, g.crop_w, g.crop_h, cwp, g.res_w) : (1 << 30);
+    return n_pos <= SM_MT_MAX * 128 && tmpl_w <= g.crop_w && tmpl_h <= g.crop_h && k_total <= 64 * 1024 &&
+           prep_smem <= 200 * 1024 && g.crop_h <= 1024;
+}
+
+void melf_match_small_plan(MelfSmallArgs &a)
+{
+    a.n_pos = a.geom.res_w * a.geom.res_h;
+    a.n_mt = (a.n_pos + 127) / 128;
+    a.cwp = (a.geom.crop_w + 31) & ~31;
+    a.n_kstages = (a.geom.crop_h * a.cwp + 32 * SM_KS - 1) / (32 * SM_KS);
+    for (int mt = 0; mt < SM_MT_MAX; ++mt) { a.mt_k0[mt] = 0; a.mt_k1[mt] = 0; }
+    for (int mt = 0; mt < a.n_mt; ++mt) {
+        const int p0 = mt * 128, p1 = (p0 + 128 < a.n_pos ? p0 + 128 : a.n_pos) - 1;
+        const int y0 = p0 / a.geom.res_w, y1 = p1 / a.geom.res_w;
+        const long long k_lo = (long long)y0 * a.cwp, k_hi = (long long)(y1 + a.tmpl_h) * a.cwp;
+        a.mt_k0[mt] = (int)(k_lo / (32 * SM_KS));
+        a.mt_k1[mt] = (int)((k_hi + 32 * SM_KS - 1) / (32 * SM_KS));
+        if (a.mt_k1[mt] > a.n_kstages) a.mt_k1[mt] = a.n_kstages;
+    }
+}
+
+size_t melf_match_small_tpos_bytes(const MelfSmallArgs &a) { return (size_t)a.n_kstages * a.n_mt * SM_KS * SM_A_TILE; }
+size_t melf_match_small_bop_bytes(const MelfSmallArgs &a)
+{
+    return (size_t)((a.n_frames + SM_N - 1) / SM_N) * a.n_kstages * (SM_KS * SM_B_STEP) + 64;
+}
+size_t melf_match_small_wsum_bytes(const MelfSmallArgs &a)
+{
+    return (size_t)((a.n_frames + SM_N - 1) / SM_N) * (a.n_mt * 128) * SM_N * 4;
+}
+
+// Tpos: [K stage][position tile][K-step][strip][128 positions][16 B], byte = T(r - y, c - x) for K index (r, c)
+void melf_match_small_build_tpos(const MelfSmallArgs &a, const uint8_t *tmpl, uint8_t *out)
+{
+    std::memset(out, 0, melf_match_small_tpos_bytes(a));
+    for (int pos = 0; pos < a.n_pos; ++pos) {
+        const int y = pos / a.geom.res_w, x = pos - y * a.geom.res_w;
+        const int mt = pos >> 7, m = pos & 127;
+        for (int i = 0; i < a.tmpl_h; ++i)
+            for (int j = 0; j < a.tmpl_w; ++j) {
+                const long long k = (long long)(y + i) * a.cwp + (x + j);
+                const long long kstep = k >> 5;
+                const int st = (int)(kstep / SM_KS), ks = (int)(kstep % SM_KS), strip = (int)((k >> 4) & 1), b = (int)(k & 15);
+                out[((((size_t)st * a.n_mt + mt) * SM_KS + ks) * 2 + strip) * BSTRIP_BYTES + (size_t)m * 16 + b] =
+                    tmpl[(size_t)i * a.tmpl_w + j];
+            }
+    }
+}
+
+cudaError_t melf_launch_match_small(const MelfSmallArgs &a, cudaStream_t stream)
+{
+    const int cw = a.geom.crop_w, ch = a.geom.crop_h;
+    const int prep_smem = sm_prep_smem(a.channels, cw, ch, a.cwp, a.geom.res_w);
+    cudaError_t e = cudaFuncSetAttribute(melf_small_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, prep_smem);
+    if (e != cudaSuccess) return e;
+    const int gemm_smem = SM_STAGES * (a.n_mt * SM_KS * SM_A_TILE + SM_KS * SM_B_STEP) + (int)sizeof(CtrlS);
+    e = cudaFuncSetAttribute(melf_small_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem);
+    if (e != cudaSuccess) return e;
+    if (a.n_frames <= 0) return cudaSuccess;
+    melf_small_prep_kernel<<<a.n_frames, SM_PREP_THREADS, prep_smem, stream>>>(a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    melf_small_gemm_kernel<<<(a.n_frames + SM_N - 1) / SM_N, 192, gemm_smem, stream>>>(a);
+    return cudaGetLastError();
 }

@@ -686,3 +686,56 @@ def test_alternative_locate_kernels_still_match(tmp_path, env_switch):
     subprocess.run([sys.executable, '-c', code], check=True, env=env, timeout=300)
     got = np.load(str(tmp_path / 'out.npy'))
     assert got.tobytes() == want.tobytes()
+
+
+def test_small_result_map_path_equals_the_toeplitz_kernel(tmp_path):
+    """Sample set 2 (33 x 17 result map) and small single-channel search windows through the positions-as-M /
+    frames-as-N GEMM (csrc/melf_match_tc.cu, last section; an opt-in path, MELF_MATCH_SMALL=1, run here in a
+    child process) against the default Toeplitz kernel: records and arg-max
+    bit-identical -- sample crops, synthetic blob frames (ties, flat frames), a batch that is not a multiple
+    of 32, whole 640 x 480 frames with the meter_rect cut on the device, grey windows of three sizes."""
+    import subprocess
+    import sys
+    gs = golden_set(2)
+    (x0, y0, x1, y1) = gs.meter_rect
+    crops = np.concatenate([gs.subset()['crops'][:40], synthetic_batch(1, 70, y1 - y0, x1 - x0)])[:107]
+    rng = np.random.default_rng(3)
+    frames = rng.integers(0, 256, size=(37, 640, 480, 3), dtype=np.uint8)
+    frames[:, y0:y1, x0:x1] = crops[:37]
+    np.save(str(tmp_path / 'crops.npy'), crops)
+    np.save(str(tmp_path / 'frames.npy'), frames)
+    greys = {}
+    for (h, w) in ((135, 220), (119, 188), (130, 200)):
+        greys['%dx%d' % (w, h)] = rng.integers(0, 256, size=(45, h, w), dtype=np.uint8)
+        np.save(str(tmp_path / ('grey%dx%d.npy' % (w, h))), greys['%dx%d' % (w, h)])
+    code = (
+        "import sys, numpy as np, torch\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from helpers import golden_set\n"
+        "gs = golden_set(2)\n"
+        "d = %r\n"
+        "np.save(d + '/out_crops.npy', gs.engine(cropped_input=True, threshold=-1e30).read_frames(np.load(d + '/crops.npy')))\n"
+        "np.save(d + '/out_frames.npy', gs.engine(cropped_input=False).read_frames(np.load(d + '/frames.npy')))\n"
+        "eng = gs.engine(cropped_input=True)\n"
+        "for name in ('220x135', '188x119', '200x130'):\n"
+        "    g = torch.from_numpy(np.load(d + '/grey%%s.npy' %% name)).cuda()\n"
+        "    (n, h, w) = g.shape\n"
+        "    xy = torch.zeros((n, 2), dtype=torch.int32, device='cuda'); val = torch.zeros((n,), dtype=torch.float32, device='cuda')\n"
+        "    eng.match_template_device(g.data_ptr(), 1, n, h, w, w, h * w, False, xy.data_ptr(), val.data_ptr())\n"
+        "    torch.cuda.synchronize()\n"
+        "    np.save(d + '/out_grey%%s.npy' %% name, np.concatenate([xy.cpu().numpy().astype(np.float64), val.cpu().numpy().astype(np.float64)[:, None]], axis=1))\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)), str(tmp_path))
+    results = {}
+    for (tag, env_switch) in (('small', {'MELF_MATCH_SMALL': '1'}), ('toeplitz', {'MELF_MATCH_SMALL': '0'})):
+        subprocess.run([sys.executable, '-c', code], check=True, env=dict(os.environ, **env_switch), timeout=600)
+        results[tag] = {k: np.load(str(tmp_path / k)) for k in ('out_crops.npy', 'out_frames.npy', 'out_grey220x135.npy',
+                                                                'out_grey188x119.npy', 'out_grey200x130.npy')}
+    for k in results['small']:
+        assert results['small'][k].tobytes() == results['toeplitz'][k].tobytes(), k
+    want = oracle.read_batch(gs.oracle_params(threshold=-1e30), crops, n_threads=8)
+    for (g, w) in zip(results['small']['out_crops.npy'], want):
+        assert_results_equal(g, w, len(gs.names))
+    for (name, imgs) in greys.items():
+        for i in (0, 7, 44):
+            (x, y, val, _m) = oracle.match_template(imgs[i], gs.template, want_map=False)
+            assert tuple(results['small']['out_grey%s.npy' % name][i]) == (float(x), float(y), float(val)), (name, i)
