@@ -36,7 +36,6 @@ size_t melf_match_fused_ov_scratch_bytes(int num_sms);
 bool melf_match_small_supported(const MelfGeom &g, int tmpl_w, int tmpl_h, int channels);
 void melf_match_small_plan(MelfSmallArgs &a);
 size_t melf_match_small_tpos_bytes(const MelfSmallArgs &a);
-size_t melf_match_small_bop_bytes(const MelfSmallArgs &a);
 size_t melf_match_small_wsum_bytes(const MelfSmallArgs &a);
 void melf_match_small_build_tpos(const MelfSmallArgs &a, const uint8_t *tmpl, uint8_t *out);
 cudaError_t melf_launch_match_small(const MelfSmallArgs &a, cudaStream_t stream);
@@ -99,8 +98,6 @@ struct melf_ctx {
     std::vector<uint8_t> h_tmpl;
     uint8_t *d_tpos = nullptr;
     int tpos_crop_w = -1, tpos_crop_h = -1;
-    uint8_t *d_small_bop[kScratchSlots] = {};
-    size_t small_bop_cap[kScratchSlots] = {};
     uint32_t *d_small_wsum[kScratchSlots] = {};
     size_t small_wsum_cap[kScratchSlots] = {};
     uint8_t *d_tc_scratch[kScratchSlots] = {};   // [0]: caller-stream path, [1], [2]: pipeline streams, ...
@@ -208,14 +205,28 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
                   float *d_result, cudaStream_t stream, int scratch_slot)
 {
     MELF_CUDA(ctx, cudaMemsetAsync(d_keys, 0, (size_t)n * sizeof(u64), stream));
-    // small result maps (sample set 2): one GEMM per group of 32 frames, positions as M.  Measured on 4096 frames
-    // (profiles/r02_small_launches.csv): the GEMM 0.26 ms against 0.53 ms for the Toeplitz kernel, but the
-    // preparation kernel in front of it 0.35 ms -- the Toeplitz kernel converts in the shadow of its MMAs -- so the
-    // pair is not faster yet and the path is OFF unless MELF_MATCH_SMALL=1 (frames >= MELF_MATCH_SMALL_MIN, default 1).
-    static const bool small_on = std::getenv("MELF_MATCH_SMALL") && std::atoi(std::getenv("MELF_MATCH_SMALL"));
-    static const int small_min = std::getenv("MELF_MATCH_SMALL_MIN") ? std::atoi(std::getenv("MELF_MATCH_SMALL_MIN")) : 1;
-    if (ctx->use_tc && small_on && !d_result && n >= small_min &&
-        melf_match_small_supported(geom, ctx->params.tmpl_w, ctx->params.tmpl_h, channels)) {
+    // small result maps (sample set 2): one GEMM per group of 32 frames, positions as M (melf_match_tc.cu, last
+    // section).  Its time barely depends on the batch (one wave of 32-frame groups), the Toeplitz kernel's is
+    // proportional to it, so a cost model in clocks picks the path: measured per MMA slot 132 clk in the fused
+    // GEMM kernel (+ 35 clk per frame for the edge kernel) against ~78 clk per MMA in the Toeplitz kernel
+    // (profiles/r02_small_launches.csv).  MELF_MATCH_SMALL=0 / 1 forces the choice.
+    bool small_path = false;
+    if (ctx->use_tc && !d_result && melf_match_small_supported(geom, ctx->params.tmpl_w, ctx->params.tmpl_h, channels)) {
+        static const int forced = std::getenv("MELF_MATCH_SMALL") ? std::atoi(std::getenv("MELF_MATCH_SMALL")) : -1;
+        if (forced >= 0) {
+            small_path = forced != 0;
+        } else {
+            MelfSmallArgs plan{};
+            plan.geom = geom; plan.tmpl_w = ctx->params.tmpl_w; plan.tmpl_h = ctx->params.tmpl_h;
+            melf_match_small_plan(plan);
+            const long long groups = ((long long)n + 31) / 32, sms = ctx->num_sms;
+            const long long t_small = ((groups + sms - 1) / sms) * (long long)plan.n_kstages * plan.n_mt * 2 * 132 + 35ll * n;
+            const long long n_pairs = (ctx->params.tmpl_h + 1) / 2;
+            const long long t_toeplitz = (((long long)n + 2 * sms - 1) / (2 * sms)) * (n_pairs * 16 * 78 + 4000);
+            small_path = t_small < t_toeplitz;
+        }
+    }
+    if (small_path) {
         MelfSmallArgs a{};
         a.img = d_img;
         const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride + (size_t)w * channels;
@@ -236,20 +247,13 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             ctx->tpos_crop_w = geom.crop_w; ctx->tpos_crop_h = geom.crop_h;
         }
         a.tpos = ctx->d_tpos;
-        const size_t bop_need = melf_match_small_bop_bytes(a), wsum_need = melf_match_small_wsum_bytes(a);
-        if (ctx->small_bop_cap[scratch_slot] < bop_need) {
-            if (ctx->d_small_bop[scratch_slot]) { MELF_CUDA(ctx, cudaStreamSynchronize(stream)); cudaFree(ctx->d_small_bop[scratch_slot]); }
-            ctx->d_small_bop[scratch_slot] = nullptr; ctx->small_bop_cap[scratch_slot] = 0;
-            MELF_CUDA(ctx, cudaMalloc(&ctx->d_small_bop[scratch_slot], bop_need));
-            ctx->small_bop_cap[scratch_slot] = bop_need;
-        }
+        const size_t wsum_need = melf_match_small_wsum_bytes(a);
         if (ctx->small_wsum_cap[scratch_slot] < wsum_need) {
             if (ctx->d_small_wsum[scratch_slot]) { MELF_CUDA(ctx, cudaStreamSynchronize(stream)); cudaFree(ctx->d_small_wsum[scratch_slot]); }
             ctx->d_small_wsum[scratch_slot] = nullptr; ctx->small_wsum_cap[scratch_slot] = 0;
             MELF_CUDA(ctx, cudaMalloc(reinterpret_cast<void **>(&ctx->d_small_wsum[scratch_slot]), wsum_need));
             ctx->small_wsum_cap[scratch_slot] = wsum_need;
         }
-        a.bop = ctx->d_small_bop[scratch_slot];
         a.wsum = ctx->d_small_wsum[scratch_slot];
         MELF_CUDA(ctx, timed(ctx, MELF_PROF_MATCH_TC, stream, [&] { return melf_launch_match_small(a, stream); }));
         g_launches += 2;
@@ -453,7 +457,7 @@ void free_ctx(melf_ctx *ctx)
     cudaFree(ctx->d_ring_sqd); cudaFree(ctx->d_tmpl_words); cudaFree(ctx->d_ones_words);
     cudaFree(ctx->d_toeplitz);
     cudaFree(ctx->d_tpos);
-    for (int i = 0; i < kScratchSlots; i++) { cudaFree(ctx->d_small_bop[i]); cudaFree(ctx->d_small_wsum[i]); }
+    for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_small_wsum[i]);
     cudaFree(ctx->d_keys);
     for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_dial_slots[i]);
     for (int i = 0; i < kScratchSlots; i++) cudaFree(ctx->d_tc_scratch[i]);

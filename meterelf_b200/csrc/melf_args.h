@@ -88,13 +88,12 @@ struct MelfSmallArgs {
     MelfGeom geom;
     int32_t n_frames;
     int32_t tmpl_w, tmpl_h;
-    int32_t n_pos, n_mt;         // res_w * res_h result positions in n_mt tiles of 128
+    int32_t n_pos, n_mt;         // res_w * res_h result positions (+ res_w box-sum rows) in n_mt tiles of 128
     int32_t cwp;                 // crop width padded to 32: K index of crop pixel (r, c) = r * cwp + c
     int32_t n_kstages;           // ceil(crop_h * cwp / 64)
     int32_t mt_k0[5], mt_k1[5];  // K-stage range in which tile mt has a non-zero template byte
     const uint8_t *tpos;         // template per position: [n_kstages][n_mt][2 K-steps][2 strips][128 positions][16 B]
-    uint8_t *bop;                // frames as MMA operand: [group][K / 16][32 frames][16 B]
-    uint32_t *wsum;              // window sums: [group][n_mt * 128 positions][32 frames]
+    uint32_t *wsum;              // edge sums E(y, x): [group][n_mt * 128 positions][32 frames]
     long long sum_t, n_t;
     u64 *match_key;              // [n_frames]
 };

@@ -1222,7 +1222,7 @@ __device__ __forceinline__ void stage_slabs_tma(const MelfMatchTcArgs &A, const 
         const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
         const int n_units = ((n_rows + 7) >> 3) * 4;
         uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
-        const u64 pol_keep = policy_evict_last();
+        const u64 pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
         const uint8_t *base = A.img + (size_t)it.frame * A.frame_stride + (size_t)(A.geom.crop_y0 + it.y0) * A.row_stride +
                               (size_t)A.channels * (size_t)(A.geom.crop_x0 + it.x0);
         auto issue = [&](int u) {
@@ -1242,7 +1242,8 @@ __device__ __forceinline__ void stage_slabs_tma(const MelfMatchTcArgs &A, const 
 #endif
             if (lane == 0) mbar_expect_tx(bar, total);
             __syncwarp();
-            if (bytes) bulk_load(wbuf_s + (uint32_t)(lane * 16 * row_chunks), reinterpret_cast<const void *>(a16), bytes, bar);
+            // (frame bytes pass through L2 once: evict-first, so that they do not push out the scratch slabs)
+            if (bytes) bulk_load_keep(wbuf_s + (uint32_t)(lane * 16 * row_chunks), reinterpret_cast<const void *>(a16), bytes, bar, pol_stream);
         };
         if (wwarp < n_units) issue(wwarp);
 #pragma unroll 1
@@ -2232,39 +2233,58 @@ extern "C" int melf_host_match_tc_plan(int res_w, int res_h, int tmpl_w, int tmp
 //
 // With the Toeplitz formulation above one frame costs 60 x 8 MMAs whatever its result map: for sample set
 // 2 (meter_rect 220 x 135, 33 x 17 = 561 positions) they run at N = 32, i.e. at the instruction's fixed
-// cost (86 clk for the 4 KB Toeplitz tile) -- 5 % of the tensor peak.  When the whole map
-// has at most 640 positions the correlation is one plain GEMM per group of 32 frames:
+// cost (86 clk for the 4 KB Toeplitz tile) -- 6 % of the tensor peak.  When the whole map
+// has few enough positions the correlation is one plain GEMM per group of 32 frames:
 //     D[pos][frame] = sum_k Tpos[pos][k] * L_frame[k],   k = (r, c) over the crop,  Tpos[(y, x)][(r, c)] = T(r - y, c - x)
 // M = positions (5 tiles of 128), N = 32 frames, K = crop_h x 224 = 30240: 945 K-steps x 5 tiles = 4725 MMAs per
 // 32 frames instead of 480 per frame (3.3 x fewer), 75 % of the template operand non-zero.  Tpos (19 MB for
-// set 2, built once per crop geometry) streams from L2, 40 KB per stage; the frames' lightness is brought
-// into operand layout (and the window sums computed) by a small kernel in front.
-// Exact integer arithmetic like everything else here: bit-identical keys.
+// set 2, built once per crop geometry) streams from L2, 40 KB per stage.
+//
+// One kernel, melf_small_fused_kernel, one CTA per group of 32 frames (the version with a stand-alone
+// conversion kernel in front lost what the GEMM won: 0.35 + 0.26 ms against 0.53 ms, profiles/
+// r02_small_launches.csv): ten worker warps convert the group's crops straight into the frame operand's
+// shared-memory ring (lane = frame, 64 K bytes of all 32 frames per stage), in the shadow of the MMAs.
+// Window sums: S(y, x) = C(x) - E(y, x) with C(x) = the box sum over ALL crop rows, which res_w spare rows of
+// Tpos (ones over columns x .. x + tw - 1) deliver as extra accumulator lanes, and E(y, x) = the part of it
+// above row y and from row y + th on -- 2 (res_h - 1) crop rows in all, summed by a small kernel in front
+// (melf_small_edge_kernel).  Exact integer arithmetic like everything else here: bit-identical keys.
 // =============================================================================================
 namespace {
 
 constexpr int SM_N = 32;                               // frames per group = MMA N
 constexpr int SM_KS = 2;                               // K-steps of 32 per pipeline stage
 constexpr int SM_MT_MAX = 5;
-constexpr int SM_STAGES = 4;
 constexpr int SM_A_TILE = 2 * BSTRIP_BYTES;            // one K-step of one position tile: 4096
 constexpr int SM_B_STEP = 2 * SM_N * 16;               // one K-step of the frame operand: 1024
-constexpr int SM_PREP_THREADS = 256;
-constexpr int SM_PREP_ROWS = 16;                       // crop rows converted per round
+constexpr int SM_B_STAGE = SM_KS * SM_B_STEP;          // 2048
+constexpr int SF_THREADS = 512;
+#ifndef MELF_SF_A_STAGES
+#define MELF_SF_A_STAGES 3      // measured per 4096 set-2 frames: 3 + 32 stages 0.315 ms, 4 + 16 stages 0.330 ms, 3 + 48 stages 0.35 ms
+#define MELF_SF_B_STAGES 32
+#endif
+constexpr int SF_A_STAGES = MELF_SF_A_STAGES;          // template ring (TMA), 40 KB per stage
+constexpr int SF_B_STAGES = MELF_SF_B_STAGES;          // frame ring (written by the worker warps), 2 KB per stage
+constexpr int SF_WORKER_WARP0 = 2, SF_WORKERS = 14;    // warp 0 TMA; 1 MMA issue; 2..15 convert, then 2..5 score
+constexpr int SF_CBOX_MAX = 64;                        // res_w <= 64
+#ifndef MELF_EDGE_THREADS
+#define MELF_EDGE_THREADS 256   // (128 threads x 16 rows per round: 0.079 ms instead of 0.072 per 4096 frames)
+#define MELF_EDGE_ROWS 32
+#endif
+constexpr int SM_EDGE_THREADS = MELF_EDGE_THREADS;
+constexpr int SM_EDGE_ROWS = MELF_EDGE_ROWS;            // crop rows converted per round
 
-struct CtrlS {
-    unsigned long long full[SM_STAGES];
-    unsigned long long empty[SM_STAGES];
+struct CtrlSF {
+    unsigned long long a_full[SF_A_STAGES];
+    unsigned long long a_empty[SF_A_STAGES];
+    unsigned long long b_full[SF_B_STAGES];
+    unsigned long long b_empty[SF_B_STAGES];
     unsigned long long accum;
     unsigned long long keys[SM_N];
     uint32_t tmem_base;
     uint32_t pad;
 };
 
-}  // namespace
-
-// shared-memory geometry of the preparation kernel: pitches chosen so that the accesses below do not pile up on a
-// few banks (first version: 66 % of its shared-memory wavefronts were bank conflicts, 0.50 ms per 4096 frames)
+// shared-memory pitches of the edge kernel, chosen so that its accesses do not pile up on a few banks
 __host__ __device__ inline int sm_raw_pitch(int channels, int crop_w)
 {
     int p = ((channels * crop_w + 15 + 15) & ~15) + 16;         // a row at any 16-byte phase
@@ -2272,52 +2292,77 @@ __host__ __device__ inline int sm_raw_pitch(int channels, int crop_w)
     return p;
 }
 __host__ __device__ inline int sm_l_pitch(int cwp) { return cwp + 4; }       // odd number of words per row
-__host__ __device__ inline int sm_prep_smem(int channels, int crop_w, int crop_h, int cwp, int res_w)
+__host__ __device__ inline int sm_edge_smem(int channels, int crop_w, int cwp, int res_w, int res_h)
 {
-    return ((crop_h * sm_l_pitch(cwp) + 15) & ~15) + SM_PREP_ROWS * sm_raw_pitch(channels, crop_w) + crop_h * (res_w | 1) * 4;
+    const int n_edge = 2 * (res_h - 1) > 0 ? 2 * (res_h - 1) : 1;
+    return ((n_edge * sm_l_pitch(cwp) + 15) & ~15) + SM_EDGE_ROWS * sm_raw_pitch(channels, crop_w) + n_edge * (res_w | 1) * 4;
 }
 
-// One CTA per frame: crop -> lightness (coalesced 16-byte loads through a raw staging area), written straight
-// into operand order in global memory and kept in shared memory for the window sums of every result position.
-__global__ void __launch_bounds__(SM_PREP_THREADS)
-melf_small_prep_kernel(const MelfSmallArgs A)
+// 16 pixels of a crop row (starting at byte `pos` of the 16-byte-aligned staging row `rp`... see callers) ->
+// 16 lightness bytes, pixels from `left` on set to zero
+__device__ __forceinline__ uint4 sm_convert16(const uint32_t (&e)[17], uint32_t pos, int channels, int left)
+{
+    const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
+    uint32_t v[12];
+#pragma unroll
+    for (int j = 0; j < 12; ++j) {
+        const uint32_t lo = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
+        const uint32_t hi = ws == 0 ? e[j + 1] : ws == 1 ? e[j + 2] : ws == 2 ? e[j + 3] : e[j + 4];
+        v[j] = __funnelshift_r(lo, hi, bs);
+    }
+    const uint4 conv = channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
+    uint32_t w4[4] = {conv.x, conv.y, conv.z, conv.w};
+    if (left < 16) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int keep = left - 4 * k;                              // bytes of word k that are pixels
+            w4[k] = keep >= 4 ? w4[k] : keep <= 0 ? 0u : (w4[k] & ((1u << (8 * keep)) - 1u));
+        }
+    }
+    return make_uint4(w4[0], w4[1], w4[2], w4[3]);
+}
+
+}  // namespace
+
+// One CTA per frame: the 2 (res_h - 1) crop rows above the lowest window top and below the highest window bottom
+// -> lightness -> horizontal box sums H(r, x) -> E(y, x) = sum_{r < y} H + sum_{r >= y + th} H, for every position.
+__global__ void __launch_bounds__(SM_EDGE_THREADS)
+melf_small_edge_kernel(const MelfSmallArgs A)
 {
     extern __shared__ __align__(16) uint8_t sp_smem[];
     const int tid = threadIdx.x;
     const int f = blockIdx.x;
-    const int cw = A.geom.crop_w, ch = A.geom.crop_h, cwp = A.cwp;
+    const int cw = A.geom.crop_w, cwp = A.cwp;
     const int rw = A.geom.res_w, rh = A.geom.res_h;
+    const int n_top = rh - 1, n_edge = 2 * n_top;                           // edge row e: crop row e (e < n_top) or th + e - n_top
     const int lp = sm_l_pitch(cwp);
-    uint8_t *L = sp_smem;                                                   // [ch][lp]
+    uint8_t *L = sp_smem;                                                   // [n_edge][lp]
     const int raw_pitch = sm_raw_pitch(A.channels, cw);
-    uint8_t *raw = sp_smem + ((ch * lp + 15) & ~15);                         // [SM_PREP_ROWS][raw_pitch]
+    uint8_t *raw = sp_smem + (((n_edge > 0 ? n_edge : 1) * lp + 15) & ~15);  // [SM_EDGE_ROWS][raw_pitch]
     const int hp = rw | 1;
-    uint32_t *H = reinterpret_cast<uint32_t *>(raw + SM_PREP_ROWS * raw_pitch);   // [ch][hp]
+    uint32_t *H = reinterpret_cast<uint32_t *>(raw + SM_EDGE_ROWS * raw_pitch);   // [n_edge][hp]
     const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
     const uint8_t *base = A.img + (size_t)f * A.frame_stride + (size_t)A.geom.crop_y0 * A.row_stride +
                           (size_t)A.channels * (size_t)A.geom.crop_x0;
-    const int g = f / SM_N, slot = f - g * SM_N;
-    // the lightness bytes in operand order: [K / 16][frame slot][16 B]
-    uint8_t *B = A.bop + (size_t)g * A.n_kstages * (SM_KS * SM_B_STEP) + (size_t)slot * 16;
     const int chunks = raw_pitch >> 4;
-    const int units = cwp >> 4;                                             // 16-pixel units per row
-    for (int r0 = 0; r0 < ch; r0 += SM_PREP_ROWS) {
-        const int nr = min(SM_PREP_ROWS, ch - r0);
-        for (int i = tid; i < nr * chunks; i += SM_PREP_THREADS) {
+    const int units = cwp >> 4;
+    auto crop_row = [&](int e) { return e < n_top ? e : A.tmpl_h + e - n_top; };
+    for (int e0 = 0; e0 < n_edge; e0 += SM_EDGE_ROWS) {
+        const int nr = min(SM_EDGE_ROWS, n_edge - e0);
+        for (int i = tid; i < nr * chunks; i += SM_EDGE_THREADS) {
             const int r = i / chunks, c = i - r * chunks;
-            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)(r0 + r) * A.row_stride);
+            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)crop_row(e0 + r) * A.row_stride);
             const uintptr_t a16 = (src & ~(uintptr_t)15) + 16u * (uintptr_t)c;
             uint4 q = make_uint4(0, 0, 0, 0);
             if (a16 + 16 <= limit) q = __ldg(reinterpret_cast<const uint4 *>(a16));
             *reinterpret_cast<uint4 *>(raw + r * raw_pitch + 16 * c) = q;
         }
         __syncthreads();
-        for (int i = tid; i < nr * units; i += SM_PREP_THREADS) {
+        for (int i = tid; i < nr * units; i += SM_EDGE_THREADS) {
             const int u = i / nr, r = i - u * nr;                           // consecutive threads: consecutive rows
-            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)(r0 + r) * A.row_stride);
+            const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)crop_row(e0 + r) * A.row_stride);
             const uint32_t pos = (uint32_t)(src & 15) + (uint32_t)(16 * A.channels * u);
             const uint8_t *rp = raw + r * raw_pitch + (pos & ~15u);
-            const uint32_t ws = (pos & 15u) >> 2, bs = (pos & 3u) * 8;
             uint32_t e[17];
 #pragma unroll
             for (int cidx = 0; cidx < 4; ++cidx) {
@@ -2326,70 +2371,57 @@ melf_small_prep_kernel(const MelfSmallArgs A)
                 e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
             }
             e[16] = 0;
-            uint32_t v[12];
-#pragma unroll
-            for (int j = 0; j < 12; ++j) {
-                const uint32_t lo = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
-                const uint32_t hi = ws == 0 ? e[j + 1] : ws == 1 ? e[j + 2] : ws == 2 ? e[j + 3] : e[j + 4];
-                v[j] = __funnelshift_r(lo, hi, bs);
-            }
-            const uint4 conv = A.channels == 1 ? make_uint4(v[0], v[1], v[2], v[3]) : lightness16(v);
-            uint32_t w4[4] = {conv.x, conv.y, conv.z, conv.w};
-            // pixels behind the crop (the padding up to cwp) are zero
-            const int left = cw - 16 * u;
-            if (left < 16) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int keep = left - 4 * k;                          // bytes of word k that are pixels
-                    w4[k] = keep >= 4 ? w4[k] : keep <= 0 ? 0u : (w4[k] & ((1u << (8 * keep)) - 1u));
-                }
-            }
-            uint32_t *lrow = reinterpret_cast<uint32_t *>(L + (size_t)(r0 + r) * lp + 16 * u);
-            lrow[0] = w4[0]; lrow[1] = w4[1]; lrow[2] = w4[2]; lrow[3] = w4[3];
-            const size_t k16 = (size_t)(r0 + r) * units + u;
-            *reinterpret_cast<uint4 *>(B + k16 * (SM_N * 16)) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            const uint4 out = sm_convert16(e, pos, A.channels, cw - 16 * u);
+            uint32_t *lrow = reinterpret_cast<uint32_t *>(L + (size_t)(e0 + r) * lp + 16 * u);
+            lrow[0] = out.x; lrow[1] = out.y; lrow[2] = out.z; lrow[3] = out.w;
         }
         __syncthreads();
     }
-    // ---- window sums: horizontal sliding sums per row, then tmpl_h of them per position ----------------
-    for (int r = tid; r < ch; r += SM_PREP_THREADS) {
-        const uint8_t *row = L + (size_t)r * lp;
-        const uint32_t *row32 = reinterpret_cast<const uint32_t *>(row);
-        uint32_t s = 0;
-        const int full = A.tmpl_w >> 2;
-        for (int j = 0; j < full; ++j) s = __dp4a(row32[j], 0x01010101u, s);
-        for (int j = 4 * full; j < A.tmpl_w; ++j) s += row[j];
-        for (int x = 0; x < rw; ++x) {
-            H[r * hp + x] = s;
-            s += (uint32_t)row[x + A.tmpl_w < cwp ? x + A.tmpl_w : cwp - 1] - (uint32_t)row[x];
+    // H(r, x): thread = (edge row, one of 8 runs of x): the run's first box sum by dp4a, then sliding
+    {
+        const int run = (rw + 7) >> 3;
+        for (int t = tid; t < n_edge * 8; t += SM_EDGE_THREADS) {
+            const int r = t >> 3, x0 = (t & 7) * run, x1 = min(rw, x0 + run);
+            if (x0 >= x1) continue;
+            const uint8_t *row = L + (size_t)r * lp;
+            uint32_t s = 0;
+            int j = x0;
+            for (; (j & 3) && j < x0 + A.tmpl_w; ++j) s += row[j];
+            const uint32_t *row32 = reinterpret_cast<const uint32_t *>(row);
+            for (; j + 4 <= x0 + A.tmpl_w; j += 4) s = __dp4a(row32[j >> 2], 0x01010101u, s);
+            for (; j < x0 + A.tmpl_w; ++j) s += row[j];
+            for (int x = x0; x < x1; ++x) {
+                H[r * hp + x] = s;
+                s += (uint32_t)row[x + A.tmpl_w < cwp ? x + A.tmpl_w : cwp - 1] - (uint32_t)row[x];
+            }
         }
     }
     __syncthreads();
-    uint32_t *S = A.wsum + (size_t)g * (A.n_mt * 128) * SM_N + slot;
-    for (int p = tid; p < rw * rh; p += SM_PREP_THREADS) {
+    const int g = f / SM_N, slot = f - g * SM_N;
+    uint32_t *E = A.wsum + (size_t)g * (A.n_mt * 128) * SM_N + slot;
+    for (int p = tid; p < rw * rh; p += SM_EDGE_THREADS) {
         const int y = p / rw, x = p - y * rw;
         uint32_t s = 0;
-        for (int i = 0; i < A.tmpl_h; ++i) s += H[(y + i) * hp + x];
-        S[(size_t)p * SM_N] = s;
+        for (int e = 0; e < y; ++e) s += H[e * hp + x];                     // crop rows 0 .. y - 1
+        for (int e = n_top + y; e < n_edge; ++e) s += H[e * hp + x];        // crop rows y + th .. crop_h - 1
+        E[(size_t)p * SM_N] = s;
     }
 }
 
-// One CTA per group of 32 frames: warp 0 streams the stages (template tiles + the group's frame bytes), warp 1
-// issues the MMAs, warps 2-5 score the accumulators and take the arg-max per frame.
-__global__ void __launch_bounds__(192, 1)
-melf_small_gemm_kernel(const MelfSmallArgs A)
+__global__ void __launch_bounds__(SF_THREADS, 1)
+melf_small_fused_kernel(const MelfSmallArgs A)
 {
     uint8_t *smem = melf_tc_smem;
-    const int stage_bytes = A.n_mt * SM_KS * SM_A_TILE + SM_KS * SM_B_STEP;
-    CtrlS *ctrl = reinterpret_cast<CtrlS *>(smem + SM_STAGES * stage_bytes);
+    const int a_bytes = A.n_mt * SM_KS * SM_A_TILE;
+    uint8_t *b_ring = smem + SF_A_STAGES * a_bytes;
+    uint32_t *cbox = reinterpret_cast<uint32_t *>(b_ring + SF_B_STAGES * SM_B_STAGE);      // [res_w][32 frames]
+    CtrlSF *ctrl = reinterpret_cast<CtrlSF *>(reinterpret_cast<uint8_t *>(cbox) + SF_CBOX_MAX * SM_N * 4);
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int g = blockIdx.x;
     if (tid == 0) {
-        for (int s = 0; s < SM_STAGES; ++s) {
-            mbar_init(smem_u32(&ctrl->full[s]), 1);
-            mbar_init(smem_u32(&ctrl->empty[s]), 1);
-        }
+        for (int s = 0; s < SF_A_STAGES; ++s) { mbar_init(smem_u32(&ctrl->a_full[s]), 1); mbar_init(smem_u32(&ctrl->a_empty[s]), 1); }
+        for (int s = 0; s < SF_B_STAGES; ++s) { mbar_init(smem_u32(&ctrl->b_full[s]), 1); mbar_init(smem_u32(&ctrl->b_empty[s]), 1); }
         mbar_init(smem_u32(&ctrl->accum), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -2404,32 +2436,33 @@ melf_small_gemm_kernel(const MelfSmallArgs A)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = ctrl->tmem_base;
-    const uint32_t smem_base = smem_u32(smem);
-    const int a_bytes = A.n_mt * SM_KS * SM_A_TILE;
+    const uint32_t a_ring_s = smem_u32(smem), b_ring_s = smem_u32(b_ring);
+    const int n_valid = min(SM_N, A.n_frames - g * SM_N);
 
     if (warp == 0) {
+        // ================= template tiles: TMA, 3-stage ring =================
         if (elect_one()) {
-            const u64 pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
-            const uint8_t *bsrc = A.bop + (size_t)g * A.n_kstages * (SM_KS * SM_B_STEP);
+            const u64 pol_keep = policy_evict_last();
             for (int st = 0; st < A.n_kstages; ++st) {
-                const uint32_t slot = (uint32_t)st % SM_STAGES, ph = ((uint32_t)st / SM_STAGES) & 1;
-                mbar_wait(smem_u32(&ctrl->empty[slot]), ph ^ 1);
-                mbar_expect_tx(smem_u32(&ctrl->full[slot]), (uint32_t)stage_bytes);
-                bulk_load_keep(smem_base + slot * stage_bytes, A.tpos + (size_t)st * a_bytes, (uint32_t)a_bytes,
-                               smem_u32(&ctrl->full[slot]), pol_keep);
-                bulk_load_keep(smem_base + slot * stage_bytes + a_bytes, bsrc + (size_t)st * (SM_KS * SM_B_STEP),
-                               SM_KS * SM_B_STEP, smem_u32(&ctrl->full[slot]), pol_stream);
+                const uint32_t slot = (uint32_t)st % SF_A_STAGES, ph = ((uint32_t)st / SF_A_STAGES) & 1;
+                mbar_wait(smem_u32(&ctrl->a_empty[slot]), ph ^ 1);
+                mbar_expect_tx(smem_u32(&ctrl->a_full[slot]), (uint32_t)a_bytes);
+                bulk_load_keep(a_ring_s + slot * a_bytes, A.tpos + (size_t)st * a_bytes, (uint32_t)a_bytes,
+                               smem_u32(&ctrl->a_full[slot]), pol_keep);
             }
         }
     } else if (warp == 1) {
+        // ================= MMA issue =================
         const bool lead = elect_one();
         const uint32_t idesc = make_idesc(SM_N);
         for (int st = 0; st < A.n_kstages; ++st) {
-            const uint32_t slot = (uint32_t)st % SM_STAGES, ph = ((uint32_t)st / SM_STAGES) & 1;
-            mbar_wait(smem_u32(&ctrl->full[slot]), ph);
+            const uint32_t sa = (uint32_t)st % SF_A_STAGES, pa = ((uint32_t)st / SF_A_STAGES) & 1;
+            const uint32_t sb = (uint32_t)st % SF_B_STAGES, pb = ((uint32_t)st / SF_B_STAGES) & 1;
+            mbar_wait(smem_u32(&ctrl->a_full[sa]), pa);
+            mbar_wait(smem_u32(&ctrl->b_full[sb]), pb);
             tc_fence_after();
             if (lead) {
-                const uint32_t abase = smem_base + slot * stage_bytes, bbase = abase + a_bytes;
+                const uint32_t abase = a_ring_s + sa * a_bytes, bbase = b_ring_s + sb * SM_B_STAGE;
                 for (int mt = 0; mt < A.n_mt; ++mt) {
                     if (st < A.mt_k0[mt] || st >= A.mt_k1[mt]) continue;     // all-zero template bytes for this tile
 #pragma unroll
@@ -2437,17 +2470,83 @@ melf_small_gemm_kernel(const MelfSmallArgs A)
                         umma_i8(tmem + (uint32_t)(mt * SM_N), umma_desc(abase + (mt * SM_KS + ks) * SM_A_TILE, BSTRIP_BYTES),
                                 umma_desc(bbase + ks * SM_B_STEP, SM_N * 16), idesc, (st > A.mt_k0[mt] || ks > 0) ? 1u : 0u);
                 }
-                umma_commit(smem_u32(&ctrl->empty[slot]));
+                umma_commit(smem_u32(&ctrl->a_empty[sa]));
+                umma_commit(smem_u32(&ctrl->b_empty[sb]));
             }
             __syncwarp();
         }
         if (lead) umma_commit(smem_u32(&ctrl->accum));
     } else {
+        // ================= frame operand: lane = frame, one stage (64 K bytes of all 32 frames) per turn =================
+        const int ww = warp - SF_WORKER_WARP0;
+        const int f = g * SM_N + lane;
+        const bool have = f < A.n_frames;
+        const uintptr_t limit = reinterpret_cast<uintptr_t>(A.img_limit);
+        const uint8_t *base = A.img + (size_t)(have ? f : 0) * A.frame_stride + (size_t)A.geom.crop_y0 * A.row_stride +
+                              (size_t)A.channels * (size_t)A.geom.crop_x0;
+        const int units = A.cwp >> 4;
+        const int nchunk = A.channels == 3 ? 4 : 2;
+        for (int st = ww; st < A.n_kstages; st += SF_WORKERS) {
+            const uint32_t sb = (uint32_t)st % SF_B_STAGES, pb = ((uint32_t)st / SF_B_STAGES) & 1;
+            mbar_wait(smem_u32(&ctrl->b_empty[sb]), pb ^ 1);
+            uint8_t *bst = b_ring + sb * SM_B_STAGE + lane * 16;
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                uint32_t e[2][17];
+                uint32_t pos2[2];
+                int left2[2];
+                bool live2[2];
+                // the loads of both units first (two 64-byte windows in flight per lane), then the conversions
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int k16 = 4 * st + 2 * half + q;
+                    const int row = k16 / units, u = k16 - row * units;
+                    live2[q] = have && row < A.geom.crop_h && 16 * u < A.geom.crop_w;
+                    left2[q] = A.geom.crop_w - 16 * u;
+                    const uintptr_t src = reinterpret_cast<uintptr_t>(base + (size_t)row * A.row_stride) + (uintptr_t)(16 * A.channels * u);
+                    pos2[q] = (uint32_t)(src & 15);
+                    const uint4 *al = reinterpret_cast<const uint4 *>(src & ~(uintptr_t)15);
+#pragma unroll
+                    for (int cidx = 0; cidx < 4; ++cidx) {
+                        uint4 v = make_uint4(0, 0, 0, 0);
+                        if (live2[q] && cidx < nchunk && reinterpret_cast<uintptr_t>(al + cidx) + 16 <= limit) v = __ldg(al + cidx);
+                        e[q][4 * cidx] = v.x; e[q][4 * cidx + 1] = v.y; e[q][4 * cidx + 2] = v.z; e[q][4 * cidx + 3] = v.w;
+                    }
+                    e[q][16] = 0;
+                }
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    uint4 out = make_uint4(0, 0, 0, 0);
+                    if (live2[q]) out = sm_convert16(e[q], pos2[q], A.channels, left2[q]);
+                    // unit j of the stage = K-step j >> 1, strip j & 1: [K-step][strip][frame][16 B]
+                    *reinterpret_cast<uint4 *>(bst + (2 * half + q) * (SM_N * 16)) = out;
+                }
+            }
+            fence_async_smem();                    // generic-proxy writes before the MMA's async-proxy reads
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&ctrl->b_full[sb]));
+        }
+    }
+    if (warp >= 2 && warp < 6) {
+        // ================= scores and arg-max per frame (four of the worker warps, one per TMEM lane quadrant) =================
         const int qd = warp & 3;
+        const int et = tid - 64;                                           // 0 .. 127
+        const int rw = A.geom.res_w;
         mbar_wait(smem_u32(&ctrl->accum), 0);
         tc_fence_after();
         const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;
-        const int n_valid = min(SM_N, A.n_frames - g * SM_N);
+        // the box sums over all rows: accumulator lanes n_pos .. n_pos + res_w - 1, to shared memory
+        for (int mt = A.n_pos >> 7; mt < A.n_mt; ++mt) {
+            const int pos = mt * 128 + 32 * qd + lane;
+            uint32_t d[33];
+            tmem_ld32(tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(mt * SM_N), d);
+            tmem_ld_wait();
+            if (pos >= A.n_pos && pos < A.n_pos + rw) {
+#pragma unroll
+                for (int k = 0; k < SM_N; ++k) cbox[(pos - A.n_pos) * SM_N + k] = d[k];
+            }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
         // best key of a frame over the 32 positions of this warp, then one shared-memory atomic per warp
         auto q4_keys = [&](int q4, u64 (&k4)[4]) {
 #pragma unroll
@@ -2461,18 +2560,21 @@ melf_small_gemm_kernel(const MelfSmallArgs A)
                 if (lane == 0 && 4 * q4 + k < n_valid && best) atomicMax(&ctrl->keys[4 * q4 + k], best);
             }
         };
-        for (int mt = 0; mt < A.n_mt; ++mt) {
+        const int n_score_mt = (A.n_pos + 127) >> 7;
+        for (int mt = 0; mt < n_score_mt; ++mt) {
             const int pos = mt * 128 + 32 * qd + lane;
             u64 keys4[4];
             uint32_t d[33];
             tmem_ld32(tmem + ((uint32_t)(32 * qd) << 16) + (uint32_t)(mt * SM_N), d);
             tmem_ld_wait();
             if (pos < A.n_pos) {
-                const uint4 *S = reinterpret_cast<const uint4 *>(A.wsum + ((size_t)g * (A.n_mt * 128) + pos) * SM_N);
+                const int x = pos % rw;
+                const uint4 *E = reinterpret_cast<const uint4 *>(A.wsum + ((size_t)g * (A.n_mt * 128) + pos) * SM_N);
+                const uint4 *C = reinterpret_cast<const uint4 *>(cbox + x * SM_N);
 #pragma unroll
                 for (int q4 = 0; q4 < SM_N / 4; ++q4) {
-                    const uint4 sw = __ldcg(S + q4);
-                    const uint32_t s4[4] = {sw.x, sw.y, sw.z, sw.w};
+                    const uint4 ew = __ldcg(E + q4), cwv = C[q4];
+                    const uint32_t s4[4] = {cwv.x - ew.x, cwv.y - ew.y, cwv.z - ew.z, cwv.w - ew.w};
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         const long long num = (long long)((u64)n_t32 * (u64)d[4 * q4 + k]) - (long long)((u64)sum_t32 * (u64)s4[k]);
@@ -2490,7 +2592,6 @@ melf_small_gemm_kernel(const MelfSmallArgs A)
         }
         tc_fence_before();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int et = tid - 64;
         if (et < n_valid) A.match_key[(size_t)g * SM_N + et] = ctrl->keys[et];
     }
     tc_fence_before();
@@ -2506,20 +2607,22 @@ bool melf_match_small_supported(const MelfGeom &g, int tmpl_w, int tmpl_h, int c
     const long long n_pos = (long long)g.res_w * g.res_h;
     const int cwp = (g.crop_w + 31) & ~31;
     const long long k_total = (long long)g.crop_h * cwp;
-    const long long prep_smem = g.crop_h <= 1024 ? sm_prep_smem(channels, g.crop_w, g.crop_h, cwp, g.res_w) : (1 << 30);
-    return n_pos <= SM_MT_MAX * 128 && tmpl_w <= g.crop_w && tmpl_h <= g.crop_h && k_total <= 64 * 1024 &&
-           prep_smem <= 200 * 1024 && g.crop_h <= 1024;
+    return n_pos + g.res_w <= SM_MT_MAX * 128 && g.res_w <= SF_CBOX_MAX && tmpl_w <= g.crop_w && tmpl_h <= g.crop_h &&
+           k_total <= 64 * 1024 && g.res_h <= 64 &&
+           sm_edge_smem(channels, g.crop_w, cwp, g.res_w, g.res_h) <= 200 * 1024;
 }
 
 void melf_match_small_plan(MelfSmallArgs &a)
 {
     a.n_pos = a.geom.res_w * a.geom.res_h;
-    a.n_mt = (a.n_pos + 127) / 128;
+    const int n_rows = a.n_pos + a.geom.res_w;                       // + the box-sum rows
+    a.n_mt = (n_rows + 127) / 128;
     a.cwp = (a.geom.crop_w + 31) & ~31;
     a.n_kstages = (a.geom.crop_h * a.cwp + 32 * SM_KS - 1) / (32 * SM_KS);
     for (int mt = 0; mt < SM_MT_MAX; ++mt) { a.mt_k0[mt] = 0; a.mt_k1[mt] = 0; }
     for (int mt = 0; mt < a.n_mt; ++mt) {
-        const int p0 = mt * 128, p1 = (p0 + 128 < a.n_pos ? p0 + 128 : a.n_pos) - 1;
+        const int p0 = mt * 128, p1 = (p0 + 128 < n_rows ? p0 + 128 : n_rows) - 1;
+        if (p1 >= a.n_pos) { a.mt_k0[mt] = 0; a.mt_k1[mt] = a.n_kstages; continue; }   // a box-sum row: every crop row
         const int y0 = p0 / a.geom.res_w, y1 = p1 / a.geom.res_w;
         const long long k_lo = (long long)y0 * a.cwp, k_hi = (long long)(y1 + a.tmpl_h) * a.cwp;
         a.mt_k0[mt] = (int)(k_lo / (32 * SM_KS));
@@ -2529,46 +2632,45 @@ void melf_match_small_plan(MelfSmallArgs &a)
 }
 
 size_t melf_match_small_tpos_bytes(const MelfSmallArgs &a) { return (size_t)a.n_kstages * a.n_mt * SM_KS * SM_A_TILE; }
-size_t melf_match_small_bop_bytes(const MelfSmallArgs &a)
-{
-    return (size_t)((a.n_frames + SM_N - 1) / SM_N) * a.n_kstages * (SM_KS * SM_B_STEP) + 64;
-}
 size_t melf_match_small_wsum_bytes(const MelfSmallArgs &a)
 {
     return (size_t)((a.n_frames + SM_N - 1) / SM_N) * (a.n_mt * 128) * SM_N * 4;
 }
 
-// Tpos: [K stage][position tile][K-step][strip][128 positions][16 B], byte = T(r - y, c - x) for K index (r, c)
+// Tpos: [K stage][position tile][K-step][strip][128 rows][16 B]; row = position (y, x): byte = T(r - y, c - x) for
+// K index (r, c); row n_pos + x: 1 for every crop row r and x <= c < x + tw (the box sum C(x))
 void melf_match_small_build_tpos(const MelfSmallArgs &a, const uint8_t *tmpl, uint8_t *out)
 {
     std::memset(out, 0, melf_match_small_tpos_bytes(a));
+    auto at = [&](int row, long long k) -> uint8_t & {
+        const long long kstep = k >> 5;
+        const int st = (int)(kstep / SM_KS), ks = (int)(kstep % SM_KS), strip = (int)((k >> 4) & 1), b = (int)(k & 15);
+        const int mt = row >> 7, m = row & 127;
+        return out[((((size_t)st * a.n_mt + mt) * SM_KS + ks) * 2 + strip) * BSTRIP_BYTES + (size_t)m * 16 + b];
+    };
     for (int pos = 0; pos < a.n_pos; ++pos) {
         const int y = pos / a.geom.res_w, x = pos - y * a.geom.res_w;
-        const int mt = pos >> 7, m = pos & 127;
         for (int i = 0; i < a.tmpl_h; ++i)
-            for (int j = 0; j < a.tmpl_w; ++j) {
-                const long long k = (long long)(y + i) * a.cwp + (x + j);
-                const long long kstep = k >> 5;
-                const int st = (int)(kstep / SM_KS), ks = (int)(kstep % SM_KS), strip = (int)((k >> 4) & 1), b = (int)(k & 15);
-                out[((((size_t)st * a.n_mt + mt) * SM_KS + ks) * 2 + strip) * BSTRIP_BYTES + (size_t)m * 16 + b] =
-                    tmpl[(size_t)i * a.tmpl_w + j];
-            }
+            for (int j = 0; j < a.tmpl_w; ++j) at(pos, (long long)(y + i) * a.cwp + (x + j)) = tmpl[(size_t)i * a.tmpl_w + j];
     }
+    for (int x = 0; x < a.geom.res_w; ++x)
+        for (int r = 0; r < a.geom.crop_h; ++r)
+            for (int j = 0; j < a.tmpl_w; ++j) at(a.n_pos + x, (long long)r * a.cwp + (x + j)) = 1;
 }
 
 cudaError_t melf_launch_match_small(const MelfSmallArgs &a, cudaStream_t stream)
 {
-    const int cw = a.geom.crop_w, ch = a.geom.crop_h;
-    const int prep_smem = sm_prep_smem(a.channels, cw, ch, a.cwp, a.geom.res_w);
-    cudaError_t e = cudaFuncSetAttribute(melf_small_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, prep_smem);
+    const int edge_smem = sm_edge_smem(a.channels, a.geom.crop_w, a.cwp, a.geom.res_w, a.geom.res_h);
+    cudaError_t e = cudaFuncSetAttribute(melf_small_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, edge_smem);
     if (e != cudaSuccess) return e;
-    const int gemm_smem = SM_STAGES * (a.n_mt * SM_KS * SM_A_TILE + SM_KS * SM_B_STEP) + (int)sizeof(CtrlS);
-    e = cudaFuncSetAttribute(melf_small_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem);
+    const int fused_smem = SF_A_STAGES * (a.n_mt * SM_KS * SM_A_TILE) + SF_B_STAGES * SM_B_STAGE + SF_CBOX_MAX * SM_N * 4 +
+                           (int)sizeof(CtrlSF);
+    e = cudaFuncSetAttribute(melf_small_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem);
     if (e != cudaSuccess) return e;
     if (a.n_frames <= 0) return cudaSuccess;
-    melf_small_prep_kernel<<<a.n_frames, SM_PREP_THREADS, prep_smem, stream>>>(a);
+    melf_small_edge_kernel<<<a.n_frames, SM_EDGE_THREADS, edge_smem, stream>>>(a);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    melf_small_gemm_kernel<<<(a.n_frames + SM_N - 1) / SM_N, 192, gemm_smem, stream>>>(a);
+    melf_small_fused_kernel<<<(a.n_frames + SM_N - 1) / SM_N, SF_THREADS, fused_smem, stream>>>(a);
     return cudaGetLastError();
 }

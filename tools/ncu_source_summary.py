@@ -14,6 +14,14 @@ def main():
     text = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], stdout=subprocess.PIPE,
                           stderr=subprocess.DEVNULL, text=True).stdout
     rows = list(csv.reader(text.splitlines()))
+    # one section per kernel: a "Kernel Name" row, a header row, then the instructions
+    starts = [i for (i, r) in enumerate(rows) if r and r[0] == 'Kernel Name'] + [len(rows)]
+    for (a, b) in zip(starts[:-1], starts[1:]):
+        section(rows[a:b], top_n)
+        print()
+
+
+def section(rows, top_n):
     print('#', rows[0][1] if len(rows[0]) > 1 else rows[0])
     hdr = rows[1]
     data = [r for r in rows[2:] if len(r) >= len(hdr)]
