@@ -128,6 +128,9 @@ int melf_dial_window(const melf_ctx *ctx, int dial, int32_t *win_x0, int32_t *wi
 #define MELF_PROF_JPEG_COLOR   8    /* melf_jpeg_color_kernel                                 */
 #define MELF_PROF_KINDS      9
 int melf_profile_enable(melf_ctx *ctx, int on);
+/* Name of the locate kernel the last call on this ctx took (size dispatch: Toeplitz tcgen05 kernel, small-map
+ * GEMM, dp4a kernel for templates the tensor kernels do not fit); for measurement records. */
+const char *melf_last_locate(const melf_ctx *ctx);
 int melf_profile_read(melf_ctx *ctx, float *ms /*[MELF_PROF_KINDS]*/, int32_t *launches /*[MELF_PROF_KINDS]*/);
 
 /* ---- the hot path -------------------------------------------------------------- */

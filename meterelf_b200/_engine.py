@@ -79,7 +79,7 @@ _SYMBOLS = (
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
     'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch',
-    'melf_in_range', 'melf_file_sizes', 'melf_read_files', 'melf_jpeg_probe_batch')
+    'melf_in_range', 'melf_file_sizes', 'melf_read_files', 'melf_jpeg_probe_batch', 'melf_last_locate')
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a', 'jpeg_upload', 'jpeg_destuff',
                  'jpeg_huffman', 'jpeg_idct', 'jpeg_color')
@@ -140,6 +140,8 @@ def load_library() -> C.CDLL:
         lib.melf_file_sizes.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_void_p]
         lib.melf_read_files.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.melf_jpeg_probe_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        lib.melf_last_locate.restype = C.c_char_p
+        lib.melf_last_locate.argtypes = [C.c_void_p]
         lib.melf_profile_enable.argtypes = [C.c_void_p, C.c_int]
         lib.melf_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
         _lib = lib
@@ -241,6 +243,10 @@ class Engine:
         cnt = (C.c_int32 * len(PROFILE_KINDS))()
         self._check(self.lib.melf_profile_read(self._ctx, ms, cnt))
         return {k: (float(ms[i]), int(cnt[i])) for (i, k) in enumerate(PROFILE_KINDS)}
+
+    def last_locate(self) -> str:
+        """Which locate kernel the last call took (size dispatch inside the library)."""
+        return (self.lib.melf_last_locate(self._ctx) or b'').decode()
 
     def dial_window(self, dial: int) -> Tuple[int, int]:
         x = C.c_int32()

@@ -4,7 +4,7 @@
 is done by ``read_image_files`` which maps the C ABI's per-frame status codes back onto
 the reference's exception classes, messages and ``extra_info`` dicts.
 """
-import math
+import re
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy
@@ -123,18 +123,34 @@ def read_image_files(params: _Params, imgfs: Sequence[ImageFile], device: int = 
                     numpy.cumsum([len(p) for p in parts], out=sub_offsets[1:])
                     sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
                 indices = [from_file[k] for k in members.tolist()]
-                try:
-                    records = engine.read_jpeg_blob(sub_blob, sub_offsets)
-                except _engine.EngineError as error:
-                    if error.code == _engine.ERR_TOO_SMALL:
-                        for index in indices:
-                            out[index] = Deferred(ValueError(
-                                'image smaller than the dials template: ' + imgfs[index].filename))
-                        continue
-                    if error.code not in (_engine.ERR_INVALID, _engine.ERR_UNSUPPORTED):
-                        raise
-                    # a stream the header probe accepted but the decoder rejects:
-                    # cv2.imread decides what the reference would have seen
+                records = None
+                for _attempt in range(9):
+                    try:
+                        records = engine.read_jpeg_blob(sub_blob, sub_offsets)
+                        break
+                    except _engine.EngineError as error:
+                        if error.code == _engine.ERR_TOO_SMALL:
+                            for index in indices:
+                                out[index] = Deferred(ValueError(
+                                    'image smaller than the dials template: ' + imgfs[index].filename))
+                            indices = []
+                            break
+                        if error.code not in (_engine.ERR_INVALID, _engine.ERR_UNSUPPORTED):
+                            raise
+                        # a stream the header probe accepted but the decoder rejects: cv2.imread decides what
+                        # the reference would have seen for THAT file; the others stay on the GPU
+                        bad = re.search(r'stream (\d+):', str(error))
+                        if bad is None or not 0 <= int(bad.group(1)) < len(indices) or len(indices) == 1:
+                            break
+                        drop = int(bad.group(1))
+                        host_decode.append(indices.pop(drop))
+                        lengths = numpy.diff(sub_offsets).astype(numpy.int64)
+                        keep = [k for k in range(len(lengths)) if k != drop]
+                        parts = [sub_blob[int(sub_offsets[k]):int(sub_offsets[k + 1])] for k in keep]
+                        sub_offsets = numpy.zeros(len(parts) + 1, numpy.uint64)
+                        numpy.cumsum(lengths[keep], out=sub_offsets[1:])
+                        sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
+                if records is None:
                     host_decode.extend(indices)
                     continue
                 converted = records_to_python(records, engine.names, [imgfs[i].filename for i in indices])

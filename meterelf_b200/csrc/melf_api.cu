@@ -96,6 +96,7 @@ struct melf_ctx {
     // small-result-map path (positions as M, frames as N): template per position for ONE crop geometry,
     // built on first use; frame operand + window sums per scratch slot
     std::vector<uint8_t> h_tmpl;
+    const char *last_locate = "";    // which locate kernel the last call took (measurement: melf_last_locate)
     uint8_t *d_tpos = nullptr;
     int tpos_crop_w = -1, tpos_crop_h = -1;
     uint32_t *d_small_wsum[kScratchSlots] = {};
@@ -227,6 +228,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         }
     }
     if (small_path) {
+        ctx->last_locate = "melf_small_fused_kernel";
         MelfSmallArgs a{};
         a.img = d_img;
         const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride + (size_t)w * channels;
@@ -260,6 +262,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         return MELF_OK;
     }
     if (ctx->use_tc) {
+        ctx->last_locate = "melf_match_fused_ov_kernel";
         MelfMatchTcArgs t{};
         t.img = d_img;
         const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride +
@@ -343,6 +346,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         }
         return MELF_OK;
     }
+    ctx->last_locate = "melf_match_kernel";
     MelfMatchArgs m{};
     fill_match_args(ctx, &m);
     m.channels = channels;
@@ -611,6 +615,8 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
 }
 
 void melf_destroy(melf_ctx *ctx) { free_ctx(ctx); }
+
+const char *melf_last_locate(const melf_ctx *ctx) { return ctx ? ctx->last_locate : ""; }
 
 int melf_profile_enable(melf_ctx *ctx, int on)
 {
