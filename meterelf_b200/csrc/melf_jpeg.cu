@@ -913,6 +913,9 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     static const int walk_threads = [] {
         const char *e = std::getenv("MELF_JPEG_HOST_THREADS");
         int v = e ? std::atoi(e) : (int)std::thread::hardware_concurrency() / 2;
+        // one process per GPU on the same host (torchrun): share the cores
+        const char *lws = std::getenv("LOCAL_WORLD_SIZE");
+        if (!e && lws && std::atoi(lws) > 1) v /= std::atoi(lws);
         return v < 1 ? 1 : v > 8 ? 8 : v;
     }();
     const int nt = count >= 2048 ? walk_threads : 1;
