@@ -270,6 +270,7 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
         t.img_limit = reinterpret_cast<const uint8_t *>((reinterpret_cast<uintptr_t>(end) + 15) & ~(uintptr_t)15);
         t.row_stride = row_stride; t.frame_stride = frame_stride;
         t.channels = channels;
+        t.img_w = w; t.img_h = h; t.img_n = n;
         t.geom = geom;
         t.toeplitz = ctx->d_toeplitz;
         t.tmpl_w = ctx->params.tmpl_w; t.tmpl_h = ctx->params.tmpl_h;

@@ -73,6 +73,9 @@ struct MelfMatchTcArgs {
     uint32_t *wsum;              // [max_items][64][137] window sums, x-major
     long long item0, max_items;
     long long *timeline;         // optional debug: clock64 stamps of CTA 0's first 8 passes, 8 per pass
+    int32_t img_w, img_h;        // whole frames as the caller holds them (tensor map of the batch)
+    long long img_n;
+    int32_t use_tmap;            // set by the launcher: frame bytes staged by tiled tensor copies
     int32_t debug_skip;          // measurement only (MELF_TC_DEBUG_SKIP, results become wrong): bit 0 no staging after
                                  // the prologue, bit 1 no window sums, bit 2 no drain, bit 3 no MMAs,
                                  // bit 4 staging without its global loads, bit 5 staging without the conversion

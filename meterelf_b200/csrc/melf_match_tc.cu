@@ -35,6 +35,7 @@
 // Everything is integer-exact, so results are bit-identical to melf_match.cu and to the
 // oracle.
 #include <cstring>
+#include <cuda.h>
 
 #include "melf_common.cuh"
 #include "melf_args.h"
@@ -45,7 +46,10 @@
 
 namespace {
 
-constexpr int TC_THREADS = 512;
+#ifndef MELF_TC_THREADS
+#define MELF_TC_THREADS 512
+#endif
+constexpr int TC_THREADS = MELF_TC_THREADS;
 constexpr int SLAB_ROWS = 264;                       // rows of a lightness slab (118 + 144 -> 264)
 constexpr int SLAB_DATA_ROWS = 256;                  // rows that can hold image data (plan cap)
 constexpr int KS = 16;                               // 16-byte K strips: K = 256
@@ -833,7 +837,9 @@ __device__ __forceinline__ void bulk_load_keep(uint32_t dst, const void *src, ui
 // is melf_lightness()'s operation order, two pixels per packed f32x2 instruction:
 //     vmax = fl(max * k), vmin = fl(min * k)   as fma(2^23 + v, k, -2^23 k): exact product, one rounding
 //     L = rint(fl(fl(vmax + vmin) * 127.5))    (x * .5) * 255 == x * 127.5; rint = + 1.5 * 2^23
-__device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12])
+// P = byte at which the first pixel starts inside v[0] (0 for callers that have aligned the words themselves)
+template <int P, int NW>
+__device__ __forceinline__ uint4 lightness16_at(const uint32_t (&v)[NW])
 {
     const float2 k = melf_f2(1.f / 255.f), c = melf_f2(-8388608.f * (1.f / 255.f));
     const float2 half255 = melf_f2(127.5f), M = melf_f2(MELF_MAGIC_RINT);
@@ -843,7 +849,7 @@ __device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12])
         uint32_t lb[4];
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
-            const int b0 = 12 * g + 6 * q;                   // byte index of B of the first pixel of the pair
+            const int b0 = P + 12 * g + 6 * q;               // byte index of B of the first pixel of the pair
             uint32_t ch[3];
 #pragma unroll
             for (int cidx = 0; cidx < 3; ++cidx) {
@@ -869,6 +875,30 @@ __device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12])
         o[g] = __byte_perm(lo2, hi2, 0x5410);
     }
     return make_uint4(o[0], o[1], o[2], o[3]);
+}
+__device__ __forceinline__ uint4 lightness16(const uint32_t (&v)[12]) { return lightness16_at<0, 12>(v); }
+// the same for 16 words holding the 48 bytes from byte `p` (0..15) on: the shift is folded into the byte
+// selectors, one instance per phase behind a warp-uniform switch
+__device__ __forceinline__ uint4 lightness16_phase(const uint32_t (&e)[16], uint32_t p)
+{
+    switch (p) {
+    case 0: return lightness16_at<0, 16>(e);
+    case 1: return lightness16_at<1, 16>(e);
+    case 2: return lightness16_at<2, 16>(e);
+    case 3: return lightness16_at<3, 16>(e);
+    case 4: return lightness16_at<4, 16>(e);
+    case 5: return lightness16_at<5, 16>(e);
+    case 6: return lightness16_at<6, 16>(e);
+    case 7: return lightness16_at<7, 16>(e);
+    case 8: return lightness16_at<8, 16>(e);
+    case 9: return lightness16_at<9, 16>(e);
+    case 10: return lightness16_at<10, 16>(e);
+    case 11: return lightness16_at<11, 16>(e);
+    case 12: return lightness16_at<12, 16>(e);
+    case 13: return lightness16_at<13, 16>(e);
+    case 14: return lightness16_at<14, 16>(e);
+    default: return lightness16_at<15, 16>(e);
+    }
 }
 
 // 16 consecutive pixels of slab row r / strip s of an item (fused kernel's version of stage_unit)
@@ -1308,6 +1338,98 @@ __device__ __forceinline__ void stage_slabs_tma(const MelfMatchTcArgs &A, const 
     }
 }
 
+// stage_slabs_tma with ONE tiled tensor copy per unit instead of eight row copies: the frame batch is described
+// by a 3-D tensor map (bytes of a row, rows, frames; built per launch by melf_launch_match_fused_ov when the
+// caller's base address and strides are multiples of 16), the box is 8 rows x (64 pixels + 16 bytes) from the
+// 16-byte boundary at or before the unit's first pixel.  (The innermost start coordinate of a u8 tensor copy has
+// to be a multiple of 16 BYTES: anything else ends the kernel with "illegal instruction" -- tools/tmap_probe.cu,
+// measured on this B200; the 16 spare bytes of the box are for that.)  Against the row copies this removes, per
+// unit, the eight-trip issue loop (a divergent UBLKCP is serialised lane by lane) and the twelve funnel shifts that
+// realigned each lane's window: with 16-byte-multiple strides the byte phase is the same for every unit of the
+// launch, so it is folded into the conversion's byte selectors (lightness16_phase).
+// The 208-byte row pitch keeps the quarter-warp's eight rows on eight different 16-byte bank groups (13 r mod 8).
+// Rows and bytes beyond the frame come back as zeros (tensor-map bounds), so there is no end-of-memory clamp.
+__device__ __forceinline__ void tensor_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2,
+                                               uint32_t bar, u64 pol)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+                 " [%0], [%1, {%2, %3, %4}], [%5], %6;"
+                 :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar), "l"(pol)
+                 : "memory");
+}
+
+__device__ __forceinline__ void stage_slabs_tmap(const MelfMatchTcArgs &A, const CUtensorMap *map, const Item (&its)[2],
+                                                 uint8_t *scratch, uint8_t *wbuf, uint32_t bar, uint32_t &phase,
+                                                 int wwarp, int lane)
+{
+    const int pitch = 64 * A.channels + 16;                                // box row: 208 (BGR) / 80 bytes
+    const uint32_t box_bytes = 8u * (uint32_t)pitch;
+    const uint32_t wbuf_s = smem_u32(wbuf);
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+        const Item it = slot ? its[1] : its[0];
+        if (!it.valid) continue;
+        const int n_rows = min(SLAB_DATA_ROWS, A.geom.crop_h - it.y0);
+        const int n_units = ((n_rows + 7) >> 3) * 4;
+        uint8_t *dst = scratch + (size_t)slot * SLAB_BYTES;
+        const u64 pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
+        // first byte of the item's rows; 64-pixel segments are whole 16-byte chunks, so `ph` holds for every unit
+        const int cx0 = A.channels * (A.geom.crop_x0 + it.x0), cy0 = A.geom.crop_y0 + it.y0;
+        const uint32_t ph = (uint32_t)cx0 & 15u;
+        auto issue = [&](int u) {
+            if (lane == 0) {
+                mbar_expect_tx(bar, box_bytes);
+                tensor_load_3d(wbuf_s, map, (cx0 & ~15) + 64 * A.channels * (u & 3), cy0 + 8 * (u >> 2), it.frame, bar, pol_stream);
+            }
+        };
+        if (wwarp < n_units) issue(wwarp);
+#pragma unroll 1
+        for (int u = wwarp; u < n_units; u += F_WORKER_WARPS) {
+            const int rg = u >> 2, sg = u & 3;
+            mbar_wait(bar, phase & 1);
+            ++phase;
+            const int r = lane & 7, sl = lane >> 3;
+            const int row = rg * 8 + r, sidx = sg * 4 + sl;
+            const bool live = it.y0 + row < A.geom.crop_h && it.x0 + 16 * sidx < A.geom.crop_w;
+            const uint8_t *rp = wbuf + r * pitch + 16 * A.channels * sl;
+            const int n_chunks = A.channels == 3 ? 4 : 2;
+            uint32_t e[16];
+#pragma unroll
+            for (int cidx = 0; cidx < 4; ++cidx) {
+                uint4 q = make_uint4(0, 0, 0, 0);
+                if (live && cidx < n_chunks) q = *reinterpret_cast<const uint4 *>(rp + 16 * cidx);
+                e[4 * cidx] = q.x; e[4 * cidx + 1] = q.y; e[4 * cidx + 2] = q.z; e[4 * cidx + 3] = q.w;
+            }
+            {
+                // the loads must have RETURNED (not just been issued) before the buffer is handed back
+                uint32_t seen;
+                asm volatile("xor.b32 %0, %1, %2;\n\txor.b32 %0, %0, %3;\n\txor.b32 %0, %0, %4;"
+                             : "=r"(seen) : "r"(e[0]), "r"(e[4]), "r"(e[8]), "r"(e[12]));
+                (void)seen;
+            }
+            __syncwarp();
+            if (u + F_WORKER_WARPS < n_units) issue(u + F_WORKER_WARPS);
+            uint4 out = make_uint4(0, 0, 0, 0);
+            if (live) {
+                if (A.channels == 3) {
+                    out = lightness16_phase(e, ph);
+                } else {
+                    const uint32_t ws = ph >> 2, bs = (ph & 3u) * 8;
+                    uint32_t v[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t lo = ws == 0 ? e[j] : ws == 1 ? e[j + 1] : ws == 2 ? e[j + 2] : e[j + 3];
+                        const uint32_t hi = ws == 0 ? e[j + 1] : ws == 1 ? e[j + 2] : ws == 2 ? e[j + 3] : e[j + 4];
+                        v[j] = __funnelshift_r(lo, hi, bs);
+                    }
+                    out = make_uint4(v[0], v[1], v[2], v[3]);
+                }
+            }
+            stg_keep(reinterpret_cast<uint4 *>(dst + sidx * STRIP_BYTES + row * 16), out, pol_keep);
+        }
+    }
+}
+
 // stage_slabs with the frame bytes passing through shared memory: every group of RING_ROWS crop rows is
 // fetched with cp.async (16-byte chunks, no registers held while the bytes are in flight) into one of two
 // ring buffers while the previous group is converted out of the other.  The straight version waits ~2.6 k
@@ -1738,7 +1860,7 @@ struct CtrlO {
 
 template <bool WRITE_MAP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
+melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUtensorMap frames_map)
 {
     uint8_t *smem = melf_tc_smem;
     CtrlO *ctrl = reinterpret_cast<CtrlO *>(smem + F_SMEM_CTRL);
@@ -1895,8 +2017,9 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
         const int wt = tid - 64, wwarp = warp - 2;
         const int qd = warp & 3;                               // TMEM lane quadrant this warp can read
         // drain duty inside the quadrant: quadrants 0, 1 have the warps 4,8,12 / 5,9,13; 2, 3 have four
-        const int q_members = qd < 2 ? 3 : 4;
-        const int q_index = (warp - (qd < 2 ? 4 + qd : qd)) >> 2;
+        const int q_first = qd < 2 ? 4 + qd : qd;
+        const int q_members = (TC_THREADS / 32 - 1 - q_first) / 4 + 1;
+        const int q_index = (warp - q_first) >> 2;
         const int x = 16 * qd + (lane >> 1);                       // result column inside the item
         const int odd = lane & 1;
         const uint32_t n_t32 = (uint32_t)A.n_t, sum_t32 = (uint32_t)A.sum_t;      // <= 193 * 128 (* 255)
@@ -1911,7 +2034,10 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
 #if MELF_STAGE_RING
             stage_slabs_ring(A, its, scratch, smem + F_SMEM_H, wt);
 #elif MELF_STAGE_TMA
-            stage_slabs_tma(A, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+            if (A.use_tmap)
+                stage_slabs_tmap(A, &frames_map, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+            else
+                stage_slabs_tma(A, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
 #elif MELF_STAGE_COALESCED
             stage_slabs_co(A, its, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, wwarp, lane);
 #else
@@ -1950,7 +2076,10 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
 #if MELF_STAGE_RING
                 stage_slabs_ring(A, nxt, scratch, smem + F_SMEM_H, wt);
 #elif MELF_STAGE_TMA
-                stage_slabs_tma(A, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+                if (A.use_tmap)
+                    stage_slabs_tmap(A, &frames_map, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
+                else
+                    stage_slabs_tma(A, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, smem_u32(&ctrl->stage[wwarp]), stage_phase, wwarp, lane);
 #elif MELF_STAGE_COALESCED
                 stage_slabs_co(A, nxt, scratch, smem + F_SMEM_H + wwarp * CO_BUF_BYTES, wwarp, lane);
 #else
@@ -2100,8 +2229,40 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A)
 
 size_t melf_match_fused_ov_scratch_bytes(int num_sms) { return (size_t)num_sms * F_SCRATCH_PER_CTA_OV; }
 
-cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms, cudaStream_t stream)
+// Tensor map of the caller's frame batch for stage_slabs_tmap: (bytes of a row, rows, frames), box = 8 rows x
+// (64 pixels + 16 bytes).  False when the batch cannot be described (base or strides not multiples of 16,
+// driver entry point missing): the kernel then stages with the per-row bulk copies, which take any alignment.
+static bool make_frames_map(const MelfMatchTcArgs &a, CUtensorMap *map)
 {
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                 const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = [] {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) fn = nullptr;
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
+    static const bool off = std::getenv("MELF_STAGE_TMAP") && !std::atoi(std::getenv("MELF_STAGE_TMAP"));
+    if (!encode || off || a.img_w <= 0 || a.img_h <= 0 || a.img_n <= 0) return false;
+    if ((reinterpret_cast<uintptr_t>(a.img) & 15) || (a.row_stride & 15) || (a.frame_stride & 15)) return false;
+    if (a.channels != 1 && a.channels != 3) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)a.img_w * (cuuint64_t)a.channels, (cuuint64_t)a.img_h, (cuuint64_t)a.img_n};
+    const cuuint64_t strides[2] = {(cuuint64_t)a.row_stride, (cuuint64_t)a.frame_stride};
+    const cuuint32_t box[3] = {(cuuint32_t)(64 * a.channels + 16), 8, 1};
+    const cuuint32_t elem[3] = {1, 1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t *>(a.img), dims, strides, box, elem,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args_in, int num_sms, cudaStream_t stream)
+{
+    MelfMatchTcArgs args = args_in;
+    alignas(64) CUtensorMap frames_map;
+    std::memset(&frames_map, 0, sizeof frames_map);
+    args.use_tmap = make_frames_map(args, &frames_map) ? 1 : 0;
     cudaError_t e = cudaFuncSetAttribute(melf_match_fused_ov_kernel<false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_TOTAL);
     if (e != cudaSuccess) return e;
@@ -2112,9 +2273,9 @@ cudaError_t melf_launch_match_fused_ov(const MelfMatchTcArgs &args, int num_sms,
     const long long n_pass = (args.n_items + 1) / 2;
     const unsigned grid = (unsigned)(n_pass < num_sms ? n_pass : num_sms);
     if (args.result)
-        melf_match_fused_ov_kernel<true><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+        melf_match_fused_ov_kernel<true><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args, frames_map);
     else
-        melf_match_fused_ov_kernel<false><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args);
+        melf_match_fused_ov_kernel<false><<<grid, TC_THREADS, F_SMEM_TOTAL, stream>>>(args, frames_map);
     return cudaGetLastError();
 }
 
