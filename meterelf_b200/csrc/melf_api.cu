@@ -223,7 +223,8 @@ int launch_locate(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int 
             const long long groups = ((long long)n + 31) / 32, sms = ctx->num_sms;
             const long long t_small = ((groups + sms - 1) / sms) * (long long)plan.n_kstages * plan.n_mt * 2 * 132 + 35ll * n;
             const long long n_pairs = (ctx->params.tmpl_h + 1) / 2;
-            const long long t_toeplitz = (((long long)n + 2 * sms - 1) / (2 * sms)) * (n_pairs * 16 * 78 + 4000);
+            const long long kpp = std::min(8, (ctx->params.tmpl_w + 63 + 31) / 32);      // K-steps per pair that are not all zero
+            const long long t_toeplitz = (((long long)n + 2 * sms - 1) / (2 * sms)) * (n_pairs * 2 * kpp * 78 + 4000);
             small_path = t_small < t_toeplitz;
         }
     }

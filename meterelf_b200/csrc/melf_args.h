@@ -61,6 +61,7 @@ struct MelfMatchTcArgs {
     MelfGeom geom;
     const uint8_t *toeplitz;     // [n_pairs][16 strips][128][16 B] Toeplitz operands of the template
     int32_t tmpl_w, tmpl_h, n_pairs;
+    int32_t kpp;                 // K-steps (of 32) of a pair that can hold a template byte: ceil((63 + tmpl_w) / 32) <= 8
     int32_t n_tx, n_ty, chunk_h; // work items per frame: 64-column tiles x row chunks
     long long n_items;
     long long sum_t, n_t;

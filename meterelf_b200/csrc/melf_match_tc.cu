@@ -702,6 +702,9 @@ melf_match_tc_kernel(const MelfMatchTcArgs A)
 // =======================================================================================
 namespace {
 
+#ifndef MELF_TC_EXPERIMENT
+#define MELF_TC_EXPERIMENT 0    // measurement only (profiles/r02_timeline_z_*.txt): 1 extra commit, 2 extra fence, 3 extra barrier poll per stage
+#endif
 #ifndef MELF_DRAIN_WIDE
 #define MELF_DRAIN_WIDE 0     // 1: 32 accumulator columns per tcgen05.ld, no prefetch -- measured no faster (drain 19-23 k clk per
 #endif                        // pass against 17-21 k, profiles/r02_timeline_b_*.txt): the drain is not bound by the number of TMEM loads
@@ -1852,6 +1855,7 @@ struct CtrlO {
     unsigned long long prep_done;
     unsigned long long drained[2];     // accumulator of the pass's slot 0 / slot 1 read out (14 warp arrivals)
     unsigned long long stage[F_WORKER_WARPS];   // per worker warp: its staging buffer has been filled (bulk copies)
+    unsigned long long dummy;          // MELF_TC_EXPERIMENT only
     uint32_t tmem_base;
     uint32_t pad;
 };
@@ -1883,6 +1887,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
         mbar_init(smem_u32(&ctrl->drained[0]), F_WORKER_WARPS);
         mbar_init(smem_u32(&ctrl->drained[1]), F_WORKER_WARPS);
         for (int w = 0; w < F_WORKER_WARPS; ++w) mbar_init(smem_u32(&ctrl->stage[w]), 1);
+        mbar_init(smem_u32(&ctrl->dummy), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -1900,6 +1905,10 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
     const int n_ksteps = 8 * A.n_pairs;                               // K-steps of 32 per item
     const int n_stages = (n_ksteps + F_KSTEPS - 1) / F_KSTEPS;        // per pass
     const int n_pre = n_stages < F_NSTAGE ? n_stages : F_NSTAGE;      // stages prefetched ahead of a pass
+    // K-steps of a pair that can hold a template byte: row n of the Toeplitz band ends at k = n + tmpl_w - 1 <= 62 +
+    // tmpl_w, so the K-steps from ceil((63 + tmpl_w) / 32) on are all zero (the eighth one for templates up to 161
+    // wide) and are neither loaded nor multiplied.  (A stage is one pair only with 8 K-steps per stage.)
+    const int kpp_stage = F_KSTEPS == 8 ? A.kpp : F_KSTEPS;
     const u64 pol_keep = policy_evict_last();
     auto pass_items = [&](long long pass, Item (&its)[2]) {
         its[0] = get_item(A, 2 * pass);
@@ -1915,7 +1924,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
             auto load_stage = [&](uint32_t g, int s) {
                 const uint32_t st = g % F_NSTAGE, ph = (g / F_NSTAGE) & 1;
                 mbar_wait(smem_u32(&ctrl->empty[st]), ph ^ 1);
-                const uint32_t bytes = (uint32_t)min(F_KSTEPS, n_ksteps - s * F_KSTEPS) * (2 * BSTRIP_BYTES);
+                const uint32_t bytes = (uint32_t)min(kpp_stage, n_ksteps - s * F_KSTEPS) * (2 * BSTRIP_BYTES);
                 mbar_expect_tx(smem_u32(&ctrl->full[st]), bytes);
                 bulk_load_keep(b_addr + st * F_STAGE_BYTES, A.toeplitz + (size_t)s * F_STAGE_BYTES, bytes,
                                smem_u32(&ctrl->full[st]), pol_keep);
@@ -1973,7 +1982,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
 #pragma unroll
                     for (int j = 0; j < F_KSTEPS; ++j) {
                         const int kk = kk0 + j;
-                        if (kk < n_ksteps) {
+                        if (kk < n_ksteps && j < kpp_stage) {
                             const int pp = kk >> 3, ks = kk & 7;
                             umma_i8(d0, umma_desc(abase + j * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
                                     umma_desc(slab_addr + (2 * pp) * 16 + ks * 2 * STRIP_BYTES, STRIP_BYTES),
@@ -1981,6 +1990,14 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
                         }
                     }
                 }
+#if MELF_TC_EXPERIMENT == 1
+                if (lead) umma_commit(smem_u32(&ctrl->dummy));      // what does a commit cost the MMA stream?
+#elif MELF_TC_EXPERIMENT == 2
+                tc_fence_after();
+#elif MELF_TC_EXPERIMENT == 3
+                mbar_wait(smem_u32(&ctrl->full[st]), ph);
+                __syncwarp();
+#endif
                 if (s == 0 && pc >= 1) {
                     // slot 1's buffer held slot 0 of the previous pass: wait until it has been read out
                     mbar_wait(smem_u32(&ctrl->drained[0]), (pc - 1) & 1);
@@ -1991,7 +2008,7 @@ melf_match_fused_ov_kernel(const MelfMatchTcArgs A, const __grid_constant__ CUte
 #pragma unroll
                         for (int j = 0; j < F_KSTEPS; ++j) {
                             const int kk = kk0 + j;
-                            if (kk < n_ksteps) {
+                            if (kk < n_ksteps && j < kpp_stage) {
                                 const int pp = kk >> 3, ks = kk & 7;
                                 umma_i8(d1, umma_desc(abase + j * 2 * BSTRIP_BYTES, BSTRIP_BYTES),
                                         umma_desc(slab_addr + SLAB_BYTES + (2 * pp) * 16 + ks * 2 * STRIP_BYTES, STRIP_BYTES),
@@ -2317,6 +2334,11 @@ long long melf_match_tc_plan(MelfMatchTcArgs &a, int n_frames)
     a.n_ty = (a.geom.res_h + cap - 1) / cap;
     a.chunk_h = (a.geom.res_h + a.n_ty - 1) / a.n_ty;
     a.n_pairs = (a.tmpl_h + 1) / 2;
+    a.kpp = (a.tmpl_w + 63 + 31) / 32;
+    {
+        static const bool all8 = std::getenv("MELF_TC_KPP8") && std::atoi(std::getenv("MELF_TC_KPP8"));   // A/B switch
+        if (all8 || a.kpp > 8) a.kpp = 8;
+    }
     a.n_items = (long long)n_frames * a.n_tx * a.n_ty;
     for (int j = 0; j < 64; ++j) {
         uint32_t w = 0;

@@ -311,6 +311,30 @@ def test_match_template_gray_sizes_and_ties(h, w):
     assert tuple(d_xy[2].cpu().numpy()) == (tx, ty)
 
 
+@pytest.mark.parametrize('tw', [33, 97, 129, 161, 162, 193])
+def test_match_template_narrow_templates_on_the_tensor_core_kernel(tw):
+    """Templates narrower than 162 px leave whole K-steps of the Toeplitz operand zero; the locate kernel
+    neither loads nor multiplies those (``MelfMatchTcArgs::kpp``: 3..7 of 8 K-steps per row pair here, all 8
+    from 162 px on).  Result map large enough that the size dispatch takes the Toeplitz kernel."""
+    from meterelf_b200 import _utils
+    torch = _torch()
+    rng = np.random.default_rng(tw)
+    (ih, iw, th) = (260, 336 if tw % 2 == 0 else 330, 57)       # 336: rows are whole 16-byte chunks (tensor-copy staging)
+    img = rng.integers(0, 256, (ih, iw), dtype=np.uint8)
+    tmpl = rng.integers(0, 256, (th, tw), dtype=np.uint8)
+    (ty, tx) = (int(rng.integers(0, ih - th + 1)), int(rng.integers(0, iw - tw + 1)))
+    planted = img.copy()
+    planted[ty:ty + th, tx:tx + tw] = tmpl
+    for (image, where) in ((img, None), (planted, (tx, ty))):
+        got = _utils.match_template(image, tmpl)
+        eng = _utils._template_engine(tmpl, torch.cuda.current_device())
+        assert eng.last_locate() == 'melf_match_fused_ov_kernel'
+        (x, y, val, _map) = oracle.match_template(image, tmpl, want_map=False)
+        assert got.rect == ((x, y), (x + tw, y + th)) and np.float32(got.max_val) == val, tw
+        if where:
+            assert (x, y) == where
+
+
 def test_operators_with_the_reference_signatures(tmp_path):
     """``match_template(img, template)`` with ANY template (``_utils.py:91-97``),
     ``get_mask_by_color(hls_image, color, color_range)`` on an HLS image (``_utils.py:113-119``),
