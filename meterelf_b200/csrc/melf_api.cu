@@ -634,6 +634,18 @@ int melf_profile_read(melf_ctx *ctx, float *ms, int32_t *launches)
     MELF_CUDA(ctx, dev_scope.status);
     MELF_CUDA(ctx, cudaDeviceSynchronize());
     for (int k = 0; k < MELF_PROF_KINDS; k++) { ms[k] = 0.f; launches[k] = 0; }
+    // MELF_PROF_TRACE=<file>: every span as "kind start_ms end_ms" relative to the first one (debug timeline)
+    if (const char *trace = std::getenv("MELF_PROF_TRACE")) {
+        if (FILE *fp = ctx->spans.empty() ? nullptr : std::fopen(trace, "w")) {
+            for (const melf_ctx::Span &sp : ctx->spans) {
+                float t0 = 0.f, t1 = 0.f;
+                cudaEventElapsedTime(&t0, ctx->spans.front().e0, sp.e0);
+                cudaEventElapsedTime(&t1, ctx->spans.front().e0, sp.e1);
+                std::fprintf(fp, "%d %.4f %.4f\n", sp.kind, t0, t1);
+            }
+            std::fclose(fp);
+        }
+    }
     for (const melf_ctx::Span &sp : ctx->spans) {
         float t = 0.f;
         if (cudaEventElapsedTime(&t, sp.e0, sp.e1) == cudaSuccess && sp.kind >= 0 && sp.kind < MELF_PROF_KINDS) {
