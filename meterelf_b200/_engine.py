@@ -210,6 +210,7 @@ class Engine:
         self.names = list(names)
         self.n_dials = cparams.n_dials
         self.device = device
+        self._call_lock = threading.Lock()
         self._ctx = C.c_void_p()
         rc = self.lib.melf_create(C.byref(self._ctx), device, C.byref(cparams))
         if rc:
@@ -264,9 +265,10 @@ class Engine:
         (n, h, w) = frames.shape[:3]
         out = np.zeros((n,), RESULT_DTYPE)
         if n:
-            self._check(self.lib.melf_read_batch(
-                self._ctx, frames.ctypes.data, n, h, w, frames.strides[1],
-                frames.strides[0], out.ctypes.data))
+            with self._call_lock:           # one batch at a time per context (its staging and slots)
+                self._check(self.lib.melf_read_batch(
+                    self._ctx, frames.ctypes.data, n, h, w, frames.strides[1],
+                    frames.strides[0], out.ctypes.data))
         return out
 
     # -- JPEG streams in (host), results out (host): SURVEY 8f-1 -------------------------
@@ -280,8 +282,9 @@ class Engine:
         n = len(offsets) - 1
         out = np.zeros((n,), RESULT_DTYPE)
         if n:
-            self._check(self.lib.melf_read_jpeg_batch(
-                self._ctx, blob.ctypes.data, offsets.ctypes.data, n, out.ctypes.data))
+            with self._call_lock:
+                self._check(self.lib.melf_read_jpeg_batch(
+                    self._ctx, blob.ctypes.data, offsets.ctypes.data, n, out.ctypes.data))
         return out
 
     def decode_jpeg_device(self, blob: np.ndarray, offsets: np.ndarray, h: int, w: int, d_bgr: int,
@@ -344,6 +347,50 @@ def pack_streams(streams: Sequence[bytes]) -> Tuple[np.ndarray, np.ndarray]:
     return (blob, offsets)
 
 
+class _Blob(np.ndarray):
+    """ndarray view of a pooled page-locked buffer (``_owner``: the torch tensor that holds the memory)."""
+    _owner: Any = None
+
+
+_blob_lock = threading.Lock()
+_blob_free: List[Any] = []                  # page-locked torch tensors waiting for the next batch
+
+
+def _blob_buffer(nbytes: int) -> np.ndarray:
+    """``nbytes`` of host memory for a batch of file bytes.  With a GPU it is page-locked and comes from a
+    small pool (``release_blob`` hands it back): the ingest path then copies it to the device as it lies --
+    pageable memory is first copied into a pinned staging area, ~40 ms per 300 MB batch -- and fresh pages are
+    not faulted in for every batch."""
+    try:
+        import torch
+        pinned = torch.cuda.is_available()
+    except ImportError:
+        pinned = False
+    if not pinned:
+        return np.empty((nbytes,), np.uint8)
+    buf = None
+    with _blob_lock:
+        fits = [k for (k, t) in enumerate(_blob_free) if t.numel() >= nbytes]
+        if fits:
+            buf = _blob_free.pop(min(fits, key=lambda k: _blob_free[k].numel()))
+    if buf is None:
+        buf = torch.empty((max(nbytes + nbytes // 4, 1 << 20),), dtype=torch.uint8, pin_memory=True)
+    arr = buf.numpy()[:nbytes].view(_Blob)
+    arr._owner = buf
+    return arr
+
+
+def release_blob(blob: np.ndarray) -> None:
+    """Hands the buffer of a ``read_files`` blob back to the pool; the blob must not be used afterwards."""
+    owner = getattr(blob, '_owner', None)
+    if owner is None:
+        return
+    blob._owner = None
+    with _blob_lock:
+        if len(_blob_free) < 4:
+            _blob_free.append(owner)
+
+
 def read_files(paths: Sequence[str]) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
     """The bytes of ``paths`` in one blob: (blob u8, offsets u64[n+1], ok bool[n]); a file that cannot be
     opened or read in full has ok False and an empty slice (``cv2.imread`` would return None for it)."""
@@ -354,7 +401,7 @@ def read_files(paths: Sequence[str]) -> Tuple[np.ndarray, np.ndarray, np.ndarray
     lib.melf_file_sizes(c_paths, n, sizes.ctypes.data)
     offsets = np.zeros(n + 1, np.uint64)
     np.cumsum(np.maximum(sizes, 0), out=offsets[1:])
-    blob = np.empty((int(offsets[-1]) + 16,), np.uint8)
+    blob = _blob_buffer(int(offsets[-1]) + 16)
     ok = np.zeros((n,), np.int32)
     lib.melf_read_files(c_paths, n, blob.ctypes.data, offsets.ctypes.data, ok.ctypes.data)
     return (blob, offsets, (ok != 0) & (sizes >= 0))

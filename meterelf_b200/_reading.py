@@ -5,6 +5,7 @@ is done by ``read_image_files`` which maps the C ABI's per-frame status codes ba
 the reference's exception classes, messages and ``extra_info`` dicts.
 """
 import re
+import threading
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy
@@ -19,6 +20,7 @@ from .exceptions import (
 
 _FULL_FRAME = (0, 0, 2 ** 30, 2 ** 30)
 _engines: Dict[Tuple[int, bool, int], Tuple[_Params, _engine.Engine]] = {}
+_engines_lock = threading.Lock()
 
 
 def get_engine(params: _Params, cropped_input: bool = False, device: int = 0) -> _engine.Engine:
@@ -26,16 +28,17 @@ def get_engine(params: _Params, cropped_input: bool = False, device: int = 0) ->
 
     ``cropped_input``: frames are already cut to ``meter_rect`` (injected ``bgr_image``)."""
     key = (id(params), cropped_input, device)
-    entry = _engines.get(key)
-    if entry is None or entry[0] is not params:
-        dial_data = get_dial_data(params)
-        rect = _FULL_FRAME if cropped_input else (
-            params.meter_rect.top_left + params.meter_rect.bottom_right)
-        (cparams, keep) = _engine.build_cparams(
-            get_dials_template(params), rect, params.hue_shift,
-            params.dials_match_threshold, _engine.dials_from_params(params, dial_data))
-        entry = (params, _engine.Engine(cparams, keep, list(dial_data.keys()), device))
-        _engines[key] = entry
+    with _engines_lock:
+        entry = _engines.get(key)
+        if entry is None or entry[0] is not params:
+            dial_data = get_dial_data(params)
+            rect = _FULL_FRAME if cropped_input else (
+                params.meter_rect.top_left + params.meter_rect.bottom_right)
+            (cparams, keep) = _engine.build_cparams(
+                get_dials_template(params), rect, params.hue_shift,
+                params.dials_match_threshold, _engine.dials_from_params(params, dial_data))
+            entry = (params, _engine.Engine(cparams, keep, list(dial_data.keys()), device))
+            _engines[key] = entry
     return entry[1]
 
 
@@ -98,66 +101,84 @@ def read_image_files(params: _Params, imgfs: Sequence[ImageFile], device: int = 
     (``cv2.imread``), grouped by frame shape and read in one GPU batch per group."""
     out: List[Any] = [None] * len(imgfs)
     debug_dir = _overlay.overlay_dir()      # debug pictures need the decoded pixels on the host
-    groups: Dict[Tuple[bool, Tuple[int, ...]], List[Tuple[int, numpy.ndarray]]] = {}
     host_decode: List[int] = []
     from_file = [i for (i, imgf) in enumerate(imgfs) if imgf.bgr_image is None]
     if from_file and gpu_ingest_enabled() and debug_dir is None:
         (blob, offsets, readable) = _engine.read_files([imgfs[i].filename for i in from_file])
-        info = _engine.jpeg_probe_batch(blob, offsets)
-        # the GPU decoder takes a stream when the probe accepts it, cv2.imread would not rotate it (EXIF)
-        # and it has its end-of-image marker (a file cut short: let cv2.imread decide what the reference sees)
-        good = readable & (info[:, 7] == 0) & (info[:, 5] == 1) & (info[:, 6] == 1)
-        host_decode.extend(from_file[k] for k in numpy.flatnonzero(~good).tolist())
-        which = numpy.flatnonzero(good)
-        if len(which):
-            (geoms, inverse) = numpy.unique(info[which, :5], axis=0, return_inverse=True)
-            inverse = inverse.reshape(-1)
-            engine = get_engine(params, cropped_input=False, device=device)
-            for g in range(len(geoms)):
-                members = which[inverse == g]
-                if len(members) == len(from_file):
-                    (sub_blob, sub_offsets) = (blob, offsets)
-                else:
-                    parts = [blob[int(offsets[k]):int(offsets[k + 1])] for k in members.tolist()]
-                    sub_offsets = numpy.zeros(len(parts) + 1, numpy.uint64)
-                    numpy.cumsum([len(p) for p in parts], out=sub_offsets[1:])
-                    sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
-                indices = [from_file[k] for k in members.tolist()]
-                records = None
-                for _attempt in range(9):
-                    try:
-                        records = engine.read_jpeg_blob(sub_blob, sub_offsets)
-                        break
-                    except _engine.EngineError as error:
-                        if error.code == _engine.ERR_TOO_SMALL:
-                            for index in indices:
-                                out[index] = Deferred(ValueError(
-                                    'image smaller than the dials template: ' + imgfs[index].filename))
-                            indices = []
-                            break
-                        if error.code not in (_engine.ERR_INVALID, _engine.ERR_UNSUPPORTED):
-                            raise
-                        # a stream the header probe accepted but the decoder rejects: cv2.imread decides what
-                        # the reference would have seen for THAT file; the others stay on the GPU
-                        bad = re.search(r'stream (\d+):', str(error))
-                        if bad is None or not 0 <= int(bad.group(1)) < len(indices) or len(indices) == 1:
-                            break
-                        drop = int(bad.group(1))
-                        host_decode.append(indices.pop(drop))
-                        lengths = numpy.diff(sub_offsets).astype(numpy.int64)
-                        keep = [k for k in range(len(lengths)) if k != drop]
-                        parts = [sub_blob[int(sub_offsets[k]):int(sub_offsets[k + 1])] for k in keep]
-                        sub_offsets = numpy.zeros(len(parts) + 1, numpy.uint64)
-                        numpy.cumsum(lengths[keep], out=sub_offsets[1:])
-                        sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
-                if records is None:
-                    host_decode.extend(indices)
-                    continue
-                converted = records_to_python(records, engine.names, [imgfs[i].filename for i in indices])
-                for (index, item) in zip(indices, converted):
-                    out[index] = item
+        try:
+            _read_jpeg_groups(params, imgfs, from_file, blob, offsets, readable, host_decode, out, device)
+        finally:
+            _engine.release_blob(blob)
     else:
         host_decode.extend(from_file)
+    _read_on_host(params, imgfs, host_decode, out, device, debug_dir)
+    return out
+
+
+def _read_jpeg_groups(params: _Params, imgfs: Sequence[ImageFile], from_file: List[int], blob: numpy.ndarray,
+                      offsets: numpy.ndarray, readable: numpy.ndarray, host_decode: List[int], out: List[Any],
+                      device: int) -> None:
+    """The files whose bytes are in ``blob``: baseline JPEG streams go to the GPU grouped by geometry, the
+    indices of everything else are appended to ``host_decode``."""
+    info = _engine.jpeg_probe_batch(blob, offsets)
+    # the GPU decoder takes a stream when the probe accepts it, cv2.imread would not rotate it (EXIF)
+    # and it has its end-of-image marker (a file cut short: let cv2.imread decide what the reference sees)
+    good = readable & (info[:, 7] == 0) & (info[:, 5] == 1) & (info[:, 6] == 1)
+    host_decode.extend(from_file[k] for k in numpy.flatnonzero(~good).tolist())
+    which = numpy.flatnonzero(good)
+    if len(which):
+        (geoms, inverse) = numpy.unique(info[which, :5], axis=0, return_inverse=True)
+        inverse = inverse.reshape(-1)
+        engine = get_engine(params, cropped_input=False, device=device)
+        for g in range(len(geoms)):
+            members = which[inverse == g]
+            if len(members) == len(from_file):
+                (sub_blob, sub_offsets) = (blob, offsets)
+            else:
+                parts = [blob[int(offsets[k]):int(offsets[k + 1])] for k in members.tolist()]
+                sub_offsets = numpy.zeros(len(parts) + 1, numpy.uint64)
+                numpy.cumsum([len(p) for p in parts], out=sub_offsets[1:])
+                sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
+            indices = [from_file[k] for k in members.tolist()]
+            records = None
+            for _attempt in range(9):
+                try:
+                    records = engine.read_jpeg_blob(sub_blob, sub_offsets)
+                    break
+                except _engine.EngineError as error:
+                    if error.code == _engine.ERR_TOO_SMALL:
+                        for index in indices:
+                            out[index] = Deferred(ValueError(
+                                'image smaller than the dials template: ' + imgfs[index].filename))
+                        indices = []
+                        break
+                    if error.code not in (_engine.ERR_INVALID, _engine.ERR_UNSUPPORTED):
+                        raise
+                    # a stream the header probe accepted but the decoder rejects: cv2.imread decides what
+                    # the reference would have seen for THAT file; the others stay on the GPU
+                    bad = re.search(r'stream (\d+):', str(error))
+                    if bad is None or not 0 <= int(bad.group(1)) < len(indices) or len(indices) == 1:
+                        break
+                    drop = int(bad.group(1))
+                    host_decode.append(indices.pop(drop))
+                    lengths = numpy.diff(sub_offsets).astype(numpy.int64)
+                    keep = [k for k in range(len(lengths)) if k != drop]
+                    parts = [sub_blob[int(sub_offsets[k]):int(sub_offsets[k + 1])] for k in keep]
+                    sub_offsets = numpy.zeros(len(parts) + 1, numpy.uint64)
+                    numpy.cumsum(lengths[keep], out=sub_offsets[1:])
+                    sub_blob = numpy.concatenate(parts + [numpy.zeros(16, numpy.uint8)])
+            if records is None:
+                host_decode.extend(indices)
+                continue
+            converted = records_to_python(records, engine.names, [imgfs[i].filename for i in indices])
+            for (index, item) in zip(indices, converted):
+                out[index] = item
+
+
+def _read_on_host(params: _Params, imgfs: Sequence[ImageFile], host_decode: List[int], out: List[Any], device: int,
+                  debug_dir: Optional[str]) -> None:
+    """Files decoded with ``cv2.imread`` as in the reference and injected images, one GPU batch per frame shape."""
+    groups: Dict[Tuple[bool, Tuple[int, ...]], List[Tuple[int, numpy.ndarray]]] = {}
     host_decode.extend(i for (i, imgf) in enumerate(imgfs) if imgf.bgr_image is not None)
     for index in sorted(host_decode):
         imgf = imgfs[index]
@@ -189,7 +210,6 @@ def read_image_files(params: _Params, imgfs: Sequence[ImageFile], device: int = 
             _overlay.write_overlays(
                 params, get_engine(params, cropped_input=True, device=device), crops,
                 [imgfs[index].filename for index in indices], debug_dir)
-    return out
 
 
 def get_meter_value(imgf: ImageFile) -> Dict[str, float]:
