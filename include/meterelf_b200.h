@@ -175,6 +175,23 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
                         size_t row_stride, size_t frame_stride, int use_rect,
                         int32_t *d_max_xy, float *d_max_val, float *d_result, void *stream);
 
+/* melf_match_template for callers that cannot allocate: no counterpart in the reference.
+ * Some callers cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it); this entry point calls no cudaMalloc / cudaFree and no allocating
+ * library routine.  Same arguments, result and error codes as melf_match_template without d_result (arg-max
+ * only).  The locate kernel's scratch (per-CTA lightness slabs + window sums, per-frame arg-max keys) lives in
+ * a static device array of MELF_NOALLOC_SCRATCH_BYTES (about 40 MiB) that every GPU which loads the library
+ * holds until exit.  Limits, each rejected with MELF_ERR_UNSUPPORTED and a message in melf_last_error:
+ * n <= MELF_NOALLOC_MAX_FRAMES per call; a template the tensor-core kernel takes (<= 193 x 128 px).
+ * Every call on a GPU SHARES that array: it is cleared on `stream` at the start of every call, and calls that
+ * overlap on the GPU (different streams, or a captured graph launched twice concurrently) race -- serialise
+ * them.  The array's device address is looked up once per device by melf_create (outside any capture). */
+#define MELF_NOALLOC_MAX_FRAMES 8192
+#define MELF_NOALLOC_SCRATCH_BYTES (148u * 282624u + MELF_NOALLOC_MAX_FRAMES * 8u)
+int melf_match_template_noalloc(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
+                                size_t row_stride, size_t frame_stride, int use_rect,
+                                int32_t *d_max_xy, float *d_max_val, void *stream);
+
 /* ---- ingest: cv2.imread of baseline JPEG streams on the GPU ------------------- */
 /* ImageFile.get_bgr_image's cv2.imread (_image.py:49) for n JPEG streams held in HOST memory:
  * stream i is jpeg[offsets[i] .. offsets[i+1]).  The pixels are bit-identical to OpenCV's bundled

@@ -79,7 +79,10 @@ _SYMBOLS = (
     'melf_dial_window', 'melf_read_batch_async', 'melf_read_batch', 'melf_convert_hls',
     'melf_match_template', 'melf_launch_count', 'melf_profile_enable', 'melf_profile_read',
     'melf_average_translated', 'melf_decode_jpeg', 'melf_jpeg_info', 'melf_read_jpeg_batch',
-    'melf_in_range', 'melf_file_sizes', 'melf_read_files', 'melf_jpeg_probe_batch', 'melf_last_locate')
+    'melf_in_range', 'melf_file_sizes', 'melf_read_files', 'melf_jpeg_probe_batch', 'melf_last_locate',
+    'melf_match_template_noalloc')
+
+NOALLOC_MAX_FRAMES = 8192           # MELF_NOALLOC_MAX_FRAMES
 
 PROFILE_KINDS = ('match_prep', 'match_tc', 'dials', 'match_dp4a', 'jpeg_upload', 'jpeg_destuff',
                  'jpeg_huffman', 'jpeg_idct', 'jpeg_color')
@@ -126,6 +129,9 @@ def load_library() -> C.CDLL:
         lib.melf_match_template.argtypes = [
             C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
             C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.melf_match_template_noalloc.argtypes = [
+            C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
+            C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.melf_average_translated.argtypes = [
             C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p,
             C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -309,6 +315,15 @@ class Engine:
         self._check(self.lib.melf_match_template(
             self._ctx, d_img, channels, n, h, w, row_stride, frame_stride,
             1 if use_rect else 0, d_max_xy, d_max_val, d_result or None, stream))
+
+    def match_template_noalloc_device(self, d_img: int, channels: int, n: int, h: int, w: int,
+                                      row_stride: int, frame_stride: int, use_rect: bool,
+                                      d_max_xy: int, d_max_val: int, stream: int = 0) -> None:
+        """``melf_match_template_noalloc``: the same arg-max on the library's static scratch (no cudaMalloc;
+        at most ``NOALLOC_MAX_FRAMES`` frames per call; calls that overlap on the GPU race)."""
+        self._check(self.lib.melf_match_template_noalloc(
+            self._ctx, d_img, channels, n, h, w, row_stride, frame_stride,
+            1 if use_rect else 0, d_max_xy, d_max_val, stream))
 
 
 def convert_hls_device(device: int, d_bgr: int, n: int, h: int, w: int, row_stride: int,

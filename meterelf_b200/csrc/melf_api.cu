@@ -483,6 +483,40 @@ void free_ctx(melf_ctx *ctx)
 
 }  // namespace
 
+// ---- melf_match_template_noalloc: scratch that is never allocated ----------------------------------------
+// The locate kernel's scratch for callers that cannot call cudaMalloc (CUDA graph capture, serving loops):
+// [per-CTA slabs + window sums of melf_match_fused_ov_kernel for kNoAllocCtas CTAs][kNoAllocMaxFrames arg-max keys].
+// One copy per GPU that loads the library, held until exit.  In HOST code the array's name is a host-side
+// stand-in, not a device address: noalloc_setup() asks the runtime for the address, once per device.
+constexpr int kNoAllocCtas = 148;                                   // B200: one CTA per SM
+constexpr size_t kNoAllocCtaBytes = 282624;                         // F_SCRATCH_PER_CTA_OV (checked at run time)
+constexpr size_t kNoAllocKeysOff = (size_t)kNoAllocCtas * kNoAllocCtaBytes;              // 41,828,352
+constexpr size_t kNoAllocBytes = kNoAllocKeysOff + (size_t)MELF_NOALLOC_MAX_FRAMES * sizeof(u64);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+namespace {
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+unsigned char *g_noalloc_ptr[kNoAllocMaxDevices] = {};               // device address of g_noalloc_scratch per device
+cudaError_t g_noalloc_err[kNoAllocMaxDevices] = {};
+
+// Once per device, with that device current (the caller holds a DeviceScope): the device address of the array.
+cudaError_t noalloc_setup(int device, unsigned char **ptr)
+{
+    if (device < 0 || device >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device] && g_noalloc_err[device] == cudaSuccess) {
+        void *p = nullptr;
+        g_noalloc_err[device] = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (g_noalloc_err[device] == cudaSuccess) g_noalloc_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    if (ptr) *ptr = g_noalloc_ptr[device];
+    return g_noalloc_err[device];
+}
+
+}  // namespace
+
 extern "C" {
 
 int melf_abi_version(void) { return MELF_ABI_VERSION; }
@@ -586,6 +620,7 @@ int melf_create(melf_ctx **out, int device, const melf_params *P)
         MELF_CREATE_CUDA(cudaMalloc(&ctx->d_ones_words, ones.size() * 4));
         MELF_CREATE_CUDA(cudaMemcpy(ctx->d_ones_words, ones.data(), ones.size() * 4, cudaMemcpyHostToDevice));
     }
+    noalloc_setup(device, nullptr);       // address of the static scratch of melf_match_template_noalloc, once per device
     if (melf_match_tc_supported(P->tmpl_w, P->tmpl_h)) {
         std::vector<uint8_t> toep(melf_match_tc_toeplitz_bytes(P->tmpl_h));
         melf_match_tc_build_toeplitz(P->tmpl, P->tmpl_w, P->tmpl_h, toep.data());
@@ -976,6 +1011,62 @@ int melf_match_template(melf_ctx *ctx, const uint8_t *d_img, int channels, int n
     if (rc) return rc;
     MELF_CUDA(ctx, melf_launch_match_unpack(ctx->d_keys, n, geom.res_w, d_max_xy, d_max_val, st));
     g_launches++;
+    return MELF_OK;
+}
+
+// melf_match_template without any allocation (include/meterelf_b200.h): the tensor-core locate kernel on the
+// static scratch array.  Nothing here may call cudaMalloc / cudaFree / cudaEventCreate or a library that does.
+int melf_match_template_noalloc(melf_ctx *ctx, const uint8_t *d_img, int channels, int n, int h, int w,
+                                size_t row_stride, size_t frame_stride, int use_rect,
+                                int32_t *d_max_xy, float *d_max_val, void *stream)
+{
+    if (!ctx) return MELF_ERR_INVALID;
+    if ((channels != 1 && channels != 3) || n < 0 || h < 1 || w < 1 || (n > 0 && !d_img) ||
+        !d_max_xy || !d_max_val || row_stride < (size_t)w * channels)
+        return fail(ctx, MELF_ERR_INVALID, "bad melf_match_template_noalloc arguments");
+    if (n > MELF_NOALLOC_MAX_FRAMES)
+        return fail(ctx, MELF_ERR_UNSUPPORTED, "melf_match_template_noalloc: n = " + std::to_string(n) +
+                    " frames exceeds MELF_NOALLOC_MAX_FRAMES = " + std::to_string(MELF_NOALLOC_MAX_FRAMES) +
+                    " (static scratch); split the batch or use melf_match_template");
+    if (!ctx->d_toeplitz || !melf_match_tc_supported(ctx->params.tmpl_w, ctx->params.tmpl_h))
+        return fail(ctx, MELF_ERR_UNSUPPORTED, "melf_match_template_noalloc: the template does not fit the "
+                    "tensor-core locate kernel (at most 193 x 128 px); use melf_match_template");
+    if (n == 0) return MELF_OK;
+    DeviceScope dev_scope(ctx->device);
+    MELF_CUDA(ctx, dev_scope.status);
+    MelfGeom geom;
+    int rc = make_geom(ctx, h, w, use_rect != 0, &geom);
+    if (rc) return rc;
+    unsigned char *scratch = nullptr;
+    MELF_CUDA(ctx, noalloc_setup(ctx->device, &scratch));          // normally done by melf_create already
+    const int ctas = ctx->num_sms < kNoAllocCtas ? ctx->num_sms : kNoAllocCtas;
+    if (!scratch || melf_match_fused_ov_scratch_bytes(ctas) > kNoAllocKeysOff)
+        return fail(ctx, MELF_ERR_UNSUPPORTED, "melf_match_template_noalloc: static scratch unavailable or too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    u64 *keys = reinterpret_cast<u64 *>(scratch + kNoAllocKeysOff);
+    // every call shares the array and it keeps the last call's contents: the keys must start at zero (atomicMax
+    // slots), and the slab rows a geometry never writes must be zero whatever an earlier geometry left there
+    MELF_CUDA(ctx, cudaMemsetAsync(scratch, 0, melf_match_fused_ov_scratch_bytes(ctas), st));
+    MELF_CUDA(ctx, cudaMemsetAsync(keys, 0, (size_t)n * sizeof(u64), st));
+    MelfMatchTcArgs t{};
+    t.img = d_img;
+    const uint8_t *end = d_img + (size_t)(n - 1) * frame_stride + (size_t)(h - 1) * row_stride + (size_t)w * channels;
+    t.img_limit = reinterpret_cast<const uint8_t *>((reinterpret_cast<uintptr_t>(end) + 15) & ~(uintptr_t)15);
+    t.row_stride = row_stride; t.frame_stride = frame_stride;
+    t.channels = channels;
+    t.img_w = w; t.img_h = h; t.img_n = n;
+    t.geom = geom;
+    t.toeplitz = ctx->d_toeplitz;
+    t.tmpl_w = ctx->params.tmpl_w; t.tmpl_h = ctx->params.tmpl_h;
+    t.sum_t = ctx->sum_t; t.n_t = ctx->n_t;
+    t.match_key = keys;
+    t.result = nullptr;
+    melf_match_tc_plan(t, n);
+    t.slabs = scratch;
+    t.max_items = t.n_items;
+    MELF_CUDA(ctx, melf_launch_match_fused_ov(t, ctas, st));
+    MELF_CUDA(ctx, melf_launch_match_unpack(keys, n, geom.res_w, d_max_xy, d_max_val, st));
+    g_launches += 2;
     return MELF_OK;
 }
 
