@@ -401,23 +401,54 @@ __device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
     return v;
 }
 
-template <int G, bool SHARED>
+// MODE (round 2, the instruction count per symbol is what bounds this stage):
+//   HUFF_CAREFUL  everything: restart intervals and jdhuff.c's behaviour when a stream runs out of data
+//   HUFF_FAST     for chunks without restart intervals: none of that in the loop (the end-of-MCU path shrinks from
+//                 ~60 to ~10 instructions, and some lane of the warp takes it in a third of the iterations).  A
+//                 stream that read past its end is only FLAGGED (flags[stream] = 1, else 0) ...
+//   HUFF_REDO     ... and decoded again by this careful variant, launched right behind on the same stream: warps
+//                 without a flagged stream return at once, the others clear the coefficients of the flagged
+//                 streams (the fast pass wrote rubbish behind the end of the data) and decode them as HUFF_CAREFUL.
+enum { HUFF_CAREFUL = 0, HUFF_FAST = 1, HUFF_REDO = 2 };
+
+template <int G, bool SHARED, int MODE>
 __global__ void __launch_bounds__(32)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
                          const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ order,
-                         const uint32_t *__restrict__ clean_len,
+                         const uint32_t *__restrict__ clean_len, uint32_t *__restrict__ flags,
                          int n, const JpegGeom g, const McuRect R, int16_t *__restrict__ coef)
 {
     extern __shared__ __align__(16) unsigned char huff_smem[];
     HuffSmem *S = reinterpret_cast<HuffSmem *>(huff_smem);
     const int lane = threadIdx.x;
     const int img0 = blockIdx.x * G;
-    for (int gi = 0; gi < (SHARED ? 1 : G) && img0 + gi < n; gi++) {
-        const JpegDesc d = desc[order[img0 + gi]];
-        build_tables(S[gi], blob + d.base, d, lane);
+    if (MODE == HUFF_REDO) {
+        const bool mine = lane < G && img0 + lane < n && flags[order[img0 + lane]] != 0;
+        uint32_t todo = __ballot_sync(0xffffffffu, mine);
+        if (!todo) return;
+        // the whole warp clears the coefficients of every flagged stream of this warp
+        const size_t per_stream = (size_t)R.stride_blocks * 64;               // int16 elements, a multiple of 8 bytes
+        while (todo) {
+            const int l = __ffs(todo) - 1;
+            todo &= todo - 1;
+            uint2 *dst = reinterpret_cast<uint2 *>(coef + (size_t)order[img0 + l] * per_stream);
+            for (size_t i = lane; i < per_stream / 4; i += 32) dst[i] = make_uint2(0u, 0u);
+        }
+        __syncwarp();
+        for (int gi = 0; gi < (SHARED ? 1 : G) && img0 + gi < n; gi++) {
+            const JpegDesc d = desc[order[img0 + gi]];
+            build_tables(S[gi], blob + d.base, d, lane);
+        }
+        __syncwarp();
+        if (!mine) return;
+    } else {
+        for (int gi = 0; gi < (SHARED ? 1 : G) && img0 + gi < n; gi++) {
+            const JpegDesc d = desc[order[img0 + gi]];
+            build_tables(S[gi], blob + d.base, d, lane);
+        }
+        __syncwarp();
+        if (lane >= G || img0 + lane >= n) return;
     }
-    __syncwarp();
-    if (lane >= G || img0 + lane >= n) return;
     const int img = (int)order[img0 + lane];            // lanes take the streams longest first (host-sorted)
     const HuffSmem &T = S[SHARED ? 0 : lane];
     // the look-ahead tables are read through a shared-window address computed once (a generic pointer
@@ -458,6 +489,13 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             w0 = need ? w1 : w0;
             w1 = need ? __byte_perm(nextw, 0, 0x0123) : w1;
             wp += need ? 1 : 0;
+            if (MODE == HUFF_FAST) {
+                // predicated load instead of a branch (a lone warp cannot issue past an unresolved branch, and this
+                // loop is bound by its latency per symbol): the destuffed data is followed by >= 16 zero bytes
+                const uint32_t *ptr = src + min(wp, wmax + 2);
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p ld.global.nc.u32 %0, [%1];\n\t}"
+                             : "+r"(nextw) : "l"(ptr), "r"((int)need));
+            } else
             if (need) nextw = wp < wmax ? src[wp] : 0;
         }
         const bool is_dc = k == 0;
@@ -482,6 +520,11 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
         // DC: difference to the predictor of the component; AC: run r, value v; (0,0) end of block; (15,0) 16 zeros
         pred += is_dc ? v : 0;
         const int pos = is_dc ? 0 : k + r;
+        if (MODE == HUFF_FAST) {
+            // no branch around the store: what is not to be kept goes to the stream's spare block
+            int16_t *dst = (is_dc || (s != 0 && pos < 64)) ? blk + pos : trash;
+            *dst = (int16_t)(is_dc ? pred : v);
+        } else
         if (is_dc || (s != 0 && pos < 64)) blk[pos] = (int16_t)(is_dc ? pred : v);
         k = (is_dc || s != 0) ? pos + 1 : (r == 15 ? k + 16 : 64);
         const bool block_end = k >= 64;
@@ -499,6 +542,12 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                 pred = pred1; pred1 = pred2; pred2 = t0;
                 comp = ncomp;
             }
+            if (MODE == HUFF_FAST) {
+                if (mcu_end && --run == 0) {
+                    keep = !keep;
+                    run = keep ? run_keep : run_skip;
+                }
+            } else
             if (mcu_end) {                                            // one MCU in every nslots blocks
                 if (--run == 0) {
                     keep = !keep;
@@ -538,6 +587,9 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
             blk = keep ? kept : trash;
         }
     }
+    // a symbol needed bits past the end of the data (a stream cut short): the careful variant decides what libjpeg
+    // would have left in the coefficients
+    if (MODE == HUFF_FAST) flags[img] = (uint32_t)(wp - 2) * 32u + (uint32_t)bp > avail_bits ? 1u : 0u;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -998,7 +1050,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     const size_t coef_elems = (size_t)count * mr.stride_blocks * 64;
     JPEG_CUDA(grow(&S.d_blob, &S.blob_cap, desc_bytes + blob_bytes + 16));
     JPEG_CUDA(grow(&S.d_clean, &S.clean_cap, clean_bytes + 64));
-    JPEG_CUDA(grow(&S.d_clean_len, &S.len_cap, (size_t)count * 4));
+    JPEG_CUDA(grow(&S.d_clean_len, &S.len_cap, (size_t)count * 8));     // lengths, then the redo flags of the Huffman stage
     JPEG_CUDA(grow(&S.d_coef, &S.coef_cap, coef_elems * 2));
     JPEG_CUDA(grow(&S.d_planes, &S.planes_cap, (size_t)count * g.plane_bytes));
     (void)S.d_desc; (void)S.desc_cap;
@@ -1027,16 +1079,30 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     if (forced == 1 || forced == 2 || forced == 4 || forced == 8 || forced == 16 || forced == 32) G = forced;
     const int ctas = (count + G - 1) / G;
     const size_t hsmem = sizeof(HuffSmem) * (shared_tables ? 1 : G);
+    // chunks without restart intervals take the lean loop + the redo pass for streams that ran out of data
+    // (MELF_JPEG_FAST=0: the careful loop for everything, A/B runs)
+    bool any_restart = false;
+    for (int i = 0; i < count; i++) any_restart = any_restart || descs[i].restart != 0;
+    static const bool fast_allowed = !(std::getenv("MELF_JPEG_FAST") && !std::atoi(std::getenv("MELF_JPEG_FAST")));
+    const bool fast = fast_allowed && !any_restart;
+    uint32_t *d_flags = S.d_clean_len + count;
+#define MELF_HUFF_GO(GG, SH, MODE)                                                                        \
+    melf_jpeg_huffman_kernel<GG, SH, MODE><<<ctas, 32, hsmem, stream>>>(                                  \
+        d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, d_flags, count, g, mr, S.d_coef)
 #define MELF_HUFF_LAUNCH(GG)                                                                              \
     case GG:                                                                                              \
         if (shared_tables) {                                                                              \
-            melf_jpeg_huffman_kernel<GG, true><<<ctas, 32, hsmem, stream>>>(                              \
-                d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, count, g, mr, S.d_coef);            \
+            if (fast) { MELF_HUFF_GO(GG, true, HUFF_FAST); MELF_HUFF_GO(GG, true, HUFF_REDO); }           \
+            else MELF_HUFF_GO(GG, true, HUFF_CAREFUL);                                                    \
         } else {                                                                                          \
-            JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false>,                           \
+            JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false, HUFF_CAREFUL>,             \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
-            melf_jpeg_huffman_kernel<GG, false><<<ctas, 32, hsmem, stream>>>(                             \
-                d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, count, g, mr, S.d_coef);            \
+            JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false, HUFF_FAST>,                \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
+            JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false, HUFF_REDO>,                \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hsmem));     \
+            if (fast) { MELF_HUFF_GO(GG, false, HUFF_FAST); MELF_HUFF_GO(GG, false, HUFF_REDO); }         \
+            else MELF_HUFF_GO(GG, false, HUFF_CAREFUL);                                                   \
         }                                                                                                 \
         break;
     switch (G) {
@@ -1047,6 +1113,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         MELF_HUFF_LAUNCH(2)
         MELF_HUFF_LAUNCH(1)
     }
+#undef MELF_HUFF_GO
 #undef MELF_HUFF_LAUNCH
     if (spans) { cudaEventRecord(spans[2][1], stream); cudaEventRecord(spans[3][0], stream); }
     const int idct_blocks = (br.bx1[0] - br.bx0[0] + 1) * (br.by1[0] - br.by0[0] + 1) +
@@ -1062,6 +1129,6 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     melf_jpeg_color_kernel<<<cgrid, cthreads, 0, stream>>>(ca, g);
     if (spans) cudaEventRecord(spans[4][1], stream);
     JPEG_CUDA(cudaGetLastError());
-    if (launches) *launches += 4;
+    if (launches) *launches += fast ? 5 : 4;
     return 0;
 }
