@@ -456,10 +456,10 @@ def ingest_leg(torch, D, wl, n_streams, reps=3):
             'h2d_gbs_per_rank': [round(r, 2) for r in rates],
             'golden_lines_checked_per_rank': len(base), 'golden_line_mismatches_per_rank': [int(b) for b in bad_all],
             'distinct_streams': len(base),
-            'workload_note': 'the streams are the %d sample files repeated; the Huffman stage sorts a chunk by entropy-coded '
-                             'length, so the lanes of a warp decode identical copies here and do not diverge -- with different '
-                             'files in every warp the rate measured the same within 2 %% (profiles/r02_huffman_variants.txt, '
-                             'DESIGN.md section 10)' % len(base),
+            'workload_note': 'the streams are the %d sample files repeated; the Huffman stage orders a chunk by entropy-coded '
+                             'length in 1 KB buckets, so a warp decodes different files, as in real use (an exact sort would '
+                             'put byte-identical copies into one warp: profiles/r02_huffman_variants.txt, DESIGN.md section 10)'
+                             % len(base),
             'route': 'melf_read_jpeg_batch (the default route of get_meter_values for baseline JPEG files): header walk '
                      'on the host, Huffman / IDCT / upsampling / colour on the GPU (bit-identical to cv2.imread), '
                      'then the same locate and dial kernels; GPU-bound (Huffman stage), DESIGN.md section 8'}

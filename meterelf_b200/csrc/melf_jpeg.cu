@@ -410,6 +410,28 @@ __device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
 //                 without a flagged stream return at once, the others clear the coefficients of the flagged
 //                 streams (the fast pass wrote rubbish behind the end of the data) and decode them as HUFF_CAREFUL.
 enum { HUFF_CAREFUL = 0, HUFF_FAST = 1, HUFF_REDO = 2 };
+#ifndef MELF_HUFF_LEAN
+#define MELF_HUFF_LEAN 1     // 0: HUFF_FAST as the generic loop with its restart / out-of-data parts compiled out (A/B builds)
+#endif
+
+// The decoder consumes its stream one 32-bit word per ~5 symbols and holds one word in flight (nextw): a word that
+// misses L1 comes from L2 / DRAM (the destuffed chunk does not fit L2) in 600+ clk, several times the ~300 clk
+// between two refills -- 28 % of all stall samples of the lean loop sat on the first use of that word
+// (profiles/r02_ncu_huffman_lean_source.txt).  So every eighth refill asks for the 32-byte sector one cache line
+// further on; the request needs no register and nothing waits for it.
+#ifndef MELF_HUFF_DEBUG
+#define MELF_HUFF_DEBUG 0
+#endif
+#ifndef MELF_HUFF_PREFETCH
+#define MELF_HUFF_PREFETCH 0     // measured: no gain, the lone launch 10.8 -> 11.7 ms (profiles/r02_huffman_variants.txt)
+#endif
+__device__ __forceinline__ void huff_prefetch(const uint32_t *src, int wp, int wmax, bool need)
+{
+#if MELF_HUFF_PREFETCH
+    if (need && (wp & 7) == 0 && wp + 32 < wmax)
+        asm volatile("prefetch.global.L1 [%0];" :: "l"(src + wp + 32));
+#endif
+}
 
 template <int G, bool SHARED, int MODE>
 __global__ void __launch_bounds__(32)
@@ -455,7 +477,11 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     // makes the compiler rebuild the window base in every iteration, on the critical path of the lookup)
     const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(&T.lut[0][0]);
     const int restart = (int)desc[img].restart;
+#if MELF_HUFF_DEBUG & 1       // measurement only: every lane reads the stream of the warp's first lane
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[order[img0]].clean_off);
+#else
     const uint32_t *src = reinterpret_cast<const uint32_t *>(clean + desc[img].clean_off);
+#endif
     const int wmax = (int)((clean_len[img] + 3) >> 2);
     const uint32_t avail_bits = clean_len[img] * 8u;           // parse_stream caps a scan at 256 MB
     int16_t *kept = coef + (size_t)img * R.stride_blocks * 64;
@@ -482,6 +508,100 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
     const int nslots = g.nslots;
     const uint32_t slot_info = g.slot_info;
     int left = (R.my1 * mcus_x + R.mx1 + 1) * nslots;          // nothing after the last kept MCU is needed
+    if (MODE == HUFF_FAST && MELF_HUFF_LEAN) {
+        // The lean loop.  Same decoding as the loop below, minus restart / out-of-data handling, written for the
+        // latency of ONE warp (466 clk and 82 instructions per symbol before, profiles/r02_ncu_huffman_fast_source.txt):
+        // table bases of the current component kept in registers (no table index arithmetic per symbol), the shared
+        // window base computed once by volatile asm (the compiler re-derived it from SR_CgaCtaId in every iteration),
+        // 32-bit coefficient offsets instead of 64-bit pointer selects, sign extension without compares.
+        uint32_t lut0;
+        asm volatile("{\n\t.reg .u64 a;\n\tcvta.to.shared.u64 a, %1;\n\tcvt.u32.u64 %0, a;\n\t}"
+                     : "=r"(lut0) : "l"(&T.lut[0][0]));
+        constexpr uint32_t kTab = kLutEntries * 2;
+        uint32_t lut_dc = lut0, lut_ac = lut0 + kTab;                  // component 0
+        int16_t *const base = kept;
+        const uint32_t trash_off = (uint32_t)(R.stride_blocks - 1) * 64u;
+        uint32_t kept_off = 0, blk_off = keep ? 0u : trash_off;
+        uint32_t nextw2 = src[min(wp + 1, wmax + 2)];
+#if MELF_HUFF_DEBUG & 4       // measurement only: per-stream clocks and iterations instead of the redo flag
+        const long long dbg_t0 = clock64();
+        uint32_t dbg_iters = 0;
+#endif
+        while (left > 0) {
+#if MELF_HUFF_DEBUG & 4
+            ++dbg_iters;
+#endif
+            {
+                const bool need = bp >= 32;
+                bp -= need ? 32 : 0;
+                w0 = need ? w1 : w0;
+                w1 = need ? __byte_perm(nextw, 0, 0x0123) : w1;
+                wp += need ? 1 : 0;
+                // two words in flight (nextw = word wp, nextw2 = word wp + 1): the load issued here is used two
+                // refills (~3000 clk) later; with one word in flight 28 % of all stall samples sat on its first use
+                nextw = need ? nextw2 : nextw;
+                const uint32_t *ptr = src + min(wp + 1, wmax + 2);     // >= 16 zero bytes follow the destuffed data
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p ld.global.nc.u32 %0, [%1];\n\t}"
+                             : "+r"(nextw2) : "l"(ptr), "r"((int)need));
+            }
+            const bool is_dc = k == 0;
+            const uint32_t win = __funnelshift_l(w1, w0, bp);
+            const uint32_t e = lds_u16((is_dc ? lut_dc : lut_ac) + ((win >> (32 - kLook)) << 1));
+            int len = (int)(e >> 8), sym = (int)(e & 255);
+            if (e == 0) {                                    // code longer than kLook bits (rare)
+                const int t = (comp ? 2 : 0) + (is_dc ? 0 : 1);
+                const uint32_t win16 = win >> 16;
+                int l = kLook + 1;
+#pragma unroll
+                for (int j = 0; j < 16 - kLook - 1; j++) l += win16 >= T.limit[t][j] ? 1 : 0;
+                const bool valid = win16 < T.limit[t][16 - kLook - 1];
+                const int idx = (int)(win16 >> (16 - l)) + T.valoff[t][l - kLook - 1];
+                sym = valid ? T.vals[t][idx & 255] : 0;
+                len = l;
+            }
+            const int s = sym & 15, r = sym >> 4;
+            const uint32_t field = win << len;                          // the s extra bits from bit 31 down
+            const uint32_t bits = (field >> 1) >> (31 - s);
+            bp += len + s;
+            // EXTEND: a field whose first bit is 0 stands for bits - (2^s - 1); s = 0 gives 0 either way
+            const int v = (int)bits + (~((int)field >> 31) & (1 - (1 << s)));
+            pred += is_dc ? v : 0;
+            const int pos = is_dc ? 0 : k + r;
+            const bool st = is_dc || (s != 0 && pos < 64);
+#if MELF_HUFF_DEBUG & 2       // measurement only: every store goes to the spare block
+            base[trash_off + (uint32_t)(pos & 63) + (st ? 0u : 0u)] = (int16_t)(is_dc ? pred : v);
+#else
+            base[st ? blk_off + (uint32_t)pos : trash_off] = (int16_t)(is_dc ? pred : v);
+#endif
+            k = (is_dc || s != 0) ? pos + 1 : (r == 15 ? k + 16 : 64);
+            if (k >= 64) {
+                k = 0;
+                kept_off += keep ? 64u : 0u;
+                left--;
+                const bool mcu_end = slot + 1 == nslots;
+                slot = mcu_end ? 0 : slot + 1;
+                const int ncomp = (int)(slot_info >> (4 * slot) & 3);
+                if (ncomp != comp) {
+                    const int t0 = pred;
+                    pred = pred1; pred1 = pred2; pred2 = t0;
+                    comp = ncomp;
+                    lut_dc = lut0 + (comp ? 2 * kTab : 0u);
+                    lut_ac = lut_dc + kTab;
+                }
+                if (mcu_end && --run == 0) {
+                    keep = !keep;
+                    run = keep ? run_keep : run_skip;
+                }
+                blk_off = keep ? kept_off : trash_off;
+            }
+        }
+#if MELF_HUFF_DEBUG & 4
+        flags[img] = ((uint32_t)((clock64() - dbg_t0) >> 9) << 16) | ((dbg_iters >> 2) & 0xffffu);
+        return;
+#endif
+        flags[img] = (uint32_t)(wp - 2) * 32u + (uint32_t)bp > avail_bits ? 1u : 0u;
+        return;
+    }
     while (left > 0) {
         {   // refill: w0 is used up
             const bool need = bp >= 32;
@@ -497,6 +617,7 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
                              : "+r"(nextw) : "l"(ptr), "r"((int)need));
             } else
             if (need) nextw = wp < wmax ? src[wp] : 0;
+            huff_prefetch(src, wp, wmax, need);
         }
         const bool is_dc = k == 0;
         const int t = (comp ? 2 : 0) + (is_dc ? 0 : 1);
@@ -1004,10 +1125,16 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     {
         uint32_t *order = reinterpret_cast<uint32_t *>(S.h_stage + order_off);
         for (int i = 0; i < count; i++) order[i] = (uint32_t)i;
-        static const bool sorted = !(std::getenv("MELF_JPEG_SORT") && !std::atoi(std::getenv("MELF_JPEG_SORT")));
-        if (sorted)
-            std::sort(order, order + count, [&](uint32_t a, uint32_t b) {
-                return descs[a].scan_len != descs[b].scan_len ? descs[a].scan_len > descs[b].scan_len : a < b; });
+        // ... in buckets of 1 KB (MELF_JPEG_SORT=<shift>, default 10; 0 = stream order, 1 = exact lengths): inside a
+        // bucket the streams keep their order.  A finer order buys nothing (lanes within 3 % of each other), and an
+        // exact one puts byte-identical streams -- a benchmark's repeated files -- into one warp, whose lanes then
+        // hit the same L2 slices with every store (profiles/r02_huffman_variants.txt: slower than stream order).
+        static const int sort_shift = std::getenv("MELF_JPEG_SORT") ? std::atoi(std::getenv("MELF_JPEG_SORT")) : 10;
+        if (sort_shift > 0) {
+            const int sh = sort_shift == 1 ? 0 : sort_shift;
+            std::stable_sort(order, order + count, [&](uint32_t a, uint32_t b) {
+                return (descs[a].scan_len >> sh) > (descs[b].scan_len >> sh); });
+        }
     }
     if (g.w != w || g.h != h) {
         if (err) *err = "the streams decode to " + std::to_string(g.w) + "x" + std::to_string(g.h) +
@@ -1092,7 +1219,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
 #define MELF_HUFF_LAUNCH(GG)                                                                              \
     case GG:                                                                                              \
         if (shared_tables) {                                                                              \
-            if (fast) { MELF_HUFF_GO(GG, true, HUFF_FAST); MELF_HUFF_GO(GG, true, HUFF_REDO); }           \
+            if (fast) { MELF_HUFF_GO(GG, true, HUFF_FAST); if (!(MELF_HUFF_DEBUG & 4)) MELF_HUFF_GO(GG, true, HUFF_REDO); }           \
             else MELF_HUFF_GO(GG, true, HUFF_CAREFUL);                                                    \
         } else {                                                                                          \
             JPEG_CUDA(cudaFuncSetAttribute(melf_jpeg_huffman_kernel<GG, false, HUFF_CAREFUL>,             \
@@ -1114,6 +1241,19 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         MELF_HUFF_LAUNCH(1)
     }
 #undef MELF_HUFF_GO
+#if MELF_HUFF_DEBUG & 4
+    if (const char *dump = std::getenv("MELF_HUFF_DUMP")) {
+        std::vector<uint32_t> hf((size_t)count), ho((size_t)count);
+        cudaStreamSynchronize(stream);
+        cudaMemcpy(hf.data(), d_flags, (size_t)count * 4, cudaMemcpyDeviceToHost);
+        if (FILE *fp = std::fopen(dump, "w")) {
+            const uint32_t *order = reinterpret_cast<const uint32_t *>(S.h_stage + order_off);
+            for (int i = 0; i < count; i++)
+                std::fprintf(fp, "%d %u %u %u %u\n", i, order[i], descs[order[i]].scan_len, (hf[order[i]] >> 16) << 9, (hf[order[i]] & 0xffffu) << 2);
+            std::fclose(fp);
+        }
+    }
+#endif
 #undef MELF_HUFF_LAUNCH
     if (spans) { cudaEventRecord(spans[2][1], stream); cudaEventRecord(spans[3][0], stream); }
     const int idct_blocks = (br.bx1[0] - br.bx0[0] + 1) * (br.by1[0] - br.by0[0] + 1) +
