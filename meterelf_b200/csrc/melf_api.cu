@@ -124,6 +124,7 @@ struct melf_ctx {
     // JPEG ingest (melf_jpeg.cu): [0] caller-stream path, [1 ..] pipeline slots of melf_read_jpeg_batch
     MelfJpegState *jpeg[1 + kJpegSlots] = {};
     cudaStream_t jstreams[kJpegSlots] = {};
+    cudaStream_t jcopy = nullptr;                 // the uploads of melf_read_jpeg_batch, in chunk order
     uint8_t *d_jchunk[kJpegSlots] = {};
     size_t jchunk_bytes = 0;
     melf_result *d_jres[kJpegSlots] = {};
@@ -478,6 +479,7 @@ void free_ctx(melf_ctx *ctx)
         cudaFree(ctx->d_jchunk[i]); cudaFree(ctx->d_jres[i]); cudaFree(ctx->d_jkeys[i]);
     }
     if (ctx->h_jres) cudaFreeHost(ctx->h_jres);
+    if (ctx->jcopy) cudaStreamDestroy(ctx->jcopy);
     delete ctx;
 }
 
@@ -883,7 +885,11 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
             MELF_CUDA(ctx, cudaMalloc(&ctx->d_jkeys[i], sizeof(u64) * kJpegChunkFrames));
         }
         MELF_CUDA(ctx, cudaMallocHost(&ctx->h_jres, sizeof(melf_result) * kJpegChunkFrames * kJpegSlots));
+        MELF_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->jcopy, cudaStreamNonBlocking));
     }
+    // all uploads of a batch on ONE stream, in chunk order (MELF_JPEG_COPY_STREAM=0: on the chunks' streams, A/B runs)
+    static const bool own_copy_stream = !(std::getenv("MELF_JPEG_COPY_STREAM") && !std::atoi(std::getenv("MELF_JPEG_COPY_STREAM")));
+    const cudaStream_t copy_stream = own_copy_stream ? ctx->jcopy : nullptr;
     if (need > ctx->jchunk_bytes) {
         for (int i = 0; i < slots; i++) {
             if (ctx->d_jchunk[i]) cudaFree(ctx->d_jchunk[i]);
@@ -919,7 +925,7 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
         const auto t_host = std::chrono::steady_clock::now();
         rc = melf_jpeg_decode_range(&ctx->jpeg[1 + b], batch, f0, nf, h, w, jx0, geom.crop_y0,
                                     jw, geom.crop_h, ctx->d_jchunk[b], pitch, frame_bytes, st, &err,
-                                    &launches, spans.get());
+                                    &launches, spans.get(), copy_stream);
         spans.commit(ctx);
         host_ms += ms_since(t_host);
         g_launches += launches;

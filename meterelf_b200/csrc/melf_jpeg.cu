@@ -1014,7 +1014,7 @@ int melf_jpeg_probe(const uint8_t *jpeg, size_t len, int *h, int *w, int *ncomp,
 int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, int first, int count,
                            int h, int w, int x0, int y0, int cw, int ch, uint8_t *d_out,
                            size_t row_stride, size_t frame_stride, cudaStream_t stream,
-                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2])
+                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2], cudaStream_t copy_stream)
 {
     if (count <= 0) return 0;
     if (!*state) *state = new MelfJpegState();
@@ -1182,21 +1182,28 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     JPEG_CUDA(grow(&S.d_planes, &S.planes_cap, (size_t)count * g.plane_bytes));
     (void)S.d_desc; (void)S.desc_cap;
 
-    if (spans) cudaEventRecord(spans[0][0], stream);
+    // The upload goes on the caller's copy stream when there is one: the chunks of a batch then cross PCIe back to
+    // back in issue order, whatever the chunk streams are busy with (their copies used to start late behind other
+    // chunks' kernels: profiles/r02_ingest_trace_65536.txt), and `stream` waits for the event.  The caller makes
+    // sure the previous work on this state has finished before it calls again (it reads d_blob).
+    const cudaStream_t cs = copy_stream ? copy_stream : stream;
+    if (spans) cudaEventRecord(spans[0][0], cs);
     if (direct) {
-        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes, cudaMemcpyHostToDevice, stream));
-        JPEG_CUDA(cudaMemcpyAsync(S.d_blob + desc_bytes, batch.jpeg + blob0, blob_bytes, cudaMemcpyHostToDevice, stream));
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes, cudaMemcpyHostToDevice, cs));
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob + desc_bytes, batch.jpeg + blob0, blob_bytes, cudaMemcpyHostToDevice, cs));
     } else {
-        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes + blob_bytes, cudaMemcpyHostToDevice, stream));
+        JPEG_CUDA(cudaMemcpyAsync(S.d_blob, S.h_stage, desc_bytes + blob_bytes, cudaMemcpyHostToDevice, cs));
     }
-    JPEG_CUDA(cudaEventRecord(S.uploaded, stream));
+    JPEG_CUDA(cudaEventRecord(S.uploaded, cs));
     S.upload_pending = true;
+    if (spans) cudaEventRecord(spans[0][1], cs);
     const JpegDesc *d_desc = reinterpret_cast<const JpegDesc *>(S.d_blob);
     const uint32_t *d_order = reinterpret_cast<const uint32_t *>(S.d_blob + order_off);
     const uint8_t *d_streams = S.d_blob + desc_bytes;
-    JPEG_CUDA(cudaMemsetAsync(S.d_coef, 0, coef_elems * 2, stream));
+    JPEG_CUDA(cudaMemsetAsync(S.d_coef, 0, coef_elems * 2, stream));        // (under the upload when that has its own stream)
+    if (cs != stream) JPEG_CUDA(cudaStreamWaitEvent(stream, S.uploaded, 0));
 
-    if (spans) { cudaEventRecord(spans[0][1], stream); cudaEventRecord(spans[1][0], stream); }
+    if (spans) cudaEventRecord(spans[1][0], stream);
     melf_jpeg_destuff_kernel<<<count, DESTUFF_THREADS, 0, stream>>>(d_streams, d_desc, S.d_clean, S.d_clean_len);
     if (spans) { cudaEventRecord(spans[1][1], stream); cudaEventRecord(spans[2][0], stream); }
     // lanes per warp: few enough that the batch still reaches every SM sub-partition

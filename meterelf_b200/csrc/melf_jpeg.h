@@ -25,7 +25,9 @@ int melf_jpeg_probe(const uint8_t *jpeg, size_t len, int *h, int *w, int *ncomp,
 int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, int first, int count,
                            int h, int w, int x0, int y0, int cw, int ch, uint8_t *d_out,
                            size_t row_stride, size_t frame_stride, cudaStream_t stream,
-                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2] = nullptr);
-// spans (optional): 5 event pairs recorded around upload + clear, destuff, Huffman, IDCT, colour.
+                           std::string *err, uint64_t *launches, cudaEvent_t (*spans)[2] = nullptr,
+                           cudaStream_t copy_stream = nullptr);
+// spans (optional): 5 event pairs recorded around upload, destuff, Huffman, IDCT, colour.
+// copy_stream (optional): the stream the host-to-device copy is issued on (`stream` waits for it).
 
 void melf_jpeg_state_free(MelfJpegState *state);
