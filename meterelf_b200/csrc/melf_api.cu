@@ -64,7 +64,8 @@ std::string g_create_error;
 
 constexpr int kChunkFrames = 512;      // frames per pipelined chunk in melf_read_batch
 constexpr int kJpegChunkFrames = 8192; // most streams per pipelined chunk in melf_read_jpeg_batch ...
-constexpr int kJpegSlots = 8;          // ... and (at most) chunks in flight: the Huffman stage runs one lane per stream
+constexpr int kJpegSlots = 16;         // ... and (at most) chunks in flight: the Huffman stage runs one lane per stream
+constexpr int kJpegSlotsDefault = 8;   // (MELF_JPEG_SLOTS overrides, up to kJpegSlots)
                                        // at low occupancy, so several chunks' kernels share the GPU
 constexpr int kScratchSlots = 3 + kJpegSlots;   // [0] caller stream, [1], [2] melf_read_batch, then JPEG
 constexpr long long kTcMaxItems = 4096; // work items per prep + correlation launch pair (~400 MB scratch)
@@ -865,7 +866,7 @@ int melf_read_jpeg_batch(melf_ctx *ctx, const uint8_t *jpeg, const uint64_t *off
     // the batch is cut so that every slot is busy, in multiples of 512 streams
     static const int slots = [] {
         const char *e = std::getenv("MELF_JPEG_SLOTS");
-        const int v = e ? std::atoi(e) : kJpegSlots;         // measured: profiles/r01_v11_jpeg_sweep.txt
+        const int v = e ? std::atoi(e) : kJpegSlotsDefault;  // measured: profiles/r01_v11_jpeg_sweep.txt, r02_huffman_variants.txt
         return v < 1 ? 1 : v > kJpegSlots ? kJpegSlots : v;
     }();
     static const int chunk_cap = [] {

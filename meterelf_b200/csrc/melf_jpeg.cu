@@ -1208,7 +1208,8 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
     if (spans) { cudaEventRecord(spans[1][1], stream); cudaEventRecord(spans[2][0], stream); }
     // lanes per warp: few enough that the batch still reaches every SM sub-partition
     int G = 16;                                  // measured: profiles/r01_v11_jpeg_sweep.txt
-    while (G > 2 && count / G < 256) G >>= 1;
+    static const int min_warps = std::getenv("MELF_JPEG_MIN_WARPS") ? std::atoi(std::getenv("MELF_JPEG_MIN_WARPS")) : 256;
+    while (G > 2 && count / G < min_warps) G >>= 1;
     static const int forced = std::getenv("MELF_JPEG_LANES") ? std::atoi(std::getenv("MELF_JPEG_LANES")) : 0;
     if (forced == 1 || forced == 2 || forced == 4 || forced == 8 || forced == 16 || forced == 32) G = forced;
     const int ctas = (count + G - 1) / G;
