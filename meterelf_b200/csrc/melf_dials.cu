@@ -19,6 +19,12 @@
 //                    static tables (per-pixel angle / squared distance / sort order depend
 //                    only on params), so dial positions are bit-identical to the oracle.
 #include "melf_common.cuh"
+#ifndef MELF_DIALS_U4
+#define MELF_DIALS_U4 2      // unroll factors of the kernel's loops (code size against loop overhead: the kernel is
+#define MELF_DIALS_U2 1      // ~75 KB of SASS and 18 % of its stall samples are instruction fetch)
+#endif
+#define MELF_PRAGMA_(x) _Pragma(#x)
+#define MELF_UNROLL(n) MELF_PRAGMA_(unroll n)
 #include "melf_args.h"
 
 namespace {
@@ -113,12 +119,26 @@ __device__ int filled_area2(const u64 fa, const u64 fb, const int lane)
     return __reduce_add_sync(0xffffffffu, a);
 }
 
-// Python float % for a positive modulus
-__device__ __forceinline__ double py_mod_pos(double a, double m)
+// Python float % for a positive modulus.  Not inlined: fmod is ~110 instructions, and the kernel's code size costs
+// time (18 % of its stall samples were instruction fetch with five inlined copies).
+__device__ __noinline__ double py_mod_pos(double a, double m)
 {
     double r = fmod(a, m);
     if (r != 0.0) {
         if (r < 0.0) r = __dadd_rn(r, m);
+    } else {
+        r = 0.0;
+    }
+    return r;
+}
+
+// Python float % 1.0: fmod(a, 1) is a - trunc(a), an exact subtraction (the zero result's sign does not matter, it
+// becomes +0.0 as in py_mod_pos)
+__device__ __forceinline__ double py_mod1(double a)
+{
+    double r = __dsub_rn(a, trunc(a));
+    if (r != 0.0) {
+        if (r < 0.0) r = __dadd_rn(r, 1.0);
     } else {
         r = 0.0;
     }
@@ -130,7 +150,7 @@ __device__ double angle_by_vector(double x, double y)
 {
     if (y == 0.0) return x > 0.0 ? 0.25 : x < 0.0 ? 0.75 : __longlong_as_double(0x7ff8000000000000ll);
     const double at = __ddiv_rn(atan(__ddiv_rn(x, y)), 2 * 3.141592653589793);
-    return py_mod_pos(__dadd_rn(-at, y > 0.0 ? 0.5 : 0.0), 1.0);
+    return py_mod1(__dadd_rn(-at, y > 0.0 ? 0.5 : 0.0));
 }
 
 __device__ __forceinline__ bool near_momentum(double a, double mom)
@@ -143,7 +163,7 @@ __device__ __forceinline__ bool near_momentum(double a, double mom)
 
 __device__ __forceinline__ int carry_digit(double r, double lower)
 {
-    const double frac = py_mod_pos(r, 1.0);
+    const double frac = py_mod1(r);
     int v = (int)r + ((frac > 0.55 && lower <= 2.0) ? 1 : 0) - ((frac < 0.45 && lower >= 8.0) ? 1 : 0);
     v %= 10;
     return v < 0 ? v + 10 : v;
@@ -231,7 +251,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         const uint32_t pix_s = (uint32_t)__cvta_generic_to_shared(pix);
         const uintptr_t end = reinterpret_cast<uintptr_t>(A.bgr_end);
         if (ch < n_chunk && V) {
-#pragma unroll 4
+MELF_UNROLL(MELF_DIALS_U4)
             for (int rr = sub; rr < D.win_h; rr += 2) {
                 if (!((RV >> rr) & 1)) continue;
                 const uintptr_t rowp = reinterpret_cast<uintptr_t>(win0 + (size_t)rr * A.row_stride);
@@ -288,7 +308,7 @@ melf_dials_kernel(const MelfDialsArgs A)
     {
         uint32_t *bal_s = reinterpret_cast<uint32_t *>(nm_s[wslot]);       // 128 words >= 4096 / 32
         const float s_lo_f = (float)(lo_s - 1), s_hi_f = (float)(hi_s + 1);
-#pragma unroll 2
+MELF_UNROLL(MELF_DIALS_U2)
         for (int base = 0; base < n_need; base += 32) {
             const int p = base + lane;
             const bool valid = p < n_need;
@@ -416,7 +436,7 @@ melf_dials_kernel(const MelfDialsArgs A)
                     if ((wh >> lane) & 1) tbuf[n_lo + __popc(wh & below)] = tx_hi;
                     __syncwarp();
                     const double ty = D.termy[2 * l + half];
-#pragma unroll 4
+MELF_UNROLL(MELF_DIALS_U4)
                     for (int i = 0; i < n; ++i) {
                         mom_x = __dadd_rn(mom_x, tbuf[i]);
                         mom_y = __dadd_rn(mom_y, ty);
@@ -442,7 +462,7 @@ melf_dials_kernel(const MelfDialsArgs A)
         double min_angle = 0.0;
         int n_unwrapped = 0;
         int rpos_nx = lane < D.n_ring ? (int)rpos[lane] : 0;      // fetched one iteration ahead
-#pragma unroll 2
+MELF_UNROLL(MELF_DIALS_U2)
         for (int base = 0; base < D.n_ring; base += 32) {
             const int e = base + lane;
             bool kept = false, wrapped = false;
@@ -478,7 +498,7 @@ melf_dials_kernel(const MelfDialsArgs A)
                 // keys) come first, then the others, each group in table order
                 const int cut = min(2, (n_kept - 3) / 2);
                 const int n_wrapped = n_kept - n_unwrapped;
-#pragma unroll 4
+MELF_UNROLL(MELF_DIALS_U4)
                 for (int k = cut; k < n_kept - cut; ++k) {
                     const bool w = k < n_wrapped;
                     const int e = klist[w ? n_unwrapped + k : k - n_wrapped];
