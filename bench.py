@@ -486,9 +486,12 @@ def api_leg(wl, n_files):
                 fp.write(data)
         names = [paths[i % len(paths)] for i in range(n_files)]
         list(meterelf_b200.get_meter_values(wl.params_file, names))          # warm-up (page-locked blob pool at its final size)
-        t0 = time.perf_counter()
-        got = list(meterelf_b200.get_meter_values(wl.params_file, names))
-        dt = time.perf_counter() - t0
+        runs = []
+        for _ in range(3):          # host-bound and noisy from box to box and run to run: the median of three
+            t0 = time.perf_counter()
+            got = list(meterelf_b200.get_meter_values(wl.params_file, names))
+            runs.append(time.perf_counter() - t0)
+        dt = sorted(runs)[1]
         bad = 0
         for (i, item) in enumerate(got[:len(base)]):
             exp = wl.gs.expected[base[i][0]]
@@ -498,7 +501,8 @@ def api_leg(wl, n_files):
     finally:
         shutil.rmtree(d, ignore_errors=True)
     return {'metric': 'get_meter_values(params_file, filenames) over JPEG files on a RAM disk', 'value': n_files / dt,
-            'unit': 'files/s', 'files': n_files, 'seconds': dt, 'golden_line_mismatches': int(bad),
+            'unit': 'files/s', 'files': n_files, 'seconds': dt, 'files_per_s_all_runs': [round(n_files / t) for t in runs],
+            'golden_line_mismatches': int(bad),
             'golden_lines_checked': len(base),
             'note': 'one Python process: file reads and header probes batched on host threads behind the C ABI into '
                     'pooled page-locked buffers, two batches in flight (files of batch k + 1 read under the GPU work of '
