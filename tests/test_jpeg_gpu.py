@@ -130,6 +130,26 @@ def test_streams_cut_short_decode_like_libjpeg():
     assert n >= 150 and n_vec >= 60
 
 
+def test_intact_and_cut_streams_in_one_warp():
+    """The lean Huffman loop only FLAGS a stream that read past its end; the careful redo pass behind it clears and
+    decodes the flagged streams again and must leave their neighbours in the warp alone.  One batch, intact and
+    cut streams alternating (several cut points, so that flagged and unflagged lanes share every warp), twice in a
+    row on the same buffers."""
+    eng = golden_set(1).engine()
+    streams = load_streams(os.path.join(GOLDEN, 'jpeg_subset.npz'))
+    base = max(batches([s for s in streams if s[2] == (640, 480)]), key=len)      # one geometry, most streams
+    assert len(base) >= 3
+    mixed = []
+    for (k, s) in enumerate((base * 16)[:48]):
+        frac = (1.0, 0.5, 1.0, 0.93, 0.77, 1.0, 0.35, 0.999)[k % 8]
+        mixed.append(s[1] if frac == 1.0 else s[1][:int(len(s[1]) * frac)])
+    want = [oracle.decode_jpeg(m) for m in mixed]
+    for _ in range(2):
+        got = decode_on_gpu(eng, mixed, 640, 480)
+        for (k, (img, ref)) in enumerate(zip(got, want)):
+            assert np.array_equal(img, ref), (k, len(mixed[k]), np.argwhere(img != ref)[:3])
+
+
 def test_readings_from_streams_cut_short_match_the_oracle():
     """melf_read_jpeg_batch on truncated streams: the rectangle-only decode (kept / skipped MCU runs, early
     stop) has to leave the same grey MCUs behind as the full decode, so the readings -- or the errors --
