@@ -433,8 +433,10 @@ __device__ __forceinline__ void huff_prefetch(const uint32_t *src, int wp, int w
 #endif
 }
 
-template <int G, bool SHARED, int MODE>
-__global__ void __launch_bounds__(32)
+// W warps per CTA (W > 1 only with SHARED tables and the lean loop): one table set serves W warps (8 by default), so
+// that shared memory (9.5 KB per table set) no longer caps the resident warps at 24 per SM.
+template <int G, bool SHARED, int MODE, int W = 1>
+__global__ void __launch_bounds__(32 * W)
 melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__restrict__ clean,
                          const JpegDesc *__restrict__ desc, const uint32_t *__restrict__ order,
                          const uint32_t *__restrict__ clean_len, uint32_t *__restrict__ flags,
@@ -442,8 +444,17 @@ melf_jpeg_huffman_kernel(const uint8_t *__restrict__ blob, const uint8_t *__rest
 {
     extern __shared__ __align__(16) unsigned char huff_smem[];
     HuffSmem *S = reinterpret_cast<HuffSmem *>(huff_smem);
-    const int lane = threadIdx.x;
-    const int img0 = blockIdx.x * G;
+    const int lane = threadIdx.x & 31;
+    const int img0 = (blockIdx.x * W + (threadIdx.x >> 5)) * G;
+    if (W > 1) {
+        // (SHARED tables, lean loop) warp 0 builds the CTA's table set from the CTA's first stream
+        if (threadIdx.x < 32) {
+            const JpegDesc d = desc[order[blockIdx.x * W * G]];
+            build_tables(S[0], blob + d.base, d, lane);
+        }
+        __syncthreads();
+        if (lane >= G || img0 + lane >= n) return;
+    } else
     if (MODE == HUFF_REDO) {
         const bool mine = lane < G && img0 + lane < n && flags[order[img0 + lane]] != 0;
         uint32_t todo = __ballot_sync(0xffffffffu, mine);
@@ -1224,9 +1235,21 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
 #define MELF_HUFF_GO(GG, SH, MODE)                                                                        \
     melf_jpeg_huffman_kernel<GG, SH, MODE><<<ctas, 32, hsmem, stream>>>(                                  \
         d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, d_flags, count, g, mr, S.d_coef)
+    static const int cta_warps = std::getenv("MELF_JPEG_CTA_WARPS") ? std::atoi(std::getenv("MELF_JPEG_CTA_WARPS")) : 8;   // 1, 4, 8, 16 measured: profiles/r02_huffman_variants.txt
+#define MELF_HUFF_GO4(GG)                                                                                 \
+    if (cta_warps == 16)                                                                                  \
+        melf_jpeg_huffman_kernel<GG, true, HUFF_FAST, 16><<<(ctas + 15) / 16, 512, hsmem, stream>>>(     \
+            d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, d_flags, count, g, mr, S.d_coef);       \
+    else if (cta_warps == 8)                                                                              \
+        melf_jpeg_huffman_kernel<GG, true, HUFF_FAST, 8><<<(ctas + 7) / 8, 256, hsmem, stream>>>(        \
+            d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, d_flags, count, g, mr, S.d_coef);       \
+    else                                                                                                  \
+        melf_jpeg_huffman_kernel<GG, true, HUFF_FAST, 4><<<(ctas + 3) / 4, 128, hsmem, stream>>>(        \
+            d_streams, S.d_clean, d_desc, d_order, S.d_clean_len, d_flags, count, g, mr, S.d_coef)
 #define MELF_HUFF_LAUNCH(GG)                                                                              \
     case GG:                                                                                              \
         if (shared_tables) {                                                                              \
+            if (fast && cta_warps >= 4 && !(MELF_HUFF_DEBUG & 4)) { MELF_HUFF_GO4(GG); MELF_HUFF_GO(GG, true, HUFF_REDO); } else \
             if (fast) { MELF_HUFF_GO(GG, true, HUFF_FAST); if (!(MELF_HUFF_DEBUG & 4)) MELF_HUFF_GO(GG, true, HUFF_REDO); }           \
             else MELF_HUFF_GO(GG, true, HUFF_CAREFUL);                                                    \
         } else {                                                                                          \
@@ -1249,6 +1272,7 @@ int melf_jpeg_decode_range(MelfJpegState **state, const MelfJpegBatch &batch, in
         MELF_HUFF_LAUNCH(1)
     }
 #undef MELF_HUFF_GO
+#undef MELF_HUFF_GO4
 #if MELF_HUFF_DEBUG & 4
     if (const char *dump = std::getenv("MELF_HUFF_DUMP")) {
         std::vector<uint32_t> hf((size_t)count), ho((size_t)count);
