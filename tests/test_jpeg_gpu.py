@@ -150,6 +150,34 @@ def test_intact_and_cut_streams_in_one_warp():
             assert np.array_equal(img, ref), (k, len(mixed[k]), np.argwhere(img != ref)[:3])
 
 
+def test_fresh_encodes_mixed_tables_restarts_and_cuts():
+    """Batches the committed streams do not offer: DHTs that differ from stream to stream (one table set per lane
+    instead of one per CTA), with and without restart intervals (careful loop / lean loop + redo pass), intact and
+    cut streams side by side.  Intact streams against cv2.imdecode, cut ones against the oracle."""
+    cv2 = pytest.importorskip('cv2')
+    from test_jpeg_oracle import fresh_encodes
+    eng = golden_set(1).engine()
+    enc = fresh_encodes(seed=5, sizes=((120, 200), (481, 643)))
+    for sampling in ('420', '444'):
+        for with_restarts in (False, True):
+            for (h, w) in ((120, 200), (481, 643)):
+                group = [(t, d) for (t, d) in enc if t[:2] == (h, w) and t[4] == sampling and
+                         (with_restarts or t[3] != 'rst')]
+                if not group:
+                    continue
+                streams = []
+                for (k, (_t, d)) in enumerate(group * 3):
+                    frac = (1.0, 0.6, 1.0, 0.9)[k % 4]
+                    streams.append(d if frac == 1.0 else d[:int(len(d) * frac)])
+                got = decode_on_gpu(eng, streams, h, w)
+                for (k, (img, d)) in enumerate(zip(got, streams)):
+                    if len(d) == len(group[k % len(group)][1]):
+                        want = cv2.imdecode(np.frombuffer(d, np.uint8), cv2.IMREAD_COLOR)
+                    else:
+                        want = oracle.decode_jpeg(d)
+                    assert np.array_equal(img, want), (group[k % len(group)][0], len(d))
+
+
 def test_readings_from_streams_cut_short_match_the_oracle():
     """melf_read_jpeg_batch on truncated streams: the rectangle-only decode (kept / skipped MCU runs, early
     stop) has to leave the same grey MCUs behind as the full decode, so the readings -- or the errors --

@@ -94,3 +94,39 @@ def test_colour_space_choice_follows_libjpeg():
             else:
                 assert geometry is not None and geometry[:2] == tuple(v['shape']), (name, key)
     assert n_rgb == 8
+
+
+def fresh_encodes(seed=1, sizes=((16, 16), (33, 47), (120, 200), (481, 643))):
+    """(tag, stream) of synthetic images encoded here by cv2 / libjpeg: three qualities x {standard tables,
+    optimised Huffman tables, restart interval 5} x {4:2:0, 4:4:4 where this cv2 can ask for it}."""
+    import cv2
+    rng = np.random.default_rng(seed)
+    out = []
+    for (h, w) in sizes:
+        base = rng.integers(0, 256, (h // 8 + 2, w // 8 + 2, 3), dtype=np.uint8)
+        img = cv2.resize(base, (w, h), interpolation=cv2.INTER_CUBIC)
+        img = np.clip(img.astype(int) + rng.integers(-12, 13, img.shape), 0, 255).astype(np.uint8)
+        for q in (35, 75, 95):
+            for (label, extra) in (('std', []), ('opt', [cv2.IMWRITE_JPEG_OPTIMIZE, 1]),
+                                   ('rst', [cv2.IMWRITE_JPEG_RST_INTERVAL, 5])):
+                samplings = [('420', [])]
+                if hasattr(cv2, 'IMWRITE_JPEG_SAMPLING_FACTOR'):
+                    samplings.append(('444', [cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_444]))
+                for (sname, sflags) in samplings:
+                    (ok, buf) = cv2.imencode('.jpg', img, [cv2.IMWRITE_JPEG_QUALITY, q] + extra + sflags)
+                    assert ok
+                    out.append(((h, w, q, label, sname), buf.tobytes()))
+    return out
+
+
+def test_oracle_matches_cv2_on_fresh_encodes():
+    """Streams the fixtures do not hold: odd sizes, optimised Huffman tables (DHTs that differ from stream to
+    stream), restart intervals, 4:4:4 -- encoded and decoded by the installed cv2 on the spot."""
+    cv2 = pytest.importorskip('cv2')
+    n = 0
+    for (tag, data) in fresh_encodes():
+        want = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
+        assert np.array_equal(oracle.decode_jpeg(data), want), tag
+        n += 1
+    assert n >= 36
+
