@@ -151,6 +151,24 @@ def test_synthetic_blob_frames_all_branches(case):
     assert seen == {0, 2, 3}, seen        # the generator must reach the error branches
 
 
+@pytest.mark.parametrize('set_no,seed', [(1, 303), (2, 404)])
+def test_gpu_equals_the_unmodified_reference_run_live(set_no, seed, tmp_path):
+    """No fixture and no port in between: the unmodified reference (``oracle/_ref``, worker processes on the host
+    cores) and the CUDA path read the same freshly perturbed sample crops; status, failing / unreadable dials
+    and the float64 dial positions and value agree bit for bit."""
+    from helpers import write_params_file
+    from test_oracle_vs_reference_live import perturbed_crops
+    if not oracle.ref_available():
+        pytest.skip('oracle/_ref not built')
+    gs = golden_set(set_no)
+    crops = perturbed_crops(gs, seed, copies=3)
+    with oracle.RefPool(write_params_file(gs, tmp_path), crops, workers=4) as pool:
+        (_wall, ref_records) = pool.run()
+    got = gs.engine(cropped_input=True).read_frames(crops)
+    assert oracle.ref_mismatches(ref_records, got, len(gs.names)) == 0
+    assert sum(1 for r in ref_records if r['status'] == 0) > len(crops) // 2
+
+
 def test_dial_taps_with_discs_cut_by_the_rect_frame():
     """Set 3: needle masks, point counts and contour areas of components lying on the frame of
     the dials rect (cv2.findContours pads the image) -- GPU taps against the oracle's,
