@@ -42,3 +42,30 @@ def test_library_exports_every_declared_symbol():
 
 def test_python_binding_covers_the_header():
     assert set(declared_functions()) <= set(_engine._SYMBOLS)
+
+
+def test_the_stub_in_integration_md_has_the_library_s_struct_layout():
+    """INTEGRATION.md shows the ctypes stub a maintainer of the reference would add; its structures must be the
+    ones the library was compiled with (sizes and field offsets of melf_dial, melf_params, melf_result)."""
+    import numpy as np
+    path = os.path.join(os.path.dirname(HEADER), os.pardir, 'INTEGRATION.md')
+    with open(path) as fp:
+        text = fp.read()
+    code = []
+    for name in ('_Dial', '_Params'):
+        m = re.search(r'^class %s\(C\.Structure\):.*?\n(?=\n)' % name, text, flags=re.S | re.M)
+        assert m, name
+        code.append(m.group(0))
+    m = re.search(r'^RESULT = np\.dtype\(.*?align=True\)', text, flags=re.S | re.M)
+    assert m
+    code.append(m.group(0))
+    scope = {'C': ctypes, 'np': np}
+    exec('\n'.join(code), scope)
+    for (stub, ours) in ((scope['_Dial'], _engine.CDial), (scope['_Params'], _engine.CParams)):
+        assert ctypes.sizeof(stub) == ctypes.sizeof(ours)
+        assert [(f[0], getattr(stub, f[0]).offset) for f in stub._fields_] == \
+               [(f[0], getattr(ours, f[0]).offset) for f in ours._fields_]
+    assert scope['RESULT'].itemsize == _engine.RESULT_DTYPE.itemsize
+    assert {k: v[1] for (k, v) in scope['RESULT'].fields.items()} == \
+           {k: v[1] for (k, v) in _engine.RESULT_DTYPE.fields.items()}
+
