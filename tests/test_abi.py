@@ -69,3 +69,26 @@ def test_the_stub_in_integration_md_has_the_library_s_struct_layout():
     assert {k: v[1] for (k, v) in scope['RESULT'].fields.items()} == \
            {k: v[1] for (k, v) in _engine.RESULT_DTYPE.fields.items()}
 
+
+def test_header_compiles_as_plain_c_and_agrees_with_the_binding(tmp_path):
+    """include/meterelf_b200.h is a C header (C99, -pedantic clean): what gcc lays out is what the Python
+    binding assumes."""
+    import shutil
+    import subprocess
+    gcc = shutil.which('gcc')
+    if gcc is None:
+        import pytest
+        pytest.skip('no gcc')
+    src = tmp_path / 'layout.c'
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "meterelf_b200.h"\n'
+        'int main(void) { printf("%zu %zu %zu %zu %zu %d\\n", sizeof(melf_dial), sizeof(melf_params), '
+        'sizeof(melf_result), offsetof(melf_params, dials), offsetof(melf_result, dial_pos), MELF_MAX_DIALS); '
+        'return 0; }\n')
+    exe = tmp_path / 'layout'
+    subprocess.run([gcc, '-std=c99', '-Wall', '-Wextra', '-pedantic', '-Werror', '-I', os.path.dirname(HEADER),
+                    str(src), '-o', str(exe)], check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE).stdout.split()]
+    assert got == [ctypes.sizeof(_engine.CDial), ctypes.sizeof(_engine.CParams), _engine.RESULT_DTYPE.itemsize,
+                   _engine.CParams.dials.offset, _engine.RESULT_DTYPE.fields['dial_pos'][1], _engine.MAX_DIALS]
+
